@@ -1,0 +1,1234 @@
+// oracle.cpp -- CPU restatement of the GMRES + BoomerAMG hot path that Exawind/hypre-mini-app drives.
+//
+// *** TEST INFRASTRUCTURE ONLY. ***  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+// --impl reference legs may load this library.  The product (libb200hypre.so) never links or calls it.
+//
+// PARITY UNPINNED: the arithmetic of this path lives in hypre (LLNL/Exawind fork, no version pinned:
+// /root/reference/.gitmodules is empty, CMakeLists.txt:64 only has the floor "HYPRE 2.20.0").  hypre is absent
+// from /root/reference and from this image, and the reference ships no tests/golden vectors.
+// This file therefore restates hypre's *published* algorithms as summarised in SURVEY.md Appendix A and
+// anchors on the reference's own call sites:
+//   * call order Setup -> Solve                     /root/reference/src/HypreSystem.cpp:673-737
+//   * GMRES options (tol, max_iter, kspace)         /root/reference/src/HypreSystem.cpp:390-404
+//   * BoomerAMG option surface                      /root/reference/src/HypreSystem.cpp:119-326
+//   * block-row partition                           /root/reference/src/HypreSystem.cpp:525-544
+//   * generator numbering / values                  /root/reference/src/laplace_3d_weak_scaling.hpp:98-169,216-233,321,558,600
+//                                                   /root/reference/src/HypreSystem.cpp:1516,1540-1556
+// Pins that do exist are exercised in tests/: generator known answer x==1 and nnz=(3n-2)^3, scipy cross
+// checks (SpMV, P^T A P, GMRES solution), hand-computable PMIS/ext+i cases.
+//
+// Multi-rank semantics are modelled with "virtual ranks": one global matrix plus a row partition.  Every row is
+// stored in ParCSR order as seen by its owner (diagonal entry, then own-range columns, then off-range columns)
+// and the PMIS random measure restarts with seed 2747+rank at each rank's first row, so that an
+// N-GPU run can be compared with an N-virtual-rank oracle run.
+//
+// Threading: row-parallel loops use OpenMP; every floating-point value that feeds a discrete decision is
+// computed sequentially inside one row, so the hierarchy does not depend on the thread count.  Dot products
+// use a fixed 4096-element blocking so they do not depend on the thread count either.
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+namespace {
+
+typedef long long i64;
+
+struct Csr {
+  int nr = 0, nc = 0;
+  std::vector<int> ptr, col;
+  std::vector<double> val;
+  i64 nnz() const { return ptr.empty() ? 0 : ptr[nr]; }
+};
+
+static double now_s() {
+  return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// partition helpers (HypreSystem.cpp:525-544)
+// ---------------------------------------------------------------------------------------------------------
+static std::vector<int> block_partition(int n, int np) {
+  std::vector<int> p(np + 1);
+  int q = n / np, r = n % np;
+  for (int k = 0; k <= np; ++k) p[k] = q * k + std::min(k, r);
+  return p;
+}
+static inline int owner_of(const std::vector<int> &part, int i) {
+  return int(std::upper_bound(part.begin(), part.end(), i) - part.begin()) - 1;
+}
+
+// Put the rows of a matrix into ParCSR order: for the row owned by rank r the diagonal entry
+// (square matrices only) comes first, then the columns inside r's column range ascending, then the others ascending.
+static void parcsr_order(Csr &A, const std::vector<int> &rpart, const std::vector<int> &cpart, bool diag_first) {
+#pragma omp parallel
+  {
+    std::vector<std::pair<i64, double>> tmp;
+#pragma omp for schedule(dynamic, 1024)
+    for (int i = 0; i < A.nr; ++i) {
+      int r = owner_of(rpart, i);
+      int c0 = cpart[r], c1 = cpart[r + 1];
+      tmp.clear();
+      for (int k = A.ptr[i]; k < A.ptr[i + 1]; ++k) {
+        int c = A.col[k];
+        i64 cls = (diag_first && c == i) ? 0 : ((c >= c0 && c < c1) ? 1 : 2);
+        tmp.emplace_back((cls << 40) | (i64)c, A.val[k]);
+      }
+      std::sort(tmp.begin(), tmp.end(), [](const std::pair<i64, double> &a, const std::pair<i64, double> &b) { return a.first < b.first; });
+      for (size_t k = 0; k < tmp.size(); ++k) {
+        A.col[A.ptr[i] + k] = int(tmp[k].first & ((1LL << 40) - 1));
+        A.val[A.ptr[i] + k] = tmp[k].second;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// hypre_Rand: Park-Miller minimal standard via Schrage
+// ---------------------------------------------------------------------------------------------------------
+struct HypreRand {
+  int seed = 13579;
+  void set(int s) { seed = s; }
+  int randi() {
+    const int a = 16807, m = 2147483647, q = 127773, r = 2836;
+    int low = seed % q, high = seed / q;
+    int test = a * low - r * high;
+    seed = test > 0 ? test : test + m;
+    return seed;
+  }
+  double rand() { return (double)randi() / 2147483647.0; }
+};
+
+// ---------------------------------------------------------------------------------------------------------
+// basic kernels
+// ---------------------------------------------------------------------------------------------------------
+static void spmv(const Csr &A, const double *x, double *y) {  // y = A x
+#pragma omp parallel for schedule(static)
+  for (int i = 0; i < A.nr; ++i) {
+    double s = 0.0;
+    for (int k = A.ptr[i]; k < A.ptr[i + 1]; ++k) s += A.val[k] * x[A.col[k]];
+    y[i] = s;
+  }
+}
+static void residual(const Csr &A, const double *x, const double *b, double *r) {  // r = b - A x
+#pragma omp parallel for schedule(static)
+  for (int i = 0; i < A.nr; ++i) {
+    double s = 0.0;
+    for (int k = A.ptr[i]; k < A.ptr[i + 1]; ++k) s += A.val[k] * x[A.col[k]];
+    r[i] = b[i] - s;
+  }
+}
+static double dot(const double *a, const double *b, i64 n) {  // fixed blocking => thread-count independent
+  const i64 B = 4096;
+  i64 nb = (n + B - 1) / B;
+  std::vector<double> part(nb);
+#pragma omp parallel for schedule(static)
+  for (i64 ib = 0; ib < nb; ++ib) {
+    double s = 0.0;
+    i64 e = std::min(n, (ib + 1) * B);
+    for (i64 i = ib * B; i < e; ++i) s += a[i] * b[i];
+    part[ib] = s;
+  }
+  double s = 0.0;
+  for (i64 ib = 0; ib < nb; ++ib) s += part[ib];
+  return s;
+}
+static void axpy(double a, const double *x, double *y, i64 n) {
+#pragma omp parallel for schedule(static)
+  for (i64 i = 0; i < n; ++i) y[i] += a * x[i];
+}
+static void scal(double a, double *x, i64 n) {
+#pragma omp parallel for schedule(static)
+  for (i64 i = 0; i < n; ++i) x[i] *= a;
+}
+
+static Csr transpose(const Csr &A) {  // stable: within a row of A^T the entries are ordered by ascending row of A
+  Csr T;
+  T.nr = A.nc;
+  T.nc = A.nr;
+  T.ptr.assign(T.nr + 1, 0);
+  i64 nnz = A.nnz();
+  for (i64 k = 0; k < nnz; ++k) T.ptr[A.col[k] + 1]++;
+  for (int i = 0; i < T.nr; ++i) T.ptr[i + 1] += T.ptr[i];
+  T.col.resize(nnz);
+  T.val.resize(nnz);
+  std::vector<int> pos(T.ptr.begin(), T.ptr.end() - 1);
+  for (int i = 0; i < A.nr; ++i)
+    for (int k = A.ptr[i]; k < A.ptr[i + 1]; ++k) {
+      int p = pos[A.col[k]]++;
+      T.col[p] = i;
+      T.val[p] = A.val[k];
+    }
+  return T;
+}
+
+// Gustavson product C = A*B, accumulation in storage order.  Output rows are left in
+// ascending column order; the caller re-orders to ParCSR order.
+static Csr spgemm(const Csr &A, const Csr &B) {
+  Csr C;
+  C.nr = A.nr;
+  C.nc = B.nc;
+  C.ptr.assign(C.nr + 1, 0);
+  // symbolic
+#pragma omp parallel
+  {
+    std::vector<int> mark(B.nc, -1);
+#pragma omp for schedule(dynamic, 512)
+    for (int i = 0; i < A.nr; ++i) {
+      int cnt = 0;
+      for (int ka = A.ptr[i]; ka < A.ptr[i + 1]; ++ka) {
+        int k = A.col[ka];
+        for (int kb = B.ptr[k]; kb < B.ptr[k + 1]; ++kb) {
+          int j = B.col[kb];
+          if (mark[j] != i) { mark[j] = i; ++cnt; }
+        }
+      }
+      C.ptr[i + 1] = cnt;
+    }
+  }
+  for (int i = 0; i < C.nr; ++i) C.ptr[i + 1] += C.ptr[i];
+  C.col.resize(C.ptr[C.nr]);
+  C.val.resize(C.ptr[C.nr]);
+#pragma omp parallel
+  {
+    std::vector<int> mark(B.nc, -1);
+    std::vector<double> acc(B.nc, 0.0);
+#pragma omp for schedule(dynamic, 512)
+    for (int i = 0; i < A.nr; ++i) {
+      int beg = C.ptr[i], cnt = 0;
+      for (int ka = A.ptr[i]; ka < A.ptr[i + 1]; ++ka) {
+        int k = A.col[ka];
+        double a = A.val[ka];
+        for (int kb = B.ptr[k]; kb < B.ptr[k + 1]; ++kb) {
+          int j = B.col[kb];
+          if (mark[j] != i) { mark[j] = i; acc[j] = 0.0; C.col[beg + cnt++] = j; }
+          double prod = a * B.val[kb];
+          acc[j] = acc[j] + prod;
+        }
+      }
+      std::sort(C.col.begin() + beg, C.col.begin() + beg + cnt);
+      for (int k = 0; k < cnt; ++k) C.val[beg + k] = acc[C.col[beg + k]];
+    }
+  }
+  return C;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// options (names follow the YAML keys of /root/reference/src/HypreSystem.cpp:119-326,390-404; defaults = the
+// values bench/tests use)
+// ---------------------------------------------------------------------------------------------------------
+struct Options {
+  // gmres
+  double tol = 1e-8, atol = 0.0;
+  int max_iter = 1000, kdim = 50, precond = 1;  // precond: 1 = boomeramg, 0 = none
+  // amg
+  int coarsen_type = 8, interp_type = 6, relax_type = 18, relax_order = 0, max_levels = 20;
+  int num_sweeps = 1, p_max_elmts = 4, max_coarse_size = 9, min_coarse_size = 0, cheby_order = 2, cheby_eig_est = 10;
+  double strong_threshold = 0.25, max_row_sum = 0.9, trunc_factor = 0.0, cheby_fraction = 0.3, relax_weight = 1.0;
+};
+
+struct Level {
+  Csr A, S, P, R;
+  std::vector<int> part;       // row partition over virtual ranks (np+1)
+  std::vector<int> cf;         // +1 C, -1 F (SF points already folded to -1), size nr
+  std::vector<int> cf_raw;     // as produced by PMIS (-3 kept)
+  std::vector<double> l1;      // smoother diagonal (l1 norm or a_ii)
+  std::vector<double> ds;      // Chebyshev D^{-1/2}
+  std::vector<double> cheby_coef;
+  double cheby_max = 0, cheby_min = 0;
+  std::vector<double> u, f, vtemp, tmp, tmp2;
+};
+
+struct Sys {
+  Options opt;
+  int np = 1;
+  std::vector<Level> lev;
+  std::vector<double> b;
+  std::vector<double> ge;  // dense coarsest matrix, row-major
+  int ge_n = 0;
+  // results
+  int iters = 0;
+  double relres = 0.0, setup_s = 0.0, solve_s = 0.0;
+  std::vector<double> hist;
+  int converged = 0;
+};
+
+// ---------------------------------------------------------------------------------------------------------
+// Generator: laplace_3d_weak_scaling semantics (laplace_3d_weak_scaling.hpp:98-169,216-233,321,558,600;
+// HypreSystem.cpp:1516,1540-1556).  stencil = 27 (reference) or 7.  Rows are numbered rank-contiguously
+// (global row = rank*nx*ny*nz + local lexicographic index, x fastest); neighbours outside the global grid are
+// dropped; diag = (#stencil points - 1), off-diagonals = -1; rhs = row sum so that x == 1.
+// Off-rank columns use the TRUE neighbour's global row id (the reference glue's surrogate numbering at
+// HypreSystem.cpp:1555 is documented in DESIGN.md as not reproduced).
+// ---------------------------------------------------------------------------------------------------------
+static void gen_laplace(Sys &s, int nx, int ny, int nz, int px, int py, int pz, int stencil) {
+  int np = px * py * pz;
+  i64 nloc = (i64)nx * ny * nz;
+  i64 N = nloc * np;
+  int GX = nx * px, GY = ny * py, GZ = nz * pz;
+  s.np = np;
+  s.lev.clear();
+  s.lev.emplace_back();
+  Level &L = s.lev[0];
+  Csr &A = L.A;
+  A.nr = A.nc = (int)N;
+  A.ptr.assign(N + 1, 0);
+  L.part.resize(np + 1);
+  for (int r = 0; r <= np; ++r) L.part[r] = int(r * nloc);
+  auto gid = [&](int gx, int gy, int gz) -> int {
+    int rx = gx / nx, ry = gy / ny, rz = gz / nz;
+    int r = rx + px * (ry + py * rz);
+    int lx = gx - rx * nx, ly = gy - ry * ny, lz = gz - rz * nz;
+    return int(r * nloc + lx + (i64)nx * (ly + (i64)ny * lz));
+  };
+  auto count_row = [&](int gx, int gy, int gz) {
+    int c = 0;
+    for (int dz = -1; dz <= 1; ++dz)
+      for (int dy = -1; dy <= 1; ++dy)
+        for (int dx = -1; dx <= 1; ++dx) {
+          if (stencil == 7 && (std::abs(dx) + std::abs(dy) + std::abs(dz)) > 1) continue;
+          int x = gx + dx, y = gy + dy, z = gz + dz;
+          if (x < 0 || y < 0 || z < 0 || x >= GX || y >= GY || z >= GZ) continue;
+          ++c;
+        }
+    return c;
+  };
+#pragma omp parallel for schedule(static)
+  for (i64 row = 0; row < N; ++row) {
+    int r = int(row / nloc);
+    i64 l = row % nloc;
+    int lx = int(l % nx), ly = int((l / nx) % ny), lz = int(l / ((i64)nx * ny));
+    int gx = (r % px) * nx + lx, gy = ((r / px) % py) * ny + ly, gz = (r / (px * py)) * nz + lz;
+    A.ptr[row + 1] = count_row(gx, gy, gz);
+  }
+  for (i64 i = 0; i < N; ++i) A.ptr[i + 1] += A.ptr[i];
+  A.col.resize(A.ptr[N]);
+  A.val.resize(A.ptr[N]);
+  s.b.assign(N, 0.0);
+  double dval = (stencil == 7) ? 6.0 : 26.0;
+#pragma omp parallel for schedule(static)
+  for (i64 row = 0; row < N; ++row) {
+    int r = int(row / nloc);
+    i64 l = row % nloc;
+    int lx = int(l % nx), ly = int((l / nx) % ny), lz = int(l / ((i64)nx * ny));
+    int gx = (r % px) * nx + lx, gy = ((r / px) % py) * ny + ly, gz = (r / (px * py)) * nz + lz;
+    int p = A.ptr[row];
+    int cnt = 0;
+    for (int dz = -1; dz <= 1; ++dz)
+      for (int dy = -1; dy <= 1; ++dy)
+        for (int dx = -1; dx <= 1; ++dx) {
+          if (stencil == 7 && (std::abs(dx) + std::abs(dy) + std::abs(dz)) > 1) continue;
+          int x = gx + dx, y = gy + dy, z = gz + dz;
+          if (x < 0 || y < 0 || z < 0 || x >= GX || y >= GY || z >= GZ) continue;
+          int c = gid(x, y, z);
+          A.col[p] = c;
+          A.val[p] = (c == row) ? dval : -1.0;
+          ++p;
+          ++cnt;
+        }
+    s.b[row] = dval - (cnt - 1);  // laplace_3d_weak_scaling.hpp:321
+  }
+  parcsr_order(A, L.part, L.part, true);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// A.3 strength of connection (hypre_BoomerAMGCreateS)
+// ---------------------------------------------------------------------------------------------------------
+static void strength(const Csr &A, double theta, double max_row_sum, Csr &S) {
+  S.nr = A.nr;
+  S.nc = A.nc;
+  S.ptr.assign(A.nr + 1, 0);
+  std::vector<char> flag(A.nnz(), 0);
+#pragma omp parallel for schedule(static)
+  for (int i = 0; i < A.nr; ++i) {
+    int b = A.ptr[i], e = A.ptr[i + 1];
+    if (e == b) continue;
+    double diag = A.val[b];  // diagonal first (ParCSR order)
+    double row_scale = 0.0, row_sum = diag;
+    for (int k = b + 1; k < e; ++k) {
+      double a = A.val[k];
+      if (diag < 0) row_scale = std::max(row_scale, a);
+      else row_scale = std::min(row_scale, a);
+      row_sum += a;
+    }
+    int cnt = 0;
+    if ((std::fabs(row_sum) > std::fabs(diag) * max_row_sum) && (max_row_sum < 1.0)) {
+      // all dependencies weak
+    } else {
+      double thr = theta * row_scale;
+      for (int k = b + 1; k < e; ++k) {
+        double a = A.val[k];
+        bool strong = (diag < 0) ? (a > thr) : (a < thr);
+        if (strong) { flag[k] = 1; ++cnt; }
+      }
+    }
+    S.ptr[i + 1] = cnt;
+  }
+  for (int i = 0; i < S.nr; ++i) S.ptr[i + 1] += S.ptr[i];
+  S.col.resize(S.ptr[S.nr]);
+#pragma omp parallel for schedule(static)
+  for (int i = 0; i < A.nr; ++i) {
+    int p = S.ptr[i];
+    for (int k = A.ptr[i]; k < A.ptr[i + 1]; ++k)
+      if (flag[k]) S.col[p++] = A.col[k];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// A.4 PMIS (hypre_BoomerAMGCoarsenPMIS + hypre_BoomerAMGIndepSet), sequential sweeps on the global graph.
+// ---------------------------------------------------------------------------------------------------------
+static void pmis(const Csr &S, const std::vector<int> &part, std::vector<int> &cf, std::vector<double> *measure_out) {
+  int n = S.nr;
+  std::vector<double> measure(n, 0.0);
+  for (i64 k = 0; k < S.nnz(); ++k) measure[S.col[k]] += 1.0;  // |S^T_i|
+  int np = (int)part.size() - 1;
+  for (int r = 0; r < np; ++r) {  // A.2: each rank reseeds 2747 + rank and draws for its local rows in order
+    HypreRand rng;
+    rng.set(2747 + r);
+    for (int i = part[r]; i < part[r + 1]; ++i) measure[i] += rng.rand();
+  }
+  if (measure_out) *measure_out = measure;
+  cf.assign(n, 0);
+  std::vector<int> graph;
+  graph.reserve(n);
+  for (int i = 0; i < n; ++i) {
+    if (S.ptr[i + 1] == S.ptr[i]) { cf[i] = -3; measure[i] = 0.0; }  // SF_PT: no strong dependencies
+    else graph.push_back(i);
+  }
+  std::vector<char> is(n, 0);
+  while (true) {
+    // points nobody depends on become F at once
+    {
+      size_t w = 0;
+      for (size_t g = 0; g < graph.size(); ++g) {
+        int i = graph[g];
+        if (measure[i] < 1.0) { cf[i] = -1; measure[i] = 0.0; }
+        else graph[w++] = i;
+      }
+      graph.resize(w);
+    }
+    if (graph.empty()) break;
+    // independent set
+    for (int i : graph) is[i] = (measure[i] > 1.0) ? 1 : 0;
+    for (int i : graph) {
+      if (!(measure[i] > 1.0)) continue;
+      for (int k = S.ptr[i]; k < S.ptr[i + 1]; ++k) {
+        int j = S.col[k];
+        if (measure[j] > 1.0) {
+          if (measure[i] > measure[j]) is[j] = 0;
+          else if (measure[j] > measure[i]) is[i] = 0;
+        }
+      }
+    }
+    for (int i : graph)
+      if (is[i]) cf[i] = 1;
+    // undecided points that strongly depend on a C point become F
+    for (int i : graph) {
+      if (cf[i] != 0) continue;
+      for (int k = S.ptr[i]; k < S.ptr[i + 1]; ++k)
+        if (cf[S.col[k]] > 0) { cf[i] = -1; break; }
+    }
+    size_t w = 0;
+    for (size_t g = 0; g < graph.size(); ++g) {
+      int i = graph[g];
+      if (cf[i] != 0) { measure[i] = 0.0; is[i] = 0; }
+      else graph[w++] = i;
+    }
+    graph.resize(w);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// hypre_qsort2abs: descending by |w|, exact swap sequence
+// ---------------------------------------------------------------------------------------------------------
+static void swap2(int *v, double *w, int i, int j) {
+  int t = v[i]; v[i] = v[j]; v[j] = t;
+  double d = w[i]; w[i] = w[j]; w[j] = d;
+}
+static void qsort2abs(int *v, double *w, int left, int right) {
+  if (left >= right) return;
+  swap2(v, w, left, (left + right) / 2);
+  int last = left;
+  for (int i = left + 1; i <= right; ++i)
+    if (std::fabs(w[i]) > std::fabs(w[left])) swap2(v, w, ++last, i);
+  swap2(v, w, left, last);
+  qsort2abs(v, w, left, last - 1);
+  qsort2abs(v, w, last + 1, right);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// A.5 extended+i interpolation (hypre_BoomerAMGBuildExtPIInterp) followed by hypre_BoomerAMGInterpTruncation.
+// cf: +1 C, -1 F, -3 isolated.  cpart = partition of the coarse numbering.  P rows: own-range coarse columns
+// first (discovery order) then off-range coarse columns (discovery order); truncated rows are in qsort2abs order.
+// ---------------------------------------------------------------------------------------------------------
+static void interp_extpi(const Csr &A, const Csr &S, const std::vector<int> &cf, const std::vector<int> &f2c,
+                         const std::vector<int> &rpart, const std::vector<int> &cpart, int ncoarse, double trunc_factor,
+                         int p_max, Csr &P) {
+  int n = A.nr;
+  P.nr = n;
+  P.nc = ncoarse;
+  std::vector<std::vector<int>> rc(n);
+  std::vector<std::vector<double>> rv(n);
+#pragma omp parallel
+  {
+    std::vector<int> marker(n, -1);      // position in the row's list, or -2 - i for "strong F neighbour of i"
+    std::vector<int> lc_d, lc_o;         // fine ids of C points in discovery order (own range / off range)
+    std::vector<int> lc;
+    std::vector<double> lv;
+#pragma omp for schedule(dynamic, 256)
+    for (int i = 0; i < n; ++i) {
+      if (cf[i] >= 0) {
+        rc[i].assign(1, f2c[i]);
+        rv[i].assign(1, 1.0);
+        continue;
+      }
+      if (cf[i] == -3) continue;
+      int r = owner_of(rpart, i);
+      int c0 = cpart[r], c1 = cpart[r + 1];
+      lc_d.clear();
+      lc_o.clear();
+      const int strong_f = -2 - i;
+      // marker[k] >= 0 : position of C point k in this row's list; == strong_f : strong F neighbour; -1 : none
+      auto push = [&](int k1) {
+        if (marker[k1] >= 0) return;  // already in the list of this row
+        int cid = f2c[k1];
+        if (cid >= c0 && cid < c1) { marker[k1] = (int)lc_d.size(); lc_d.push_back(k1); }
+        else { marker[k1] = (1 << 28) + (int)lc_o.size(); lc_o.push_back(k1); }
+      };
+      std::vector<int> fmarked;
+      for (int kk = S.ptr[i]; kk < S.ptr[i + 1]; ++kk) {
+        int i1 = S.col[kk];
+        if (cf[i1] >= 0) push(i1);
+        else if (cf[i1] != -3) {
+          marker[i1] = strong_f;
+          fmarked.push_back(i1);
+          for (int k2 = S.ptr[i1]; k2 < S.ptr[i1 + 1]; ++k2) {
+            int k1 = S.col[k2];
+            if (cf[k1] >= 0) push(k1);
+          }
+        }
+      }
+      int nd = (int)lc_d.size(), no = (int)lc_o.size();
+      lc.resize(nd + no);
+      lv.assign(nd + no, 0.0);
+      for (int k = 0; k < nd; ++k) lc[k] = lc_d[k];
+      for (int k = 0; k < no; ++k) { lc[nd + k] = lc_o[k]; marker[lc_o[k]] = nd + k; }
+      // weights
+      double diagonal = A.val[A.ptr[i]];
+      for (int jj = A.ptr[i] + 1; jj < A.ptr[i + 1]; ++jj) {
+        int i1 = A.col[jj];
+        double aij = A.val[jj];
+        if (marker[i1] >= 0) {
+          lv[marker[i1]] += aij;
+        } else if (marker[i1] == strong_f) {
+          double sum = 0.0;
+          double sgn = (A.val[A.ptr[i1]] < 0) ? -1.0 : 1.0;
+          for (int j1 = A.ptr[i1] + 1; j1 < A.ptr[i1 + 1]; ++j1) {
+            int i2 = A.col[j1];
+            double a = A.val[j1];
+            if ((marker[i2] >= 0 || i2 == i) && (sgn * a) < 0) sum += a;
+          }
+          if (sum != 0.0) {
+            double distribute = aij / sum;
+            for (int j1 = A.ptr[i1] + 1; j1 < A.ptr[i1 + 1]; ++j1) {
+              int i2 = A.col[j1];
+              double a = A.val[j1];
+              if ((sgn * a) < 0) {
+                if (marker[i2] >= 0) { double t = distribute * a; lv[marker[i2]] += t; }
+                if (i2 == i) { double t = distribute * a; diagonal += t; }
+              }
+            }
+          } else {
+            diagonal += aij;
+          }
+        } else if (cf[i1] != -3) {
+          diagonal += aij;
+        }
+      }
+      if (diagonal != 0.0) {
+        double md = -diagonal;
+        for (size_t k = 0; k < lv.size(); ++k) lv[k] = lv[k] / md;
+      }
+      // clear markers
+      for (int k : lc) marker[k] = -1;
+      for (int k : fmarked) marker[k] = -1;
+      // coarse ids
+      for (size_t k = 0; k < lc.size(); ++k) lc[k] = f2c[lc[k]];
+      // truncation (hypre_BoomerAMGInterpTruncation)
+      int len = (int)lc.size();
+      if (trunc_factor > 0.0 && len > 0) {
+        double max_coef = 0.0, row_sum = 0.0, scale = 0.0;
+        for (int k = 0; k < len; ++k) max_coef = std::max(max_coef, std::fabs(lv[k]));
+        max_coef *= trunc_factor;
+        int w = 0;
+        for (int k = 0; k < len; ++k) {
+          row_sum += lv[k];
+          if (std::fabs(lv[k]) >= max_coef) { scale += lv[k]; lc[w] = lc[k]; lv[w] = lv[k]; ++w; }
+        }
+        len = w;
+        if (scale != 0.0 && scale != row_sum) {
+          double f = row_sum / scale;
+          for (int k = 0; k < len; ++k) lv[k] *= f;
+        }
+      }
+      if (p_max > 0 && len > p_max) {
+        double row_sum = 0.0, scale = 0.0;
+        for (int k = 0; k < len; ++k) row_sum += lv[k];
+        qsort2abs(lc.data(), lv.data(), 0, len - 1);
+        for (int k = 0; k < p_max; ++k) scale += lv[k];
+        len = p_max;
+        if (scale != 0.0 && scale != row_sum) {
+          double f = row_sum / scale;
+          for (int k = 0; k < len; ++k) lv[k] *= f;
+        }
+        // re-split: own-range entries first, each part keeping the sorted order
+        std::vector<int> tc;
+        std::vector<double> tv;
+        for (int k = 0; k < len; ++k)
+          if (lc[k] >= c0 && lc[k] < c1) { tc.push_back(lc[k]); tv.push_back(lv[k]); }
+        for (int k = 0; k < len; ++k)
+          if (!(lc[k] >= c0 && lc[k] < c1)) { tc.push_back(lc[k]); tv.push_back(lv[k]); }
+        for (int k = 0; k < len; ++k) { lc[k] = tc[k]; lv[k] = tv[k]; }
+      }
+      rc[i].assign(lc.begin(), lc.begin() + len);
+      rv[i].assign(lv.begin(), lv.begin() + len);
+    }
+  }
+  P.ptr.assign(n + 1, 0);
+  for (int i = 0; i < n; ++i) P.ptr[i + 1] = P.ptr[i] + (int)rc[i].size();
+  P.col.resize(P.ptr[n]);
+  P.val.resize(P.ptr[n]);
+#pragma omp parallel for schedule(static)
+  for (int i = 0; i < n; ++i) {
+    std::copy(rc[i].begin(), rc[i].end(), P.col.begin() + P.ptr[i]);
+    std::copy(rv[i].begin(), rv[i].end(), P.val.begin() + P.ptr[i]);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// smoother data
+// ---------------------------------------------------------------------------------------------------------
+static void l1_norms(const Csr &A, int relax_type, std::vector<double> &l1) {
+  l1.assign(A.nr, 0.0);
+#pragma omp parallel for schedule(static)
+  for (int i = 0; i < A.nr; ++i) {
+    int b = A.ptr[i], e = A.ptr[i + 1];
+    if (b == e) { l1[i] = 1.0; continue; }
+    double d = A.val[b];
+    if (relax_type == 7) { l1[i] = d; continue; }
+    double s = 0.0;
+    for (int k = b; k < e; ++k) s += std::fabs(A.val[k]);
+    l1[i] = (d < 0) ? -s : s;
+  }
+}
+
+// A.8 Chebyshev setup: lambda_max/min of D^{-1/2} A D^{-1/2} by `eig_est` CG steps (Lanczos tridiagonal),
+// start vector 2*hypre_Rand()-1 with seed rank+1 per virtual rank.
+static void tridiag_eigs(const std::vector<double> &d, const std::vector<double> &e, double &lmin, double &lmax) {
+  // eigenvalues of the symmetric tridiagonal (diag d[0..m), off-diag e[1..m)) by cyclic Jacobi on the dense form
+  int m = (int)d.size();
+  std::vector<double> T((size_t)m * m, 0.0);
+  for (int i = 0; i < m; ++i) {
+    T[(size_t)i * m + i] = d[i];
+    if (i > 0) T[(size_t)i * m + i - 1] = T[(size_t)(i - 1) * m + i] = e[i];
+  }
+  for (int sweep = 0; sweep < 100; ++sweep) {
+    double off = 0.0;
+    for (int p = 0; p < m; ++p)
+      for (int q = p + 1; q < m; ++q) off += T[(size_t)p * m + q] * T[(size_t)p * m + q];
+    if (off < 1e-300) break;
+    for (int p = 0; p < m; ++p)
+      for (int q = p + 1; q < m; ++q) {
+        double apq = T[(size_t)p * m + q];
+        if (apq == 0.0) continue;
+        double app = T[(size_t)p * m + p], aqq = T[(size_t)q * m + q];
+        double tau = (aqq - app) / (2.0 * apq);
+        double t = (tau >= 0 ? 1.0 : -1.0) / (std::fabs(tau) + std::sqrt(1.0 + tau * tau));
+        double c = 1.0 / std::sqrt(1.0 + t * t), sn = t * c;
+        for (int k = 0; k < m; ++k) {
+          double akp = T[(size_t)k * m + p], akq = T[(size_t)k * m + q];
+          T[(size_t)k * m + p] = c * akp - sn * akq;
+          T[(size_t)k * m + q] = sn * akp + c * akq;
+        }
+        for (int k = 0; k < m; ++k) {
+          double apk = T[(size_t)p * m + k], aqk = T[(size_t)q * m + k];
+          T[(size_t)p * m + k] = c * apk - sn * aqk;
+          T[(size_t)q * m + k] = sn * apk + c * aqk;
+        }
+      }
+  }
+  lmin = lmax = T[0];
+  for (int i = 1; i < m; ++i) { lmin = std::min(lmin, T[(size_t)i * m + i]); lmax = std::max(lmax, T[(size_t)i * m + i]); }
+}
+
+static void cheby_setup(Level &L, const Options &o) {
+  const Csr &A = L.A;
+  int n = A.nr;
+  L.ds.resize(n);
+  for (int i = 0; i < n; ++i) L.ds[i] = 1.0 / std::sqrt(A.val[A.ptr[i]]);
+  double lmax = 0, lmin = 0;
+  if (o.cheby_eig_est > 0 && n > 0) {
+    // CG on the scaled operator, zero rhs: standard hypre_ParCSRMaxEigEstimateCG structure
+    std::vector<double> r(n), p(n), s(n), u(n, 0.0), t(n);
+    int np = (int)L.part.size() - 1;
+    for (int rk = 0; rk < np; ++rk) {
+      HypreRand rng;
+      rng.set(rk + 1);
+      for (int i = L.part[rk]; i < L.part[rk + 1]; ++i) r[i] = 2.0 * rng.rand() - 1.0;
+    }
+    int m = std::min(o.cheby_eig_est, n);
+    std::vector<double> td(m, 0.0), te(m, 0.0);
+    double gamma_old = 0, alpha_old = 0, beta = 0, alpha = 0, gamma = dot(r.data(), r.data(), n);
+    p = r;
+    gamma_old = gamma;
+    int it = 0;
+    while (it < m) {
+      // s = D^{-1/2} A D^{-1/2} p
+      for (int i = 0; i < n; ++i) t[i] = L.ds[i] * p[i];
+      spmv(A, t.data(), s.data());
+      for (int i = 0; i < n; ++i) s[i] = L.ds[i] * s[i];
+      double sdotp = dot(s.data(), p.data(), n);
+      if (sdotp == 0.0) { m = it; break; }
+      alpha = gamma / sdotp;
+      axpy(-alpha, s.data(), r.data(), n);
+      gamma_old = gamma;
+      gamma = dot(r.data(), r.data(), n);
+      double beta_new = gamma / gamma_old;
+      // Lanczos coefficients from CG
+      if (it == 0) td[it] = 1.0 / alpha;
+      else { td[it] = 1.0 / alpha + beta / alpha_old; te[it] = std::sqrt(beta) / alpha_old; }
+      alpha_old = alpha;
+      beta = beta_new;
+      ++it;
+      if (gamma == 0.0) { m = it; break; }
+      for (int i = 0; i < n; ++i) p[i] = r[i] + beta * p[i];
+    }
+    if (m > 0) {
+      td.resize(m);
+      te.resize(m);
+      tridiag_eigs(td, te, lmin, lmax);
+    }
+  }
+  L.cheby_max = lmax;
+  L.cheby_min = lmin;
+  double upper = 1.1 * lmax;
+  double lower = (upper - lmin) * o.cheby_fraction + lmin;
+  double theta = (upper + lower) / 2, delta = (upper - lower) / 2;
+  L.cheby_coef.clear();
+  int ord = std::max(1, std::min(4, o.cheby_order));
+  if (ord == 1) L.cheby_coef = {1.0 / theta};
+  else if (ord == 2) {
+    double den = delta * delta - 2 * theta * theta;
+    L.cheby_coef = {-4 * theta / den, 2 / den};
+  } else if (ord == 3) {
+    double den = 3 * (delta * delta) * theta - 4 * (theta * theta * theta);
+    L.cheby_coef = {(3 * delta * delta - 12 * theta * theta) / den, 12 * theta / den, -4 / den};
+  } else {
+    double den = -(delta * delta * delta * delta) + 8 * delta * delta * theta * theta - 8 * theta * theta * theta * theta;
+    L.cheby_coef = {(32 * theta * theta * theta - 16 * delta * delta * theta) / den, (8 * delta * delta - 48 * theta * theta) / den,
+                    32 * theta / den, -8 / den};
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// AMG setup (hypre_BoomerAMGSetup level loop, SURVEY.md §3.3 / A.4 setup-loop rules)
+// ---------------------------------------------------------------------------------------------------------
+static void amg_setup(Sys &s) {
+  double t0 = now_s();
+  const Options &o = s.opt;
+  s.lev.resize(1);
+  int level = 0;
+  while (true) {
+    Level &L = s.lev[level];
+    int fine = L.A.nr;
+    bool last = (level >= o.max_levels - 1) || (fine <= o.max_coarse_size);
+    if (!last) {
+      strength(L.A, o.strong_threshold, o.max_row_sum, L.S);
+      pmis(L.S, L.part, L.cf_raw, nullptr);
+      int np = (int)L.part.size() - 1;
+      std::vector<int> f2c(fine, -1), cpart(np + 1, 0);
+      int nc = 0;
+      for (int r = 0; r < np; ++r) {
+        for (int i = L.part[r]; i < L.part[r + 1]; ++i)
+          if (L.cf_raw[i] > 0) f2c[i] = nc++;
+        cpart[r + 1] = nc;
+      }
+      if (nc == 0 || nc == fine || nc < o.min_coarse_size) last = true;
+      else {
+        interp_extpi(L.A, L.S, L.cf_raw, f2c, L.part, cpart, nc, o.trunc_factor, o.p_max_elmts, L.P);
+        L.cf = L.cf_raw;
+        for (int &c : L.cf) if (c == -3) c = -1;
+        L.R = transpose(L.P);
+        parcsr_order(L.R, cpart, L.part, false);  // own-range fine rows first (ascending), then the rest
+        Csr Q = spgemm(L.A, L.P);
+        parcsr_order(Q, L.part, cpart, false);
+        Csr Ac = spgemm(L.R, Q);
+        parcsr_order(Ac, cpart, cpart, true);
+        s.lev.emplace_back();
+        s.lev[level + 1].A = std::move(Ac);
+        s.lev[level + 1].part = cpart;
+      }
+    }
+    if (last) break;
+    ++level;
+  }
+  // smoother data + work vectors
+  int nl = (int)s.lev.size();
+  for (int l = 0; l < nl; ++l) {
+    Level &L = s.lev[l];
+    int n = L.A.nr;
+    if (o.relax_type == 16) cheby_setup(L, o);
+    else l1_norms(L.A, o.relax_type, L.l1);
+    if (l > 0) { L.u.assign(n, 0.0); L.f.assign(n, 0.0); }
+    L.vtemp.assign(n, 0.0);
+    L.tmp.assign(n, 0.0);
+    L.tmp2.assign(n, 0.0);
+    if (L.cf.empty()) L.cf.assign(n, 1);
+  }
+  // coarsest: dense matrix for Gaussian elimination (A.9)
+  Level &C = s.lev[nl - 1];
+  s.ge_n = C.A.nr;
+  if (nl > 1 || true) {
+    int n = s.ge_n;
+    if ((i64)n * n <= (i64)64 * 1024 * 1024) {
+      s.ge.assign((size_t)n * n, 0.0);
+      for (int i = 0; i < n; ++i)
+        for (int k = C.A.ptr[i]; k < C.A.ptr[i + 1]; ++k) s.ge[(size_t)i * n + C.A.col[k]] = C.A.val[k];
+    } else s.ge.clear();
+  }
+  s.setup_s = now_s() - t0;
+}
+
+// A.9 unpivoted Gaussian elimination on a copy
+static void ge_solve(const std::vector<double> &Ain, int n, double *x) {
+  std::vector<double> A(Ain);
+  if (n == 1) { if (A[0] != 0.0) x[0] /= A[0]; return; }
+  for (int k = 0; k < n - 1; ++k) {
+    if (A[(size_t)k * n + k] != 0.0) {
+      for (int j = k + 1; j < n; ++j) {
+        if (A[(size_t)j * n + k] != 0.0) {
+          double f = A[(size_t)j * n + k] / A[(size_t)k * n + k];
+          for (int m = k + 1; m < n; ++m) A[(size_t)j * n + m] -= f * A[(size_t)k * n + m];
+          x[j] -= f * x[k];
+        }
+      }
+    }
+  }
+  for (int k = n - 1; k > 0; --k) {
+    if (A[(size_t)k * n + k] != 0.0) {
+      x[k] /= A[(size_t)k * n + k];
+      for (int j = 0; j < k; ++j)
+        if (A[(size_t)j * n + k] != 0.0) x[j] -= x[k] * A[(size_t)j * n + k];
+    }
+  }
+  if (A[0] != 0.0) x[0] /= A[0];
+}
+
+// one relaxation sweep on level L (A.7 / A.8).  points: 0 = all, +1 / -1 = only rows with that CF marker.
+static void relax(Level &L, const Options &o, double *u, const double *f, int points, bool zero_guess) {
+  const Csr &A = L.A;
+  int n = A.nr;
+  if (o.relax_type == 16) {
+    // Chebyshev (scaled): r = D^{-1/2}(f - A u); v = c_{o-1} r; v = c_i r + D^{-1/2} A D^{-1/2} v; u += D^{-1/2} v
+    double *r = L.tmp.data(), *v = L.tmp2.data(), *t = L.vtemp.data();
+    int ord = (int)L.cheby_coef.size();
+    if (zero_guess) {
+#pragma omp parallel for schedule(static)
+      for (int i = 0; i < n; ++i) r[i] = L.ds[i] * f[i];
+    } else {
+      residual(A, u, f, r);
+#pragma omp parallel for schedule(static)
+      for (int i = 0; i < n; ++i) r[i] = L.ds[i] * r[i];
+    }
+    double c = L.cheby_coef[ord - 1];
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < n; ++i) v[i] = c * r[i];
+    for (int k = ord - 2; k >= 0; --k) {
+#pragma omp parallel for schedule(static)
+      for (int i = 0; i < n; ++i) t[i] = L.ds[i] * v[i];
+      double ck = L.cheby_coef[k];
+#pragma omp parallel for schedule(static)
+      for (int i = 0; i < n; ++i) {
+        double sacc = 0.0;
+        for (int q = A.ptr[i]; q < A.ptr[i + 1]; ++q) sacc += A.val[q] * t[A.col[q]];
+        v[i] = ck * r[i] + L.ds[i] * sacc;
+      }
+    }
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < n; ++i) u[i] = (zero_guess ? 0.0 : u[i]) + L.ds[i] * v[i];
+    return;
+  }
+  // Jacobi-type (relax 7 / 18): u <- u + w (f - A u) ./ d, out of place
+  double w = o.relax_weight;
+  double *un = L.tmp.data();
+  if (zero_guess) {
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < n; ++i) un[i] = (points == 0 || L.cf[i] == points) ? w * f[i] / L.l1[i] : 0.0;
+  } else {
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < n; ++i) {
+      if (points != 0 && L.cf[i] != points) { un[i] = u[i]; continue; }
+      double sacc = 0.0;
+      for (int q = A.ptr[i]; q < A.ptr[i + 1]; ++q) sacc += A.val[q] * u[A.col[q]];
+      un[i] = u[i] + w * (f[i] - sacc) / L.l1[i];
+    }
+  }
+  std::memcpy(u, un, sizeof(double) * n);
+}
+
+static void relax_sweeps(Level &L, const Options &o, double *u, const double *f, bool down, bool zero_guess) {
+  for (int sw = 0; sw < o.num_sweeps; ++sw) {
+    bool zg = zero_guess && sw == 0;
+    if (o.relax_order == 1 && o.relax_type != 16) {
+      int first = down ? 1 : -1;
+      relax(L, o, u, f, first, zg);
+      relax(L, o, u, f, -first, false);
+    } else relax(L, o, u, f, 0, zg);
+  }
+}
+
+// A.7 one V(1,1) cycle from a zero initial guess: z = M^{-1} r
+static void vcycle(Sys &s, const double *rhs, double *z) {
+  int nl = (int)s.lev.size();
+  const Options &o = s.opt;
+  for (int l = 0; l < nl; ++l) {
+    Level &L = s.lev[l];
+    double *u = (l == 0) ? z : L.u.data();
+    const double *f = (l == 0) ? rhs : L.f.data();
+    int n = L.A.nr;
+    if (l == nl - 1) {
+      if (nl == 1 && o.max_levels == 1) {  // smoother-only preconditioner
+        relax_sweeps(L, o, u, f, true, true);
+      } else if (!s.ge.empty()) {
+        std::memcpy(u, f, sizeof(double) * n);
+        ge_solve(s.ge, n, u);
+      } else {
+        relax_sweeps(L, o, u, f, true, true);
+      }
+      break;
+    }
+    relax_sweeps(L, o, u, f, true, true);
+    residual(L.A, u, f, L.vtemp.data());
+    Level &C = s.lev[l + 1];
+    spmv(L.R, L.vtemp.data(), C.f.data());
+  }
+  for (int l = nl - 2; l >= 0; --l) {
+    Level &L = s.lev[l];
+    Level &C = s.lev[l + 1];
+    double *u = (l == 0) ? z : L.u.data();
+    const double *f = (l == 0) ? rhs : L.f.data();
+    const Csr &P = L.P;
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < P.nr; ++i) {
+      double sacc = 0.0;
+      for (int q = P.ptr[i]; q < P.ptr[i + 1]; ++q) sacc += P.val[q] * C.u[P.col[q]];
+      u[i] += sacc;
+    }
+    relax_sweeps(L, o, u, f, false, false);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// A.1 hypre_GMRESSolve: right-preconditioned restarted GMRES, modified Gram-Schmidt, Givens rotations
+// ---------------------------------------------------------------------------------------------------------
+static void gmres(Sys &s, double *x) {
+  double t0 = now_s();
+  const Options &o = s.opt;
+  const Csr &A = s.lev[0].A;
+  i64 n = A.nr;
+  int k_dim = o.kdim, max_iter = o.max_iter;
+  const double *b = s.b.data();
+  std::vector<std::vector<double>> p(k_dim + 1, std::vector<double>(n));
+  std::vector<double> r(n), w(n);
+  std::vector<double> rs(k_dim + 1), c(k_dim), sn(k_dim);
+  std::vector<std::vector<double>> hh(k_dim + 1, std::vector<double>(k_dim, 0.0));
+  auto precond = [&](const double *in, double *out) {
+    if (o.precond) vcycle(s, in, out);
+    else std::memcpy(out, in, sizeof(double) * n);
+  };
+  s.hist.clear();
+  double b_norm = std::sqrt(dot(b, b, n));
+  residual(A, x, b, p[0].data());
+  double r_norm = std::sqrt(dot(p[0].data(), p[0].data(), n));
+  double den_norm = (b_norm > 0.0) ? b_norm : r_norm;
+  double epsilon = std::max(o.atol, o.tol * den_norm);
+  int iter = 0;
+  double real_r_norm_old = r_norm, real_r_norm_new;
+  s.hist.push_back(r_norm);
+  s.converged = 0;
+  while (iter < max_iter) {
+    rs[0] = r_norm;
+    if (r_norm == 0.0) { s.converged = 1; break; }
+    if (r_norm <= epsilon) {
+      residual(A, x, b, r.data());
+      r_norm = std::sqrt(dot(r.data(), r.data(), n));
+      if (r_norm <= epsilon) { s.converged = 1; break; }
+    }
+    scal(1.0 / r_norm, p[0].data(), n);
+    int i = 0;
+    while (i < k_dim && iter < max_iter) {
+      ++i;
+      ++iter;
+      std::fill(r.begin(), r.end(), 0.0);
+      precond(p[i - 1].data(), r.data());
+      spmv(A, r.data(), p[i].data());
+      for (int j = 0; j < i; ++j) {
+        hh[j][i - 1] = dot(p[j].data(), p[i].data(), n);
+        axpy(-hh[j][i - 1], p[j].data(), p[i].data(), n);
+      }
+      double t = std::sqrt(dot(p[i].data(), p[i].data(), n));
+      hh[i][i - 1] = t;
+      if (t != 0.0) scal(1.0 / t, p[i].data(), n);
+      for (int j = 1; j < i; ++j) {
+        double tt = hh[j - 1][i - 1];
+        hh[j - 1][i - 1] = sn[j - 1] * hh[j][i - 1] + c[j - 1] * tt;
+        hh[j][i - 1] = -sn[j - 1] * tt + c[j - 1] * hh[j][i - 1];
+      }
+      double gamma = std::sqrt(hh[i][i - 1] * hh[i][i - 1] + hh[i - 1][i - 1] * hh[i - 1][i - 1]);
+      if (gamma == 0.0) gamma = 1e-16;
+      c[i - 1] = hh[i - 1][i - 1] / gamma;
+      sn[i - 1] = hh[i][i - 1] / gamma;
+      rs[i] = -hh[i][i - 1] * rs[i - 1];
+      rs[i] /= gamma;
+      rs[i - 1] = c[i - 1] * rs[i - 1];
+      hh[i - 1][i - 1] = sn[i - 1] * hh[i][i - 1] + c[i - 1] * hh[i - 1][i - 1];
+      r_norm = std::fabs(rs[i]);
+      s.hist.push_back(r_norm);
+      if (r_norm <= epsilon) break;
+    }
+    // back substitution
+    rs[i - 1] = rs[i - 1] / hh[i - 1][i - 1];
+    for (int k = i - 2; k >= 0; --k) {
+      double t = 0.0;
+      for (int j = k + 1; j < i; ++j) t -= hh[k][j] * rs[j];
+      t += rs[k];
+      rs[k] = t / hh[k][k];
+    }
+    std::memcpy(w.data(), p[i - 1].data(), sizeof(double) * n);
+    scal(rs[i - 1], w.data(), n);
+    for (int j = i - 2; j >= 0; --j) axpy(rs[j], p[j].data(), w.data(), n);
+    std::fill(r.begin(), r.end(), 0.0);
+    precond(w.data(), r.data());
+    axpy(1.0, r.data(), x, n);
+    if (r_norm <= epsilon) {
+      residual(A, x, b, r.data());
+      real_r_norm_new = r_norm = std::sqrt(dot(r.data(), r.data(), n));
+      if (r_norm <= epsilon) { s.converged = 1; break; }
+      p[0] = r;
+      i = 0;
+      if (real_r_norm_new >= real_r_norm_old) { break; }
+      real_r_norm_old = real_r_norm_new;
+      continue;
+    }
+    // restart: residual from the Arnoldi data
+    for (int j = i; j > 0; --j) {
+      rs[j - 1] = -sn[j - 1] * rs[j];
+      rs[j] = c[j - 1] * rs[j];
+    }
+    if (i) axpy(rs[i] - 1.0, p[i].data(), p[i].data(), n);
+    for (int j = i - 1; j > 0; --j) axpy(rs[j], p[j].data(), p[i].data(), n);
+    if (i) {
+      axpy(rs[0] - 1.0, p[0].data(), p[0].data(), n);
+      axpy(1.0, p[i].data(), p[0].data(), n);
+    }
+  }
+  s.iters = iter;
+  s.relres = (b_norm > 0.0) ? r_norm / b_norm : r_norm;
+  s.solve_s = now_s() - t0;
+}
+
+}  // namespace
+
+// =========================================================================================================
+// C API (ctypes)
+// =========================================================================================================
+extern "C" {
+
+void *ora_create() { return new Sys(); }
+void ora_destroy(void *h) { delete (Sys *)h; }
+
+int ora_set_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+  return omp_get_max_threads();
+#else
+  (void)n;
+  return 1;
+#endif
+}
+
+int ora_set_opt(void *h, const char *name, double v) {
+  Options &o = ((Sys *)h)->opt;
+  std::string k(name);
+#define OPT_I(key, field) if (k == key) { o.field = (int)v; return 0; }
+#define OPT_D(key, field) if (k == key) { o.field = v; return 0; }
+  OPT_D("tolerance", tol) OPT_D("absolute_tolerance", atol) OPT_I("max_iterations", max_iter) OPT_I("kspace", kdim)
+  OPT_I("preconditioner", precond) OPT_I("coarsen_type", coarsen_type) OPT_I("interp_type", interp_type)
+  OPT_I("relax_type", relax_type) OPT_I("relax_order", relax_order) OPT_I("max_levels", max_levels)
+  OPT_I("num_sweeps", num_sweeps) OPT_I("p_max_elmts", p_max_elmts) OPT_I("max_coarse_size", max_coarse_size)
+  OPT_I("min_coarse_size", min_coarse_size) OPT_I("cheby_order", cheby_order) OPT_I("cheby_eig_est", cheby_eig_est)
+  OPT_D("strong_threshold", strong_threshold) OPT_D("max_row_sum", max_row_sum) OPT_D("trunc_factor", trunc_factor)
+  OPT_D("cheby_fraction", cheby_fraction) OPT_D("relax_weight", relax_weight)
+#undef OPT_I
+#undef OPT_D
+  return 1;
+}
+
+// generator (stencil 7 or 27) on a px*py*pz virtual-rank grid with nx*ny*nz rows per rank
+int ora_gen_laplace(void *h, int nx, int ny, int nz, int px, int py, int pz, int stencil) {
+  if ((i64)nx * ny * nz * px * py * pz >= (1LL << 31) - 2) return 1;
+  gen_laplace(*(Sys *)h, nx, ny, nz, px, py, pz, stencil);
+  return 0;
+}
+
+// general matrix: global CSR (any entry order) + rhs + block-row partition over np virtual ranks
+int ora_set_csr(void *h, int n, const int *ptr, const int *col, const double *val, const double *b, int np, const int *part) {
+  Sys &s = *(Sys *)h;
+  s.lev.clear();
+  s.lev.emplace_back();
+  Level &L = s.lev[0];
+  L.A.nr = L.A.nc = n;
+  L.A.ptr.assign(ptr, ptr + n + 1);
+  L.A.col.assign(col, col + ptr[n]);
+  L.A.val.assign(val, val + ptr[n]);
+  s.np = np;
+  if (part) L.part.assign(part, part + np + 1);
+  else L.part = block_partition(n, np);
+  parcsr_order(L.A, L.part, L.part, true);
+  s.b.assign(b, b + n);
+  return 0;
+}
+
+int ora_amg_setup(void *h) { amg_setup(*(Sys *)h); return 0; }
+int ora_gmres_solve(void *h, double *x) {
+  Sys &s = *(Sys *)h;
+  if (s.lev.empty()) return 1;
+  if (s.lev[0].vtemp.empty()) {  // no AMG setup (preconditioner none)
+    s.opt.precond = 0;
+  }
+  gmres(s, x);
+  return 0;
+}
+int ora_vcycle(void *h, const double *r, double *z) {
+  Sys &s = *(Sys *)h;
+  std::fill(z, z + s.lev[0].A.nr, 0.0);
+  vcycle(s, r, z);
+  return 0;
+}
+
+int ora_num_levels(void *h) { return (int)((Sys *)h)->lev.size(); }
+int ora_num_iterations(void *h) { return ((Sys *)h)->iters; }
+int ora_converged(void *h) { return ((Sys *)h)->converged; }
+double ora_final_relres(void *h) { return ((Sys *)h)->relres; }
+double ora_setup_seconds(void *h) { return ((Sys *)h)->setup_s; }
+double ora_solve_seconds(void *h) { return ((Sys *)h)->solve_s; }
+int ora_history(void *h, double *out, int cap) {
+  Sys &s = *(Sys *)h;
+  int n = std::min<int>(cap, (int)s.hist.size());
+  for (int i = 0; i < n; ++i) out[i] = s.hist[i];
+  return (int)s.hist.size();
+}
+int ora_get_rhs(void *h, double *b) {
+  Sys &s = *(Sys *)h;
+  std::copy(s.b.begin(), s.b.end(), b);
+  return 0;
+}
+
+static const Csr *pick(Sys &s, int level, int which) {
+  if (level < 0 || level >= (int)s.lev.size()) return nullptr;
+  Level &L = s.lev[level];
+  switch (which) {
+    case 'A': return &L.A;
+    case 'P': return &L.P;
+    case 'R': return &L.R;
+    case 'S': return &L.S;
+  }
+  return nullptr;
+}
+// which: 'A','P','R','S'.  sizes[0]=rows, [1]=cols, [2]=nnz
+int ora_level_sizes(void *h, int level, int which, long long *sizes) {
+  const Csr *m = pick(*(Sys *)h, level, which);
+  if (!m) return 1;
+  sizes[0] = m->nr; sizes[1] = m->nc; sizes[2] = m->nnz();
+  return 0;
+}
+int ora_level_get(void *h, int level, int which, int *ptr, int *col, double *val) {
+  const Csr *m = pick(*(Sys *)h, level, which);
+  if (!m) return 1;
+  if (ptr) std::copy(m->ptr.begin(), m->ptr.end(), ptr);
+  if (col) std::copy(m->col.begin(), m->col.end(), col);
+  if (val && !m->val.empty()) std::copy(m->val.begin(), m->val.end(), val);
+  return 0;
+}
+int ora_level_cf(void *h, int level, int *cf) {
+  Sys &s = *(Sys *)h;
+  if (level < 0 || level >= (int)s.lev.size()) return 1;
+  const std::vector<int> &c = s.lev[level].cf_raw.empty() ? s.lev[level].cf : s.lev[level].cf_raw;
+  std::copy(c.begin(), c.end(), cf);
+  return 0;
+}
+int ora_level_part(void *h, int level, int *part) {
+  Sys &s = *(Sys *)h;
+  if (level < 0 || level >= (int)s.lev.size()) return 1;
+  std::copy(s.lev[level].part.begin(), s.lev[level].part.end(), part);
+  return 0;
+}
+int ora_level_smoother(void *h, int level, double *l1) {
+  Sys &s = *(Sys *)h;
+  if (level < 0 || level >= (int)s.lev.size()) return 1;
+  const std::vector<double> &v = (s.opt.relax_type == 16) ? s.lev[level].ds : s.lev[level].l1;
+  std::copy(v.begin(), v.end(), l1);
+  return 0;
+}
+int ora_level_cheby(void *h, int level, double *out /* max,min,c0..c3 */) {
+  Sys &s = *(Sys *)h;
+  if (level < 0 || level >= (int)s.lev.size()) return 1;
+  Level &L = s.lev[level];
+  out[0] = L.cheby_max; out[1] = L.cheby_min;
+  for (size_t k = 0; k < 4; ++k) out[2 + k] = k < L.cheby_coef.size() ? L.cheby_coef[k] : 0.0;
+  return 0;
+}
+
+// stand-alone pieces for unit parity tests --------------------------------------------------------------
+int ora_measure(void *h, int level, double *measure) {  // PMIS measure (count + rand) of a level whose S exists
+  Sys &s = *(Sys *)h;
+  if (level < 0 || level >= (int)s.lev.size() || s.lev[level].S.ptr.empty()) return 1;
+  std::vector<int> cf;
+  std::vector<double> m;
+  pmis(s.lev[level].S, s.lev[level].part, cf, &m);
+  std::copy(m.begin(), m.end(), measure);
+  return 0;
+}
+void ora_rand_stream(int seed, int n, double *out) {
+  HypreRand r;
+  r.set(seed);
+  for (int i = 0; i < n; ++i) out[i] = r.rand();
+}
+void ora_qsort2abs(int *v, double *w, int n) { qsort2abs(v, w, 0, n - 1); }
+void ora_ge_solve(const double *A, int n, double *x) {
+  std::vector<double> a(A, A + (size_t)n * n);
+  ge_solve(a, n, x);
+}
+void ora_spmv(int n, const int *ptr, const int *col, const double *val, const double *x, double *y) {
+  for (int i = 0; i < n; ++i) {
+    double s = 0.0;
+    for (int k = ptr[i]; k < ptr[i + 1]; ++k) s += val[k] * x[col[k]];
+    y[i] = s;
+  }
+}
+void ora_block_partition(int n, int np, int *part) {
+  std::vector<int> p = block_partition(n, np);
+  std::copy(p.begin(), p.end(), part);
+}
+
+}  // extern "C"
