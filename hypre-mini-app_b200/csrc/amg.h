@@ -1,0 +1,150 @@
+// amg.h -- internal data structures of the BoomerAMG hierarchy, GMRES solver and ParCSR objects.
+#pragma once
+#include "common.h"
+#include <map>
+#include <memory>
+#include <string>
+
+namespace b200 {
+
+void maybe_build_sell(const DCsr &A, DSell &S);
+
+// ---- ParCSR matrix: block row of the global matrix owned by this rank --------------------------
+// diag: columns inside [col_start, col_start + n_cols_local) in local numbering, diagonal entry first in each row.
+// offd: remaining columns compressed through the sorted col_map_offd (global ids); halo x values are gathered into
+// x_halo (length n_halo) before the offd product.  One rank: offd is empty.
+struct HaloPlan {                 // receive lists grouped by owner (contiguous), send lists in requester order
+  std::vector<int> recv_rank, recv_off;  // recv_off has size recv_rank.size()+1 (offsets into the halo buffer)
+  std::vector<int> send_rank, send_off;
+  DVec<int> send_idx;                     // local indices to pack, concatenated per destination
+  DVec<double> send_buf;
+  int n_send = 0;
+};
+
+struct ParCsr {
+  i64 g_rows = 0, g_cols = 0, row_start = 0, col_start = 0;
+  int n = 0, n_cols_local = 0, n_halo = 0;
+  DCsr diag, offd;
+  DVec<int> offd_rows;            // rows that own at least one offd entry (the offd product runs over these only)
+  std::vector<i64> col_map_offd;  // sorted global ids of the halo columns
+  std::vector<i64> row_starts, col_starts;  // partition over ranks (nranks + 1)
+  HaloPlan halo;
+  DVec<double> x_halo;
+  DSell sell;
+  SpmvPlan plan;
+  void finalize_spmv();           // pick kernels / build SELL after diag is final
+};
+
+struct ParVec {   // local part of a distributed vector; p may point into own or into foreign storage (a view)
+  i64 g_n = 0, start = 0;
+  int n = 0;
+  double *p = nullptr;
+  DVec<double> own;
+  void alloc(int n_) { n = n_; own.alloc(((size_t)n_ + 1) & ~(size_t)1); own.zero(); p = own.p; }
+};
+
+// y-type operation on a ParCsr: local diag product with the fused epilogue, plus halo exchange + offd correction
+// when nranks > 1.
+void par_spmv(ParCsr &A, SpmvMode mode, const SpmvArgs &args);
+
+// ---- BoomerAMG ----------------------------------------------------------------------------------------------------
+struct AmgOptions {
+  int print_level = 0, debug_flag = 0;
+  int coarsen_type = 8;        // HYPRE default 10 (HMIS); mini-app default 8 (HypreSystem.cpp:125-126)
+  int interp_type = 6, relax_type[4] = {18, 18, 18, 9}, num_sweeps[4] = {1, 1, 1, 1};
+  int relax_order = 0, max_levels = 25, cycle_type = 1, max_iter = 20, p_max_elmts = 4;
+  int max_coarse_size = 9, min_coarse_size = 0, cheby_order = 2, cheby_eig_est = 10, keep_transpose = 1, rap2 = 1;
+  int agg_num_levels = 0, smooth_type = 0;
+  double tol = 1e-7, strong_threshold = 0.25, max_row_sum = 0.9, trunc_factor = 0.0, cheby_fraction = 0.3, relax_weight = 1.0;
+  double non_galerkin_tol = 0.0;
+};
+
+struct AmgLevel {
+  ParCsr *A = nullptr;            // level 0: borrowed from the caller; others: owned (A_own)
+  std::unique_ptr<ParCsr> A_own;
+  ParCsr P, R;
+  DVec<int> Sptr, Scol;           // strength pattern (kept for inspection)
+  i64 S_nnz = 0;
+  DVec<int> cf, cf_raw;           // +1 C / -1 F ; cf_raw keeps -3 for isolated points
+  DVec<double> dsm;               // smoother diagonal: l1 norm, a_ii, or Chebyshev D^{-1/2}
+  double cheby_max = 0, cheby_min = 0;
+  std::vector<double> cheby_coef;
+  DVec<double> u, f, r, t0, t1;   // work vectors of the cycle
+};
+
+struct Amg {
+  AmgOptions opt;
+  std::vector<std::unique_ptr<AmgLevel>> lev;
+  // coarsest level: dense LU (unpivoted Gaussian elimination multipliers + U), SURVEY.md A.9
+  DVec<double> ge_lu;
+  int ge_n = 0;
+  bool setup_done = false;
+  DotWork dw;
+  double setup_seconds = 0;
+  std::map<std::string, double> setup_phase_ms;   // CUDA-event time per setup phase (strength, pmis, interp, rap ...)
+  // opaque array handed to hypre_ParAMGDataAArray()
+  std::vector<void *> a_array;
+  // levels >= 1 of the V-cycle captured as a CUDA graph (all their buffers are internal, hence pointer-stable)
+  cudaGraphExec_t graph_exec = nullptr;
+  int graph_launches = 0;
+  ~Amg();
+};
+
+void amg_setup(Amg &amg, ParCsr &A);
+void amg_vcycle(Amg &amg, const double *rhs, double *z);   // z = M^{-1} rhs, zero initial guess
+void amg_solve(Amg &amg, ParCsr &A, const double *b, double *x, int *iters, double *relres);  // BoomerAMG as a solver
+
+// ---- GMRES ----------------------------------------------------------------------------------------------------------
+typedef int (*PrecondFn)(void *solver, void *A, void *b, void *x);  // HYPRE_PtrToParSolverFcn shape
+struct Gmres {
+  double tol = 1e-6, atol = 0.0;
+  int max_iter = 1000, min_iter = 0, k_dim = 5, print_level = 0, logging = 0;
+  int orth = 1;                   // 0 = modified Gram-Schmidt (hypre's), 1 = fused CGS2 (default)
+  PrecondFn precond = nullptr, precond_setup = nullptr;
+  void *precond_data = nullptr;
+  // workspace
+  DVec<double> V;                 // (k_dim + 1) basis vectors, leading dimension ld
+  i64 ld = 0;
+  DVec<double> r, w, hdev;
+  DotWork dw;
+  int n = 0;
+  // results
+  int num_iterations = 0, converged = 0;
+  double rel_residual_norm = 0.0;
+  std::vector<double> history;
+  double solve_seconds = 0;
+};
+void gmres_setup(Gmres &g, ParCsr &A, ParVec &b, ParVec &x);
+int gmres_solve(Gmres &g, ParCsr &A, ParVec &b, ParVec &x);
+
+// ---- IJ interface (ij.cu) --------------------------------------------------------------------------------------------
+struct IJMatrix {
+  i64 ilower = 0, iupper = -1, jlower = 0, jupper = -1;
+  bool assembled = false;
+  // staged COO chunks in insertion order; op: 0 = set, 1 = add
+  struct Chunk { DVec<i64> rows, cols; DVec<double> vals; int op; i64 n; };
+  std::vector<Chunk> staged;
+  ParCsr par;
+};
+struct IJVector {
+  i64 jlower = 0, jupper = -1;
+  int component = 0, num_components = 1;
+  ParVec par;
+};
+void ij_matrix_set(IJMatrix &M, i64 nrows, const int *ncols, const i64 *rows, const int *row_indexes, const i64 *cols,
+                   const double *vals, int op);
+void ij_matrix_assemble(IJMatrix &M);
+void ij_vector_init(IJVector &v);
+void ij_vector_set(IJVector &v, i64 n, const i64 *idx, const double *vals, int op);
+void ij_vector_get(IJVector &v, i64 n, const i64 *idx, double *out);
+
+// ---- setup building blocks (amg_setup.cu), exposed for tests through include/b200hypre.h ----------------------------
+void csr_transpose(const DCsr &A, DCsr &T);
+void csr_spgemm(const DCsr &A, const DCsr &B, DCsr &C, bool diag_first);
+
+// ---- generator (generator.cu): laplace_3d_weak_scaling semantics --------------------------------------------------------
+// fills device COO (global ids) + rhs for this rank's box; returns nnz.  Arrays are allocated by the callee.
+struct GenOut { DVec<i64> rows, cols; DVec<double> vals, rhs; i64 nnz = 0, n_local = 0, row_start = 0, g_rows = 0; };
+void generate_laplace(int nx, int ny, int nz, int px, int py, int pz, int rank, int stencil, GenOut &out);
+
+}  // namespace b200

@@ -1,0 +1,134 @@
+// generator.cu -- 3-D Laplace weak-scaling generator on the device (CUDA; the reference's generator is HIP-only).
+// Semantics of /root/reference/src/laplace_3d_weak_scaling.hpp (process grid :98-169, row/neighbour indexing :216-238,
+// values :558,600, rhs :321) and of the glue in /root/reference/src/HypreSystem.cpp:1476-1607 (rank-contiguous global
+// row ids :1516,1540): every rank owns an nx*ny*nz box of a (px*nx, py*ny, pz*nz) grid, rank -> box
+// (rank % px, (rank / px) % py, rank / (px*py)); local rows are lexicographic (x fastest); global row =
+// rank * nx*ny*nz + local; neighbours outside the global grid are dropped; diagonal = 26 (27-point, the reference)
+// or 6 (7-point, BASELINE.json configs), off-diagonals -1, rhs = diag - (nnz_row - 1) so that x == 1.
+// Off-rank neighbours carry the TRUE neighbour's global row id (the reference glue's surrogate
+// numbering at HypreSystem.cpp:1555 is not reproduced).
+// Output: COO triplets in row order, stencil order (z, y, x offsets ascending) inside a row, plus the rhs.
+#include "amg.h"
+#include <cub/cub.cuh>
+
+namespace b200 {
+
+// process grid (laplace_3d_weak_scaling.hpp:80-169 restated): ascending prime factors f[0..m); m <= 3: the largest
+// factor goes to x, the next to y, the smallest to z; m > 3: x starts from the largest factor and absorbs the smallest
+// unused factors until it reaches cbrt(nprocs), y starts from the next largest and absorbs up to sqrt(nprocs / px),
+// z takes what is left.  1 -> (1,1,1), 2 -> (2,1,1), 4 -> (2,2,1), 8 -> (2,2,2).
+void process_grid(int nprocs, int *px, int *py, int *pz) {
+  std::vector<int> f;
+  for (int n = nprocs, d = 2; n > 1; ++d)
+    for (; n % d == 0; n /= d) f.push_back(d);
+  int g[3] = {1, 1, 1};
+  const size_t m = f.size();
+  if (m <= 3) {
+    for (size_t k = 0; k < m; ++k) g[k] = f[m - 1 - k];
+  } else {
+    size_t lo = 0, hi = m;  // unused factors are f[lo, hi)
+    g[0] = f[--hi];
+    for (const double target = cbrt((double)nprocs); g[0] < target && lo < hi;) g[0] *= f[lo++];
+    const double target_y = sqrt((double)(nprocs / g[0]));
+    g[1] = f[--hi];
+    while (g[1] < target_y && lo < hi) g[1] *= f[lo++];
+    while (lo < hi) g[2] *= f[lo++];
+  }
+  B200_REQUIRE(g[0] * g[1] * g[2] == nprocs, "process_grid: factorisation does not cover nprocs");
+  *px = g[0]; *py = g[1]; *pz = g[2];
+}
+
+namespace {
+
+struct Box {
+  int nx, ny, nz, px, py, pz, bx, by, bz, stencil;
+  i64 nloc, row_start;
+};
+
+__device__ __forceinline__ bool in_stencil(int stencil, int dx, int dy, int dz) {
+  return stencil == 27 || (abs(dx) + abs(dy) + abs(dz) <= 1);
+}
+
+__global__ void k_gen_count(Box b, int *cnt) {
+  i64 l = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (l == b.nloc) cnt[l] = 0;
+  if (l >= b.nloc) return;
+  int lx = (int)(l % b.nx), ly = (int)((l / b.nx) % b.ny), lz = (int)(l / ((i64)b.nx * b.ny));
+  int gx = b.bx * b.nx + lx, gy = b.by * b.ny + ly, gz = b.bz * b.nz + lz;
+  int GX = b.nx * b.px, GY = b.ny * b.py, GZ = b.nz * b.pz;
+  int c = 0;
+  for (int dz = -1; dz <= 1; ++dz)
+    for (int dy = -1; dy <= 1; ++dy)
+      for (int dx = -1; dx <= 1; ++dx) {
+        if (!in_stencil(b.stencil, dx, dy, dz)) continue;
+        int x = gx + dx, y = gy + dy, z = gz + dz;
+        if (x < 0 || y < 0 || z < 0 || x >= GX || y >= GY || z >= GZ) continue;
+        ++c;
+      }
+  cnt[l] = c;
+}
+
+__global__ void k_gen_fill(Box b, const int *ptr, i64 *rows, i64 *cols, double *vals, double *rhs) {
+  i64 l = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (l >= b.nloc) return;
+  int lx = (int)(l % b.nx), ly = (int)((l / b.nx) % b.ny), lz = (int)(l / ((i64)b.nx * b.ny));
+  int gx = b.bx * b.nx + lx, gy = b.by * b.ny + ly, gz = b.bz * b.nz + lz;
+  int GX = b.nx * b.px, GY = b.ny * b.py, GZ = b.nz * b.pz;
+  const double dval = (b.stencil == 27) ? 26.0 : 6.0;
+  i64 grow = b.row_start + l;
+  int p = ptr[l], c = 0;
+  for (int dz = -1; dz <= 1; ++dz)
+    for (int dy = -1; dy <= 1; ++dy)
+      for (int dx = -1; dx <= 1; ++dx) {
+        if (!in_stencil(b.stencil, dx, dy, dz)) continue;
+        int x = gx + dx, y = gy + dy, z = gz + dz;
+        if (x < 0 || y < 0 || z < 0 || x >= GX || y >= GY || z >= GZ) continue;
+        int rx = x / b.nx, ry = y / b.ny, rz = z / b.nz;
+        i64 r = rx + (i64)b.px * (ry + (i64)b.py * rz);
+        i64 gcol = r * b.nloc + (x - rx * b.nx) + (i64)b.nx * ((y - ry * b.ny) + (i64)b.ny * (z - rz * b.nz));
+        rows[p] = grow;
+        cols[p] = gcol;
+        vals[p] = (gcol == grow) ? dval : -1.0;
+        ++p;
+        ++c;
+      }
+  rhs[l] = dval - (double)(c - 1);
+}
+
+}  // namespace
+
+void generate_laplace(int nx, int ny, int nz, int px, int py, int pz, int rank, int stencil, GenOut &out) {
+  ensure_init();
+  B200_REQUIRE(stencil == 7 || stencil == 27, "generator: stencil must be 7 or 27");
+  B200_REQUIRE(nx > 0 && ny > 0 && nz > 0 && px > 0 && py > 0 && pz > 0 && rank >= 0 && rank < px * py * pz, "generator: bad box");
+  Box b;
+  b.nx = nx; b.ny = ny; b.nz = nz; b.px = px; b.py = py; b.pz = pz; b.stencil = stencil;
+  b.bx = rank % px; b.by = (rank / px) % py; b.bz = rank / (px * py);
+  b.nloc = (i64)nx * ny * nz;
+  b.row_start = (i64)rank * b.nloc;
+  B200_REQUIRE(b.nloc * stencil < (1LL << 31) - 8, "generator: more than 2^31 nonzeros per rank");
+  DVec<int> cnt((size_t)b.nloc + 1), ptr((size_t)b.nloc + 1);
+  int grid = div_up(b.nloc + 1, 256);
+  k_gen_count<<<grid, 256, 0, stream()>>>(b, cnt.p);
+  size_t tb = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt.p, ptr.p, (int)(b.nloc + 1), stream());
+  DVec<char> tmp(tb);
+  cub::DeviceScan::ExclusiveSum(tmp.p, tb, cnt.p, ptr.p, (int)(b.nloc + 1), stream());
+  int nnz = 0;
+  B200_CUDA(cudaMemcpyAsync(&nnz, ptr.p + b.nloc, sizeof(int), cudaMemcpyDeviceToHost, stream()));
+  B200_CUDA(cudaStreamSynchronize(stream()));
+  out.nnz = nnz;
+  out.n_local = b.nloc;
+  out.row_start = b.row_start;
+  out.g_rows = b.nloc * px * py * pz;
+  out.rows.alloc((size_t)nnz);
+  out.cols.alloc((size_t)nnz);
+  out.vals.alloc((size_t)nnz);
+  out.rhs.alloc((size_t)b.nloc);
+  k_gen_fill<<<div_up(b.nloc, 256), 256, 0, stream()>>>(b, ptr.p, out.rows.p, out.cols.p, out.vals.p, out.rhs.p);
+  count_launch(4);
+  B200_KERNEL_CHECK();
+  B200_CUDA(cudaStreamSynchronize(stream()));
+}
+
+}  // namespace b200

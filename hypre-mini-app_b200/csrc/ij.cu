@@ -1,0 +1,419 @@
+// ij.cu -- IJ matrix / vector assembly on the device: COO triplets (global ids) -> ParCSR (diag + offd).
+// Replaces HYPRE_IJMatrixSetValues2 / AddToValues2 / Assemble and HYPRE_IJVectorSetValues / GetValues as driven by
+// /root/reference/src/HypreSystem.cpp:897-1015 (one column per "row", ncols == NULL, host or device pointers),
+// :600-636 (assemble) and :1567-1596 (generator: Set for the diag block, AddTo for the offd block).
+// Semantics: Set overwrites, AddTo accumulates, in call order; rows sorted by (row, col); diag block
+// in local column numbering with the diagonal entry first; offd columns compressed through the sorted col_map_offd.
+// Fast path: a single staged chunk that is already strictly sorted by (row, col) skips the radix sorts.
+#include "amg.h"
+#include <cub/cub.cuh>
+#include <algorithm>
+
+namespace b200 {
+
+void ij_add_int(int n, const int *a, const int *b, int *c);
+void build_partition_and_halo(ParCsr &A);
+
+namespace {
+
+bool is_device_ptr(const void *p) {
+  if (!p) return false;
+  cudaPointerAttributes at;
+  cudaError_t e = cudaPointerGetAttributes(&at, p);
+  if (e != cudaSuccess) { cudaGetLastError(); return false; }
+  return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+template <class T>
+void stage_copy(DVec<T> &dst, const T *src, i64 n) {
+  dst.alloc((size_t)n);
+  if (n == 0) return;
+  B200_CUDA(cudaMemcpyAsync(dst.p, src, n * sizeof(T), is_device_ptr(src) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, stream()));
+}
+
+__global__ void k_check_sorted(i64 n, const i64 *rows, const i64 *cols, int *bad) {
+  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k == 0 || k >= n) return;
+  i64 r0 = rows[k - 1], r1 = rows[k];
+  if (r1 < r0 || (r1 == r0 && cols[k] <= cols[k - 1])) *bad = 1;
+}
+__global__ void k_check_range(i64 n, const i64 *rows, i64 lo, i64 hi, int *bad) {
+  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n && (rows[k] < lo || rows[k] > hi)) *bad = 1;
+}
+__global__ void k_iota64(i64 n, int *a) {
+  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n) a[k] = (int)k;
+}
+template <class T>
+__global__ void k_gather(i64 n, const int *perm, const T *in, T *out) {
+  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n) out[k] = in[perm[k]];
+}
+// after the stable sort by (row, col): head[k] = 1 where a new (row, col) key starts
+__global__ void k_heads(i64 n, const i64 *rows, const i64 *cols, int *head) {
+  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  head[k] = (k == 0 || rows[k] != rows[k - 1] || cols[k] != cols[k - 1]) ? 1 : 0;
+}
+// combine duplicates in insertion order: set -> v, add -> += v.  One thread per unique key (slot = scan(head)).
+__global__ void k_combine(i64 n, const int *head, const int *slot, const i64 *rows, const i64 *cols, const double *vals,
+                          const signed char *ops, i64 *urows, i64 *ucols, double *uvals) {
+  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n || !head[k]) return;
+  double v = 0.0;
+  i64 j = k;
+  do {
+    v = ops[j] ? (v + vals[j]) : vals[j];
+    ++j;
+  } while (j < n && !head[j]);
+  int s = slot[k];
+  urows[s] = rows[k];
+  ucols[s] = cols[k];
+  uvals[s] = v;
+}
+// per-row counts of diag / offd entries (rows are global ids, sorted)
+__global__ void k_row_counts(i64 n, const i64 *rows, const i64 *cols, i64 ilower, i64 jlower, i64 jupper, int *dcnt, int *ocnt) {
+  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  int r = (int)(rows[k] - ilower);
+  i64 c = cols[k];
+  if (c >= jlower && c <= jupper) atomicAdd(dcnt + r, 1);
+  else atomicAdd(ocnt + r, 1);
+}
+__device__ __forceinline__ int lower_bound_i64(const i64 *a, int n, i64 key) {
+  int lo = 0, hi = n;
+  while (lo < hi) {
+    int mid = (lo + hi) >> 1;
+    if (a[mid] < key) lo = mid + 1;
+    else hi = mid;
+  }
+  return lo;
+}
+// thread per row: split the sorted row into diag (diagonal first) and offd (compressed columns)
+__global__ void k_split_fill(int nrows, const int *rowstart, const i64 *cols, const double *vals, i64 ilower, i64 jlower, i64 jupper,
+                             const int *dptr, int *dcol, double *dval, const int *optr, int *ocol, double *oval,
+                             const i64 *colmap, int ncolmap) {
+  int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= nrows) return;
+  int b = rowstart[r], e = rowstart[r + 1];
+  i64 gdiag = ilower + r;
+  int dp = dptr[r], op = optr ? optr[r] : 0;
+  // diagonal first
+  int dk = -1;
+  for (int k = b; k < e; ++k)
+    if (cols[k] == gdiag) { dk = k; break; }
+  if (dk >= 0 && gdiag >= jlower && gdiag <= jupper) {
+    dcol[dp] = (int)(gdiag - jlower);
+    dval[dp] = vals[dk];
+    ++dp;
+  } else dk = -1;
+  for (int k = b; k < e; ++k) {
+    if (k == dk) continue;
+    i64 c = cols[k];
+    if (c >= jlower && c <= jupper) {
+      dcol[dp] = (int)(c - jlower);
+      dval[dp] = vals[k];
+      ++dp;
+    } else {
+      ocol[op] = lower_bound_i64(colmap, ncolmap, c);
+      oval[op] = vals[k];
+      ++op;
+    }
+  }
+}
+__global__ void k_collect_offd(i64 n, const i64 *cols, i64 jlower, i64 jupper, i64 *out, int *counter) {
+  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  i64 c = cols[k];
+  if (c < jlower || c > jupper) out[atomicAdd(counter, 1)] = c;
+}
+__global__ void k_offd_rows(int n, const int *optr, int *flag) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) flag[i] = optr[i + 1] > optr[i] ? 1 : 0;
+  if (i == n) flag[i] = 0;
+}
+__global__ void k_compact_rows(int n, const int *flag, const int *pos, int *list) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && flag[i]) list[pos[i]] = i;
+}
+
+template <class T>
+void exscan(const T *in, T *out, i64 n) {
+  size_t tb = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, tb, in, out, (int)n, stream());
+  DVec<char> tmp(tb);
+  cub::DeviceScan::ExclusiveSum(tmp.p, tb, in, out, (int)n, stream());
+  count_launch(2);
+}
+template <class T>
+T fetch1(const T *dev) {
+  T h;
+  B200_CUDA(cudaMemcpyAsync(&h, dev, sizeof(T), cudaMemcpyDeviceToHost, stream()));
+  B200_CUDA(cudaStreamSynchronize(stream()));
+  return h;
+}
+
+__global__ void k_vec_set(i64 n, const i64 *idx, const double *vals, i64 lo, i64 hi, double *v, int op, i64 seq_start) {
+  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  i64 g = idx ? idx[k] : (seq_start + k);
+  if (g < lo || g > hi) return;
+  if (op) v[g - lo] += vals[k];
+  else v[g - lo] = vals[k];
+}
+__global__ void k_vec_get(i64 n, const i64 *idx, double *out, i64 lo, i64 hi, const double *v) {
+  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  i64 g = idx ? idx[k] : (lo + k);
+  out[k] = (g >= lo && g <= hi) ? v[g - lo] : 0.0;
+}
+
+}  // namespace
+
+void ij_matrix_set(IJMatrix &M, i64 nrows, const int *ncols, const i64 *rows, const int *row_indexes, const i64 *cols,
+                   const double *vals, int op) {
+  ensure_init();
+  if (nrows <= 0) return;
+  IJMatrix::Chunk ch;
+  ch.op = op;
+  if (ncols == nullptr) {  // one entry per "row" (the mini-app's usage)
+    ch.n = nrows;
+    stage_copy(ch.rows, rows, nrows);
+    stage_copy(ch.cols, cols, nrows);
+    stage_copy(ch.vals, vals, nrows);
+  } else {  // general CSR-like call: expand on the host (host pointers only)
+    B200_REQUIRE(!is_device_ptr(ncols) && !is_device_ptr(rows) && !is_device_ptr(cols) && !is_device_ptr(vals),
+                 "IJMatrixSetValues2 with ncols != NULL expects host pointers");
+    std::vector<i64> r, c;
+    std::vector<double> v;
+    i64 off = 0;
+    for (i64 i = 0; i < nrows; ++i) {
+      i64 start = row_indexes ? row_indexes[i] : off;
+      for (int k = 0; k < ncols[i]; ++k) { r.push_back(rows[i]); c.push_back(cols[start + k]); v.push_back(vals[start + k]); }
+      off += ncols[i];
+    }
+    ch.n = (i64)r.size();
+    ch.rows.from_host(r);
+    ch.cols.from_host(c);
+    ch.vals.from_host(v);
+    B200_CUDA(cudaStreamSynchronize(stream()));
+  }
+  M.assembled = false;
+  M.staged.push_back(std::move(ch));
+}
+
+void ij_matrix_assemble(IJMatrix &M) {
+  ensure_init();
+  if (M.assembled && M.staged.empty()) return;
+  const int nranks = ctx().nranks;
+  i64 ntot = 0;
+  for (auto &c : M.staged) ntot += c.n;
+  B200_REQUIRE(ntot < (1LL << 31) - 8, "IJ assemble: more than 2^31 staged entries on one rank");
+  const int nloc = (int)(M.iupper - M.ilower + 1);
+  ParCsr &A = M.par;
+  A.n = nloc;
+  A.n_cols_local = (int)(M.jupper - M.jlower + 1);
+  A.row_start = M.ilower;
+  A.col_start = M.jlower;
+  // sorted, unique COO
+  DVec<i64> rows, cols;
+  DVec<double> vals;
+  i64 nu = 0;
+  bool fast = false;
+  DVec<int> bad(1);
+  if (M.staged.size() == 1 && M.staged[0].op == 0) {
+    auto &c = M.staged[0];
+    bad.zero();
+    if (c.n) k_check_sorted<<<div_up(c.n, 256), 256, 0, stream()>>>(c.n, c.rows.p, c.cols.p, bad.p);
+    count_launch();
+    fast = (fetch1(bad.p) == 0);
+  }
+  if (fast) {
+    rows = std::move(M.staged[0].rows);
+    cols = std::move(M.staged[0].cols);
+    vals = std::move(M.staged[0].vals);
+    nu = M.staged[0].n;
+  } else if (ntot > 0) {
+    DVec<i64> r0((size_t)ntot), c0((size_t)ntot);
+    DVec<double> v0((size_t)ntot);
+    DVec<signed char> o0((size_t)ntot);
+    i64 off = 0;
+    for (auto &c : M.staged) {
+      if (!c.n) continue;
+      B200_CUDA(cudaMemcpyAsync(r0.p + off, c.rows.p, c.n * sizeof(i64), cudaMemcpyDeviceToDevice, stream()));
+      B200_CUDA(cudaMemcpyAsync(c0.p + off, c.cols.p, c.n * sizeof(i64), cudaMemcpyDeviceToDevice, stream()));
+      B200_CUDA(cudaMemcpyAsync(v0.p + off, c.vals.p, c.n * sizeof(double), cudaMemcpyDeviceToDevice, stream()));
+      B200_CUDA(cudaMemsetAsync(o0.p + off, c.op, c.n, stream()));
+      off += c.n;
+    }
+    // stable sort by col, then stable sort by row (LSD on the pair)
+    DVec<int> perm0((size_t)ntot), perm1((size_t)ntot), perm2((size_t)ntot);
+    DVec<i64> k1((size_t)ntot), k2((size_t)ntot), ktmp((size_t)ntot);
+    k_iota64<<<div_up(ntot, 256), 256, 0, stream()>>>(ntot, perm0.p);
+    size_t tb = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, tb, c0.p, k1.p, perm0.p, perm1.p, (int)ntot, 0, 64, stream());
+    DVec<char> tmp(tb);
+    cub::DeviceRadixSort::SortPairs(tmp.p, tb, c0.p, k1.p, perm0.p, perm1.p, (int)ntot, 0, 64, stream());
+    k_gather<i64><<<div_up(ntot, 256), 256, 0, stream()>>>(ntot, perm1.p, r0.p, ktmp.p);  // rows in col-sorted order
+    cub::DeviceRadixSort::SortPairs(tmp.p, tb, ktmp.p, k2.p, perm1.p, perm2.p, (int)ntot, 0, 64, stream());
+    // gather everything by perm2
+    DVec<i64> rs((size_t)ntot), cs((size_t)ntot);
+    DVec<double> vs((size_t)ntot);
+    DVec<signed char> os((size_t)ntot);
+    k_gather<i64><<<div_up(ntot, 256), 256, 0, stream()>>>(ntot, perm2.p, r0.p, rs.p);
+    k_gather<i64><<<div_up(ntot, 256), 256, 0, stream()>>>(ntot, perm2.p, c0.p, cs.p);
+    k_gather<double><<<div_up(ntot, 256), 256, 0, stream()>>>(ntot, perm2.p, v0.p, vs.p);
+    k_gather<signed char><<<div_up(ntot, 256), 256, 0, stream()>>>(ntot, perm2.p, o0.p, os.p);
+    DVec<int> head((size_t)ntot + 1), slot((size_t)ntot + 1);
+    head.zero();
+    k_heads<<<div_up(ntot, 256), 256, 0, stream()>>>(ntot, rs.p, cs.p, head.p);
+    exscan(head.p, slot.p, ntot + 1);
+    nu = fetch1(slot.p + ntot);
+    rows.alloc((size_t)nu);
+    cols.alloc((size_t)nu);
+    vals.alloc((size_t)nu);
+    k_combine<<<div_up(ntot, 256), 256, 0, stream()>>>(ntot, head.p, slot.p, rs.p, cs.p, vs.p, os.p, rows.p, cols.p, vals.p);
+    count_launch(12);
+    B200_KERNEL_CHECK();
+  }
+  M.staged.clear();
+  if (nu) {
+    bad.zero();
+    k_check_range<<<div_up(nu, 256), 256, 0, stream()>>>(nu, rows.p, M.ilower, M.iupper, bad.p);
+    count_launch();
+    B200_REQUIRE(fetch1(bad.p) == 0, "IJ assemble: a row index lies outside [ilower, iupper] of this rank");
+  }
+  // row pointers
+  DVec<int> dcnt((size_t)nloc + 1), ocnt((size_t)nloc + 1);
+  dcnt.zero();
+  ocnt.zero();
+  if (nu) k_row_counts<<<div_up(nu, 256), 256, 0, stream()>>>(nu, rows.p, cols.p, M.ilower, M.jlower, M.jupper, dcnt.p, ocnt.p);
+  count_launch();
+  A.diag.nr = nloc;
+  A.diag.nc = A.n_cols_local;
+  A.diag.ptr.alloc((size_t)nloc + 1);
+  A.offd.nr = nloc;
+  A.offd.ptr.alloc((size_t)nloc + 1);
+  exscan(dcnt.p, A.diag.ptr.p, (i64)nloc + 1);
+  exscan(ocnt.p, A.offd.ptr.p, (i64)nloc + 1);
+  A.diag.nnz = fetch1(A.diag.ptr.p + nloc);
+  A.offd.nnz = fetch1(A.offd.ptr.p + nloc);
+  B200_REQUIRE(nranks > 1 || A.offd.nnz == 0, "IJ assemble: column index outside [jlower, jupper] on a single-rank run");
+  A.diag.col.alloc((size_t)A.diag.nnz);
+  A.diag.val.alloc((size_t)A.diag.nnz);
+  A.offd.col.alloc((size_t)A.offd.nnz);
+  A.offd.val.alloc((size_t)A.offd.nnz);
+  // column map of the offd block: sorted unique global ids
+  DVec<i64> colmap;
+  A.col_map_offd.clear();
+  if (A.offd.nnz > 0) {
+    DVec<i64> oc((size_t)A.offd.nnz), ocs((size_t)A.offd.nnz), ocu((size_t)A.offd.nnz);
+    DVec<int> counter(1), nsel(1);
+    counter.zero();
+    k_collect_offd<<<div_up(nu, 256), 256, 0, stream()>>>(nu, cols.p, M.jlower, M.jupper, oc.p, counter.p);
+    size_t tb = 0;
+    cub::DeviceRadixSort::SortKeys(nullptr, tb, oc.p, ocs.p, (int)A.offd.nnz, 0, 64, stream());
+    DVec<char> tmp(tb);
+    cub::DeviceRadixSort::SortKeys(tmp.p, tb, oc.p, ocs.p, (int)A.offd.nnz, 0, 64, stream());
+    size_t tb2 = 0;
+    cub::DeviceSelect::Unique(nullptr, tb2, ocs.p, ocu.p, nsel.p, (int)A.offd.nnz, stream());
+    DVec<char> tmp2(tb2);
+    cub::DeviceSelect::Unique(tmp2.p, tb2, ocs.p, ocu.p, nsel.p, (int)A.offd.nnz, stream());
+    int nh = fetch1(nsel.p);
+    A.col_map_offd.resize(nh);
+    B200_CUDA(cudaMemcpyAsync(A.col_map_offd.data(), ocu.p, nh * sizeof(i64), cudaMemcpyDeviceToHost, stream()));
+    B200_CUDA(cudaStreamSynchronize(stream()));
+    colmap.from_host(A.col_map_offd);
+    count_launch(4);
+  }
+  A.n_halo = (int)A.col_map_offd.size();
+  A.offd.nc = A.n_halo;
+  // row starts of the sorted COO = diag.ptr + offd.ptr
+  DVec<int> rowstart((size_t)nloc + 1);
+  ij_add_int(nloc + 1, A.diag.ptr.p, A.offd.ptr.p, rowstart.p);
+  if (nloc)
+    k_split_fill<<<div_up(nloc, 256), 256, 0, stream()>>>(nloc, rowstart.p, cols.p, vals.p, M.ilower, M.jlower, M.jupper,
+                                                          A.diag.ptr.p, A.diag.col.p, A.diag.val.p, A.offd.ptr.p, A.offd.col.p,
+                                                          A.offd.val.p, colmap.p, A.n_halo);
+  count_launch();
+  // rows with offd entries
+  if (A.offd.nnz > 0) {
+    DVec<int> flag((size_t)nloc + 1), pos((size_t)nloc + 1);
+    k_offd_rows<<<div_up((i64)nloc + 1, 256), 256, 0, stream()>>>(nloc, A.offd.ptr.p, flag.p);
+    exscan(flag.p, pos.p, (i64)nloc + 1);
+    int nr = fetch1(pos.p + nloc);
+    A.offd_rows.alloc((size_t)nr);
+    k_compact_rows<<<div_up(nloc, 256), 256, 0, stream()>>>(nloc, flag.p, pos.p, A.offd_rows.p);
+    count_launch(2);
+  }
+  B200_KERNEL_CHECK();
+  // global sizes / partition
+  i64 g[2] = {(i64)nloc, (i64)A.n_cols_local};
+  allreduce_sum_host_i64(g, 2);
+  A.g_rows = g[0];
+  A.g_cols = g[1];
+  build_partition_and_halo(A);
+  A.sell = DSell();
+  A.finalize_spmv();
+  M.assembled = true;
+  B200_CUDA(cudaStreamSynchronize(stream()));
+}
+
+__global__ void k_add_int(int n, const int *a, const int *b, int *c) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) c[i] = a[i] + b[i];
+}
+void ij_add_int(int n, const int *a, const int *b, int *c) {
+  if (n > 0) k_add_int<<<div_up(n, 256), 256, 0, stream()>>>(n, a, b, c);
+  count_launch();
+}
+
+void ij_vector_init(IJVector &v) {
+  ensure_init();
+  int n = (int)(v.jupper - v.jlower + 1);
+  v.par.alloc(n);
+  v.par.start = v.jlower;
+  i64 g = n;
+  allreduce_sum_host_i64(&g, 1);
+  v.par.g_n = g;
+}
+
+void ij_vector_set(IJVector &v, i64 n, const i64 *idx, const double *vals, int op) {
+  ensure_init();
+  if (n <= 0) return;
+  B200_REQUIRE(v.par.p != nullptr, "IJVector: SetValues before Initialize");
+  DVec<i64> di;
+  DVec<double> dv;
+  const i64 *pi = idx;
+  const double *pv = vals;
+  if (idx && !is_device_ptr(idx)) { di.from_host(idx, (size_t)n); pi = di.p; }
+  if (!is_device_ptr(vals)) { dv.from_host(vals, (size_t)n); pv = dv.p; }
+  k_vec_set<<<div_up(n, 256), 256, 0, stream()>>>(n, pi, pv, v.jlower, v.jupper, v.par.p, op, v.jlower);
+  count_launch();
+  B200_CUDA(cudaStreamSynchronize(stream()));
+}
+
+void ij_vector_get(IJVector &v, i64 n, const i64 *idx, double *out) {
+  ensure_init();
+  if (n <= 0) return;
+  DVec<i64> di;
+  const i64 *pi = idx;
+  if (idx && !is_device_ptr(idx)) { di.from_host(idx, (size_t)n); pi = di.p; }
+  if (is_device_ptr(out)) {
+    k_vec_get<<<div_up(n, 256), 256, 0, stream()>>>(n, pi, out, v.jlower, v.jupper, v.par.p);
+    count_launch();
+    B200_CUDA(cudaStreamSynchronize(stream()));
+  } else if (!idx && n == v.par.n) {
+    B200_CUDA(cudaMemcpyAsync(out, v.par.p, n * sizeof(double), cudaMemcpyDeviceToHost, stream()));
+    B200_CUDA(cudaStreamSynchronize(stream()));
+  } else {
+    DVec<double> tmp((size_t)n);
+    k_vec_get<<<div_up(n, 256), 256, 0, stream()>>>(n, pi, tmp.p, v.jlower, v.jupper, v.par.p);
+    count_launch();
+    B200_CUDA(cudaMemcpyAsync(out, tmp.p, n * sizeof(double), cudaMemcpyDeviceToHost, stream()));
+    B200_CUDA(cudaStreamSynchronize(stream()));
+  }
+}
+
+}  // namespace b200

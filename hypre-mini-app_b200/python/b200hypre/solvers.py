@@ -1,0 +1,177 @@
+"""BoomerAMG and ParCSR-GMRES handles over the C ABI (setters mirror /root/reference/src/HypreSystem.cpp:119-326,390-404)."""
+import ctypes as C
+
+import numpy as np
+
+from . import F64, I32, I64, VP, _ptr, check, lib
+
+
+class BoomerAMG:
+    # YAML key (boomeramg_settings, HypreSystem.cpp:119-326) -> setter
+    _INT = {
+        "print_level": "SetPrintLevel", "debug_flag": "SetDebugFlag", "coarsen_type": "SetCoarsenType",
+        "cycle_type": "SetCycleType", "relax_type": "SetRelaxType", "num_sweeps": "SetNumSweeps",
+        "smooth_num_sweeps": "SetSmoothNumSweeps", "max_iterations": "SetMaxIter", "relax_order": "SetRelaxOrder",
+        "max_levels": "SetMaxLevels", "variant": "SetVariant", "rap2": "SetRAP2", "keep_transpose": "SetKeepTranspose",
+        "interp_type": "SetInterpType", "min_coarse_size": "SetMinCoarseSize", "max_coarse_size": "SetMaxCoarseSize",
+        "pmax_elmts": "SetAggPMaxElmts", "agg_pmax_elmts": "SetAggPMaxElmts", "agg_num_levels": "SetAggNumLevels",
+        "agg_interp_type": "SetAggInterpType", "smooth_type": "SetSmoothType", "smooth_num_levels": "SetSmoothNumLevels",
+        # not reachable from the mini-app's YAML but part of hypre's API
+        "p_max_elmts": "SetPMaxElmts", "cheby_order": "SetChebyOrder", "cheby_eig_est": "SetChebyEigEst",
+    }
+    _REAL = {
+        "tolerance": "SetTol", "strong_threshold": "SetStrongThreshold", "non_galerkin_tol": "SetNonGalerkinTol",
+        "trunc_factor": "SetTruncFactor", "max_row_sum": "SetMaxRowSum", "relax_weight": "SetRelaxWt",
+        "cheby_fraction": "SetChebyFraction",
+    }
+
+    def __init__(self, **settings):
+        self.h = VP()
+        check(lib().HYPRE_BoomerAMGCreate(C.byref(self.h)), "BoomerAMGCreate")
+        self.set(**settings)
+
+    def set(self, **settings):
+        L = lib()
+        for k, v in settings.items():
+            if k in self._INT:
+                check(getattr(L, "HYPRE_BoomerAMG" + self._INT[k])(self.h, int(v)), k)
+            elif k in self._REAL:
+                check(getattr(L, "HYPRE_BoomerAMG" + self._REAL[k])(self.h, float(v)), k)
+            elif k in ("down_relax_type", "up_relax_type", "coarse_relax_type"):
+                kk = {"down_relax_type": 1, "up_relax_type": 2, "coarse_relax_type": 3}[k]
+                check(L.HYPRE_BoomerAMGSetCycleRelaxType(self.h, int(v), kk), k)
+            elif k in ("num_down_sweeps", "num_up_sweeps", "num_coarse_sweeps"):
+                kk = {"num_down_sweeps": 1, "num_up_sweeps": 2, "num_coarse_sweeps": 3}[k]
+                check(L.HYPRE_BoomerAMGSetCycleNumSweeps(self.h, int(v), kk), k)
+            else:
+                raise KeyError(f"unknown boomeramg setting {k}")
+
+    def setup(self, A, b=None, x=None):
+        check(lib().HYPRE_BoomerAMGSetup(self.h, A.object(), b.object() if b else None, x.object() if x else None), "BoomerAMGSetup")
+
+    def solve(self, A, b, x):
+        check(lib().HYPRE_BoomerAMGSolve(self.h, A.object(), b.object(), x.object()), "BoomerAMGSolve")
+
+    # ---- inspection -----------------------------------------------------------------------------------------------------
+    @property
+    def num_levels(self):
+        return lib().b200hypre_amg_num_levels(self.h)
+
+    @property
+    def setup_seconds(self):
+        return lib().b200hypre_amg_setup_seconds(self.h)
+
+    def setup_phases(self):
+        names = C.create_string_buffer(1024)
+        ms = np.zeros(32)
+        n = lib().b200hypre_amg_setup_phases(self.h, names, 1024, _ptr(ms), 32)
+        return dict(zip(names.value.decode().split(";"), ms[:n].tolist())) if n else {}
+
+    def level_sizes(self, level, which="A"):
+        sizes = np.zeros(4, dtype=np.int64)
+        check(lib().b200hypre_amg_level_sizes(self.h, level, ord(which), _ptr(sizes)), "level_sizes")
+        return sizes
+
+    def level_matrix(self, level, which="A"):
+        """(ptr int32, col int64 global, val float64 or None for 'S')"""
+        s = self.level_sizes(level, which)
+        ptr = np.zeros(s[0] + 1, dtype=np.int32)
+        col = np.zeros(s[2], dtype=np.int64)
+        val = None if which == "S" else np.zeros(s[2])
+        check(lib().b200hypre_amg_level_get(self.h, level, ord(which), _ptr(ptr), _ptr(col), _ptr(val)), "level_get")
+        return ptr, col, val
+
+    def level_cf(self, level):
+        n = int(self.level_sizes(level, "A")[0])
+        cf = np.zeros(n, dtype=np.int32)
+        check(lib().b200hypre_amg_level_cf(self.h, level, _ptr(cf)), "level_cf")
+        return cf
+
+    def level_smoother(self, level):
+        n = int(self.level_sizes(level, "A")[0])
+        d = np.zeros(n)
+        check(lib().b200hypre_amg_level_smoother(self.h, level, _ptr(d)), "level_smoother")
+        return d
+
+    def level_cheby(self, level):
+        out = np.zeros(6)
+        check(lib().b200hypre_amg_level_cheby(self.h, level, _ptr(out)))
+        return out
+
+    def vcycle_ptr(self, r_ptr, z_ptr):
+        check(lib().b200hypre_amg_vcycle(self.h, VP(r_ptr), VP(z_ptr)), "vcycle")
+
+    def relax_ptr(self, level, u_ptr, f_ptr):
+        check(lib().b200hypre_amg_relax(self.h, level, VP(u_ptr), VP(f_ptr)), "relax")
+
+    def destroy(self):
+        if self.h:
+            lib().HYPRE_BoomerAMGDestroy(self.h)
+            self.h = None
+
+
+class GMRES:
+    def __init__(self, tolerance=1e-5, max_iterations=1000, kspace=10, print_level=0, absolute_tolerance=0.0, orthogonalization=None):
+        L = lib()
+        self.h = VP()
+        check(L.HYPRE_ParCSRGMRESCreate(0, C.byref(self.h)), "GMRESCreate")
+        check(L.HYPRE_ParCSRGMRESSetTol(self.h, float(tolerance)))
+        check(L.HYPRE_ParCSRGMRESSetMaxIter(self.h, int(max_iterations)))
+        check(L.HYPRE_ParCSRGMRESSetKDim(self.h, int(kspace)))
+        check(L.HYPRE_ParCSRGMRESSetPrintLevel(self.h, int(print_level)))
+        if absolute_tolerance:
+            check(L.HYPRE_ParCSRGMRESSetAbsoluteTol(self.h, float(absolute_tolerance)))
+        if orthogonalization is not None:
+            check(L.b200hypre_gmres_set_orthogonalization(self.h, {"mgs": 0, "cgs2": 1}[orthogonalization]))
+
+    def set_precond(self, amg):
+        L = lib()
+        if amg is None:
+            check(L.HYPRE_ParCSRGMRESSetPrecond(self.h, None, None, None))
+        else:  # HypreSystem.cpp:402 with the pointers stored at :323-324
+            solve = C.cast(L.HYPRE_BoomerAMGSolve, VP)
+            setup = C.cast(L.HYPRE_BoomerAMGSetup, VP)
+            check(L.HYPRE_ParCSRGMRESSetPrecond(self.h, solve, setup, amg.h))
+
+    def setup(self, A, b, x):
+        check(lib().HYPRE_ParCSRGMRESSetup(self.h, A.object(), b.object(), x.object()), "GMRESSetup")
+
+    def solve(self, A, b, x):
+        rc = lib().HYPRE_ParCSRGMRESSolve(self.h, A.object(), b.object(), x.object())
+        if rc == 256:  # HYPRE_ERROR_CONV: reported, not fatal (the mini-app ignores return codes, HypreSystem.cpp:723)
+            lib().HYPRE_ClearAllErrors()
+            return rc
+        check(rc, "GMRESSolve")
+        return 0
+
+    @property
+    def iterations(self):
+        v = I32()
+        check(lib().HYPRE_ParCSRGMRESGetNumIterations(self.h, C.byref(v)))
+        return v.value
+
+    @property
+    def relres(self):
+        v = F64()
+        check(lib().HYPRE_ParCSRGMRESGetFinalRelativeResidualNorm(self.h, C.byref(v)))
+        return v.value
+
+    @property
+    def converged(self):
+        v = I32()
+        check(lib().HYPRE_ParCSRGMRESGetConverged(self.h, C.byref(v)))
+        return v.value
+
+    @property
+    def solve_seconds(self):
+        return lib().b200hypre_gmres_solve_seconds(self.h)
+
+    def history(self):
+        out = np.zeros(4096)
+        n = lib().b200hypre_gmres_get_history(self.h, _ptr(out), 4096)
+        return out[:n].copy()
+
+    def destroy(self):
+        if self.h:
+            lib().HYPRE_ParCSRGMRESDestroy(self.h)
+            self.h = None

@@ -1,0 +1,79 @@
+/* b200hypre.h -- extensions of libb200hypre beyond hypre's public API: rank wiring without MPI, the device generator,
+ * hierarchy inspection (the parity artefacts of SURVEY.md §8d), instrumentation used by bench.py, and a few test
+ * hooks for the building blocks.  Plain C ABI: pointers and sizes only. */
+#ifndef B200HYPRE_EXT_H
+#define B200HYPRE_EXT_H
+#include "HYPRE.h"
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- ranks: one process per GPU (replaces MPI_Init / MPI_Comm_rank / MPI_Comm_size, main.cpp:33-45) ------------------ */
+HYPRE_Int b200hypre_get_unique_id(void *out128);                     /* rank 0: 128-byte NCCL id to ship to the others */
+HYPRE_Int b200hypre_comm_init(HYPRE_Int rank, HYPRE_Int nranks, const void *id128);   /* id may be NULL when nranks == 1 */
+HYPRE_Int b200hypre_comm_init_from_env(void);                        /* RANK / WORLD_SIZE / LOCAL_RANK / MASTER_ADDR / MASTER_PORT */
+HYPRE_Int b200hypre_comm_finalize(void);
+HYPRE_Int b200hypre_comm_rank(void);
+HYPRE_Int b200hypre_comm_size(void);
+HYPRE_Int b200hypre_barrier(void);
+HYPRE_Int b200hypre_allreduce_max(double *values, HYPRE_Int count);  /* host values, in place */
+HYPRE_Int b200hypre_allreduce_sum(double *values, HYPRE_Int count);
+
+/* ---- generator: laplace_3d_weak_scaling semantics (laplace_3d_weak_scaling.hpp:604-1090, HypreSystem.cpp:1476-1607) --- */
+void b200hypre_process_grid(HYPRE_Int nprocs, HYPRE_Int *px, HYPRE_Int *py, HYPRE_Int *pz);   /* hpp:98-169; host only */
+/* Fills DEVICE arrays owned by the caller afterwards (release with b200hypre_free(p, HYPRE_MEMORY_DEVICE)):
+ * COO triplets with global ids for this rank's box and the rhs.  stencil: 27 (reference) or 7. */
+HYPRE_Int b200hypre_generate_laplace(HYPRE_Int nx, HYPRE_Int ny, HYPRE_Int nz, HYPRE_Int px, HYPRE_Int py, HYPRE_Int pz,
+                                     HYPRE_Int rank, HYPRE_Int stencil, HYPRE_BigInt **rows, HYPRE_BigInt **cols,
+                                     HYPRE_Complex **vals, HYPRE_Complex **rhs, HYPRE_BigInt *nnz, HYPRE_BigInt *n_local,
+                                     HYPRE_BigInt *row_start, HYPRE_BigInt *global_rows);
+void b200hypre_block_partition(HYPRE_BigInt n, HYPRE_Int nranks, HYPRE_BigInt *starts /* nranks + 1 */);  /* HypreSystem.cpp:525-544; host only */
+/* receive side of the halo plan for sorted halo column ids; returns the number of neighbours; host only */
+HYPRE_Int b200hypre_plan_recv(const HYPRE_BigInt *col_map, HYPRE_Int n_halo, const HYPRE_BigInt *col_starts, HYPRE_Int nranks,
+                              HYPRE_Int *recv_rank /* cap nranks */, HYPRE_Int *recv_off /* cap nranks + 1 */);
+
+/* ---- matrix / hierarchy inspection ------------------------------------------------------------------------------------------
+ * which: 'A' level operator, 'P' interpolation, 'R' restriction (stored transpose), 'S' strength pattern (no values).
+ * sizes[0] = local rows, sizes[1] = global columns, sizes[2] = local nnz (diag + offd), sizes[3] = global rows.
+ * get: rows in local order; every row lists its diag-block entries then its offd-block entries, columns as GLOBAL ids. */
+HYPRE_Int b200hypre_parcsr_sizes(HYPRE_ParCSRMatrix A, HYPRE_BigInt *sizes);
+HYPRE_Int b200hypre_parcsr_get(HYPRE_ParCSRMatrix A, HYPRE_Int *ptr, HYPRE_BigInt *col, HYPRE_Complex *val);
+HYPRE_Int b200hypre_amg_num_levels(HYPRE_Solver amg);
+HYPRE_Int b200hypre_amg_level_sizes(HYPRE_Solver amg, HYPRE_Int level, HYPRE_Int which, HYPRE_BigInt *sizes);
+HYPRE_Int b200hypre_amg_level_get(HYPRE_Solver amg, HYPRE_Int level, HYPRE_Int which, HYPRE_Int *ptr, HYPRE_BigInt *col, HYPRE_Complex *val);
+HYPRE_Int b200hypre_amg_level_cf(HYPRE_Solver amg, HYPRE_Int level, HYPRE_Int *cf);              /* +1 C, -1 F, -3 isolated */
+HYPRE_Int b200hypre_amg_level_smoother(HYPRE_Solver amg, HYPRE_Int level, HYPRE_Complex *d);     /* l1 norms / a_ii / D^-1/2 */
+HYPRE_Int b200hypre_amg_level_cheby(HYPRE_Solver amg, HYPRE_Int level, HYPRE_Real *out6);        /* max, min, c0..c3 */
+HYPRE_Real b200hypre_amg_setup_seconds(HYPRE_Solver amg);
+HYPRE_Int b200hypre_amg_setup_phases(HYPRE_Solver amg, char *names, HYPRE_Int names_cap, HYPRE_Real *ms, HYPRE_Int cap); /* ';'-joined names */
+/* one relaxation sweep of the level's smoother: u <- relax(u, f) (device pointers of the level's local length) */
+HYPRE_Int b200hypre_amg_relax(HYPRE_Solver amg, HYPRE_Int level, HYPRE_Complex *u, const HYPRE_Complex *f);
+HYPRE_Int b200hypre_amg_vcycle(HYPRE_Solver amg, const HYPRE_Complex *r, HYPRE_Complex *z);      /* z = M^-1 r, device pointers */
+
+/* ---- GMRES extras ---------------------------------------------------------------------------------------------------------- */
+HYPRE_Int b200hypre_gmres_set_orthogonalization(HYPRE_Solver gmres, HYPRE_Int kind);   /* 0 = MGS (hypre), 1 = fused CGS2 (default) */
+HYPRE_Int b200hypre_gmres_get_history(HYPRE_Solver gmres, HYPRE_Real *out, HYPRE_Int cap);   /* returns the history length */
+HYPRE_Real b200hypre_gmres_solve_seconds(HYPRE_Solver gmres);
+
+/* ---- instrumentation ------------------------------------------------------------------------------------------------------- */
+unsigned long long b200hypre_launch_count(void);   /* kernels launched by the library so far */
+void *b200hypre_stream(void);                      /* cudaStream_t every kernel of the library is launched on */
+HYPRE_Int b200hypre_device_synchronize(void);
+void *b200hypre_vector_data(HYPRE_ParVector v);    /* device pointer of the local part */
+HYPRE_Int b200hypre_vector_local_size(HYPRE_ParVector v);
+const char *b200hypre_spmv_kernel_name(HYPRE_ParCSRMatrix A);   /* "sell32" or "csr_vec<G>" chosen for the diag block */
+
+/* ---- test hooks: building blocks on host CSR arrays (int32 indices), results returned in malloc'ed host arrays that the
+ * caller releases with b200hypre_host_free ---------------------------------------------------------------------------------- */
+HYPRE_Int b200hypre_test_spgemm(HYPRE_Int a_nr, HYPRE_Int a_nc, const HYPRE_Int *a_ptr, const HYPRE_Int *a_col, const HYPRE_Complex *a_val,
+                                HYPRE_Int b_nc, const HYPRE_Int *b_ptr, const HYPRE_Int *b_col, const HYPRE_Complex *b_val,
+                                HYPRE_Int diag_first, HYPRE_Int **c_ptr, HYPRE_Int **c_col, HYPRE_Complex **c_val);
+HYPRE_Int b200hypre_test_transpose(HYPRE_Int nr, HYPRE_Int nc, const HYPRE_Int *ptr, const HYPRE_Int *col, const HYPRE_Complex *val,
+                                   HYPRE_Int **t_ptr, HYPRE_Int **t_col, HYPRE_Complex **t_val);
+HYPRE_Int b200hypre_test_rand(HYPRE_Int seed, HYPRE_Int n, HYPRE_Real *out);   /* device evaluation of the jumpable hypre_Rand stream */
+void b200hypre_host_free(void *p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

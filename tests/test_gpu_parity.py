@@ -1,0 +1,247 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on the same inputs.
+
+Bars (BASELINE.json north_star): hierarchy (CF splitting, P / R / A_c patterns, level sizes) bit-exact; operator
+values and solutions within 1e-10 relative; iteration counts within +-1; final relative residual <= the oracle's
+(up to the last-digit noise of a converged solve)."""
+import numpy as np
+import pytest
+
+from oracle_lib import Oracle, rand_stream
+
+pytestmark = pytest.mark.gpu
+
+VAL_RTOL = 1e-10  # north_star: operator values and solutions within 1e-10 relative
+
+
+def make_system(b200, n, stencil, **amg):
+    settings = {
+        "linear_system": {"type": "build_27pt_stencil" if stencil == 27 else "build_7pt_stencil", "nx": n, "ny": n, "nz": n},
+        "solver_settings": {"method": "gmres", "preconditioner": "boomeramg", "tolerance": 1e-8, "kspace": 50, "max_iterations": 200},
+        "boomeramg_settings": amg,
+    }
+    s = b200.HypreSystem(settings)
+    s.setup_precon_and_solver()
+    s.load()
+    return s
+
+
+def make_oracle(n, stencil, **opts):
+    o = Oracle(**opts)
+    o.threads(8)
+    o.gen_laplace(n, stencil=stencil)
+    return o
+
+
+def assert_same_csr(got, ref, what, values=True):
+    gptr, gcol, gval = got
+    rptr, rcol, rval = ref[0], ref[1], ref[2]
+    assert np.array_equal(gptr, rptr), f"{what}: row pointers differ"
+    assert np.array_equal(gcol, rcol.astype(np.int64)), f"{what}: column pattern / entry order differs"
+    if values and rval is not None:
+        scale = np.abs(rval).max() if len(rval) else 1.0
+        err = np.abs(gval - rval).max() / scale if len(rval) else 0.0
+        assert err <= VAL_RTOL, f"{what}: values differ by {err:.3e} relative"
+
+
+@pytest.mark.parametrize("n,stencil,theta", [(16, 7, 0.25), (24, 7, 0.25), (12, 27, 0.25), (16, 27, 0.57)])
+def test_hierarchy_bit_exact(b200, n, stencil, theta):
+    s = make_system(b200, n, stencil, strong_threshold=theta)
+    s.solve()
+    o = make_oracle(n, stencil, strong_threshold=theta)
+    o.setup()
+    amg = s.precond
+    assert amg.num_levels == o.num_levels
+    for l in range(o.num_levels):
+        assert_same_csr(amg.level_matrix(l, "A"), o.matrix(l, "A"), f"A[{l}]")
+        if l + 1 < o.num_levels:
+            assert np.array_equal(amg.level_cf(l), o.cf(l)), f"CF[{l}] differs"
+            assert_same_csr(amg.level_matrix(l, "S"), o.matrix(l, "S"), f"S[{l}]", values=False)
+            assert_same_csr(amg.level_matrix(l, "P"), o.matrix(l, "P"), f"P[{l}]")
+            assert_same_csr(amg.level_matrix(l, "R"), o.matrix(l, "R"), f"R[{l}]")
+        np.testing.assert_allclose(amg.level_smoother(l), o.smoother(l), rtol=1e-13)
+    s.destroy_system()
+
+
+@pytest.mark.parametrize("n,stencil,relax,order", [(24, 7, 18, 0), (24, 7, 18, 1), (24, 7, 7, 0), (16, 27, 18, 0), (24, 7, 16, 0)])
+def test_solve_parity(b200, n, stencil, relax, order):
+    s = make_system(b200, n, stencil, relax_type=relax, relax_order=order)
+    s.solver.destroy()
+    s.solver = b200.GMRES(tolerance=1e-8, max_iterations=200, kspace=50, orthogonalization="mgs")
+    s.solve()
+    o = make_oracle(n, stencil, relax_type=relax, relax_order=order)
+    o.setup()
+    xo = o.solve()
+    x = s.solution()
+    assert abs(s.solver.iterations - o.iterations) <= 1
+    assert s.solver.converged == 1
+    assert s.solver.relres <= max(o.relres * (1 + 1e-6), 1e-8)
+    # generator known answer (laplace_3d_weak_scaling.hpp:321): x == 1
+    assert np.abs(x - 1.0).max() < 1e-6
+    if s.solver.iterations == o.iterations:
+        assert np.abs(x - xo).max() / np.abs(xo).max() <= 1e-9
+        ho, hg = o.history(), s.solver.history()
+        np.testing.assert_allclose(hg, ho, rtol=1e-6)
+    s.destroy_system()
+
+
+def test_cgs2_matches_mgs_iterations(b200):
+    its = {}
+    for orth in ("mgs", "cgs2"):
+        s = make_system(b200, 24, 7)
+        s.solver.destroy()
+        s.solver = b200.GMRES(tolerance=1e-8, max_iterations=200, kspace=50, orthogonalization=orth)
+        s.solve()
+        its[orth] = s.solver.iterations
+        assert np.abs(s.solution() - 1.0).max() < 1e-6
+        s.destroy_system()
+    assert abs(its["mgs"] - its["cgs2"]) <= 1
+
+
+def test_vcycle_matches_oracle(b200):
+    import torch
+    n = 20
+    s = make_system(b200, n, 7)
+    s.solve()
+    o = make_oracle(n, 7)
+    o.setup()
+    rng = np.random.default_rng(7)
+    r = rng.standard_normal(n ** 3)
+    zo = o.vcycle(r)
+    rd = torch.tensor(r, device="cuda")
+    zd = torch.zeros_like(rd)
+    torch.cuda.synchronize()
+    s.precond.vcycle_ptr(rd.data_ptr(), zd.data_ptr())
+    b200.synchronize()
+    z = zd.cpu().numpy()
+    assert np.abs(z - zo).max() / np.abs(zo).max() <= VAL_RTOL
+    s.destroy_system()
+
+
+def test_spmv_matches_oracle_and_scipy(b200):
+    import scipy.sparse as sp
+    for n, stencil in ((32, 7), (20, 27)):
+        s = make_system(b200, n, stencil)
+        s.assemble_system()
+        o = make_oracle(n, stencil)
+        A = o.scipy(0, "A")
+        rng = np.random.default_rng(3)
+        x = rng.standard_normal(n ** 3)
+        s.x.set_values(x)
+        y = b200.IJVector(0, n ** 3 - 1)
+        b200.matvec(s.A, s.x, y)
+        got = y.get_values()
+        ref = A @ x
+        assert np.abs(got - ref).max() / np.abs(ref).max() <= 1e-13
+        # rhs = row sums (generator)
+        np.testing.assert_allclose(s.b.get_values(), o.rhs(), rtol=0, atol=0)
+        y.destroy()
+        s.destroy_system()
+
+
+def test_ij_assembly_unsorted_duplicates(b200):
+    """Set overwrites, AddTo accumulates, any entry order; result is ParCSR order (diagonal first, then ascending)"""
+    import scipy.sparse as sp
+    rng = np.random.default_rng(11)
+    n = 500
+    M = sp.random(n, n, density=0.02, random_state=5, format="coo") + sp.eye(n) * 4
+    M = M.tocoo()
+    perm = rng.permutation(M.nnz)
+    A = b200.IJMatrix(0, n - 1)
+    A.set_values(M.row[perm], M.col[perm], M.data[perm] + 100.0)   # first value, overwritten below
+    A.set_values(M.row[perm], M.col[perm], M.data[perm])           # Set overwrites
+    A.set_values(M.row[:50], M.col[:50], np.ones(50), add=True)      # AddTo accumulates
+    A.assemble()
+    ptr, col, val, _ = A.to_csr()
+    got = sp.csr_matrix((val, col, ptr), shape=(n, n))
+    ref = M.tocsr().copy()
+    ref = ref + sp.coo_matrix((np.ones(50), (M.row[:50], M.col[:50])), shape=(n, n)).tocsr()
+    assert abs(got - ref).max() < 1e-14
+    for i in range(n):   # diagonal first, remaining columns ascending
+        c = col[ptr[i]:ptr[i + 1]]
+        assert c[0] == i and np.all(np.diff(c[1:]) > 0)
+    A.destroy()
+
+
+def test_spgemm_and_transpose_blocks(b200):
+    import ctypes as C
+    import scipy.sparse as sp
+    L = b200.lib()
+    rng = np.random.default_rng(1)
+    for (m, k, n, dens) in ((300, 200, 250, 0.05), (64, 64, 64, 0.5), (2000, 2000, 2000, 0.004)):
+        A = sp.random(m, k, density=dens, random_state=1, format="csr")
+        B = sp.random(k, n, density=dens, random_state=2, format="csr")
+        A.sort_indices(); B.sort_indices()
+        cp, cc, cv = C.POINTER(C.c_int)(), C.POINTER(C.c_int)(), C.POINTER(C.c_double)()
+        ap, ac, av = A.indptr.astype(np.int32), A.indices.astype(np.int32), A.data.astype(np.float64)
+        bp, bc, bv = B.indptr.astype(np.int32), B.indices.astype(np.int32), B.data.astype(np.float64)
+        rc = L.b200hypre_test_spgemm(m, k, ap.ctypes, ac.ctypes, av.ctypes, n, bp.ctypes, bc.ctypes, bv.ctypes, 0,
+                                     C.byref(cp), C.byref(cc), C.byref(cv))
+        assert rc == 0
+        ptr = np.ctypeslib.as_array(cp, (m + 1,)).copy()
+        nnz = ptr[-1]
+        col = np.ctypeslib.as_array(cc, (max(nnz, 1),))[:nnz].copy()
+        val = np.ctypeslib.as_array(cv, (max(nnz, 1),))[:nnz].copy()
+        for p in (cp, cc, cv):
+            L.b200hypre_host_free(p)
+        got = sp.csr_matrix((val, col, ptr), shape=(m, n))
+        ref = (A @ B).tocsr()
+        ref.sort_indices()
+        assert np.array_equal(ptr, ref.indptr)
+        assert np.array_equal(col, ref.indices)          # ascending columns
+        assert abs(got - ref).max() <= 1e-13 * max(1.0, abs(ref).max())
+        # transpose: stable (ascending source row inside every output row)
+        tp, tc, tv = C.POINTER(C.c_int)(), C.POINTER(C.c_int)(), C.POINTER(C.c_double)()
+        rc = L.b200hypre_test_transpose(m, k, ap.ctypes, ac.ctypes, av.ctypes, C.byref(tp), C.byref(tc), C.byref(tv))
+        assert rc == 0
+        T = A.T.tocsr(); T.sort_indices()
+        assert np.array_equal(np.ctypeslib.as_array(tp, (k + 1,)), T.indptr)
+        assert np.array_equal(np.ctypeslib.as_array(tc, (max(A.nnz, 1),))[:A.nnz], T.indices)
+        assert np.array_equal(np.ctypeslib.as_array(tv, (max(A.nnz, 1),))[:A.nnz], T.data)
+        for p in (tp, tc, tv):
+            L.b200hypre_host_free(p)
+
+
+def test_device_rand_stream_matches_hypre_rand(b200):
+    for seed in (2747, 2748, 1, 5):
+        n = 5000
+        out = np.zeros(n)
+        assert b200.lib().b200hypre_test_rand(seed, n, out.ctypes) == 0
+        assert np.array_equal(out, rand_stream(seed, n))
+
+
+def test_no_precond_gmres_matches_scipy(b200):
+    import scipy.sparse.linalg as spla
+    n = 12
+    settings = {
+        "linear_system": {"type": "build_7pt_stencil", "nx": n, "ny": n, "nz": n},
+        "solver_settings": {"method": "gmres", "preconditioner": "none", "tolerance": 1e-10, "kspace": 60, "max_iterations": 400},
+    }
+    s = b200.HypreSystem(settings)
+    s.setup_precon_and_solver()
+    s.load()
+    s.solve()
+    o = make_oracle(n, 7)
+    A = o.scipy(0, "A")
+    xref = spla.spsolve(A.tocsc(), o.rhs())
+    assert np.abs(s.solution() - xref).max() / np.abs(xref).max() < 1e-8
+    s.destroy_system()
+
+
+@pytest.mark.parametrize("n,stencil", [(96, 7), (64, 27)])
+def test_larger_size_properties(b200, n, stencil):
+    """size-independent properties at a size the oracle does not need to run: x == 1, residual check, level sizes shrink"""
+    s = make_system(b200, n, stencil)
+    s.solve()
+    x = s.solution()
+    assert s.solver.converged == 1 and s.solver.relres <= 1e-8
+    assert np.abs(x - 1.0).max() < 1e-6
+    sizes = [int(s.precond.level_sizes(l, "A")[3]) for l in range(s.precond.num_levels)]
+    assert all(a > b for a, b in zip(sizes, sizes[1:]))
+    assert sizes[-1] <= 2048
+    # independent residual through the public matvec
+    r = b200.IJVector(0, n ** 3 - 1)
+    b200.matvec(s.A, s.x, r)
+    res = s.b.get_values() - r.get_values()
+    assert np.linalg.norm(res) / np.linalg.norm(s.b.get_values()) <= 1.01e-8
+    r.destroy()
+    s.destroy_system()
