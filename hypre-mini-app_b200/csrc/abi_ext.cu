@@ -245,6 +245,24 @@ HYPRE_Real b200hypre_gmres_solve_seconds(HYPRE_Solver gmres) {
   try { return as_gmres(gmres)->g.solve_seconds; } catch (const std::exception &e) { set_error(HYPRE_ERROR_ARG, e.what()); return -1.0; }
 }
 unsigned long long b200hypre_launch_count(void) { return ctx().launches; }
+HYPRE_Int b200hypre_profile_enable(HYPRE_Int on, double min_bytes) {
+  API_BEGIN ensure_init(); prof_enable(on != 0, min_bytes); API_END
+}
+HYPRE_Int b200hypre_profile_summary(char *names, HYPRE_Int names_cap, double *ms, double *calls, double *bytes, HYPRE_Int cap) {
+  int n = 0;
+  try {
+    std::vector<std::string> nm;
+    std::vector<double> t, c, b;
+    n = prof_summary(nm, t, c, b);
+    std::string joined;
+    for (int k = 0; k < n; ++k) {
+      if (k < cap) { if (ms) ms[k] = t[k]; if (calls) calls[k] = c[k]; if (bytes) bytes[k] = b[k]; }
+      joined += (k ? ";" : "") + nm[k];
+    }
+    if (names && names_cap > 0) { strncpy(names, joined.c_str(), names_cap - 1); names[names_cap - 1] = 0; }
+  } catch (const std::exception &e) { set_error(HYPRE_ERROR_GENERIC, e.what()); return 0; }
+  return n;
+}
 void *b200hypre_stream(void) {
   try { ensure_init(); } catch (const std::exception &e) { set_error(HYPRE_ERROR_GENERIC, e.what()); return nullptr; }
   return (void *)stream();

@@ -322,7 +322,7 @@ __global__ void k_spgemm_smem(rows::Csr A, rows::Csr B, const int *row_list, int
   int *keys = (int *)(base + 8 + (NUMERIC ? (size_t)H * 16 : 0));
   int *lk = keys + H;
   unsigned mask = 0xffffffffu;
-  if (G < 32) mask = ((1u << G) - 1u) << ((threadIdx.x & 31) / G * G);
+  if constexpr (G < 32) mask = ((1u << G) - 1u) << ((threadIdx.x & 31) / G * G);
   int idx = blockIdx.x * groups + g;
   if (G > 32) {  // block per row: every thread must take part in __syncthreads
     if (idx >= nrows) return;  // uniform for the whole block (groups == 1)

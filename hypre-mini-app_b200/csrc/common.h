@@ -44,6 +44,17 @@ void ensure_init();
 inline cudaStream_t stream() { return ctx().stream; }
 inline void count_launch(int n = 1) { ctx().launches += n; }
 
+// ---- kernel-class profiler: CUDA-event pairs on stream() around the large kernels, summed per class name.  Enabled by
+// b200hypre_profile_enable (bench.py's roofline leg); a scope is recorded only when its algorithmic byte count is at
+// least the configured minimum and the stream is not being captured into a graph.
+struct ProfScope {
+  int slot = -1;
+  ProfScope(const char *cls, double algorithmic_bytes);
+  ~ProfScope();
+};
+void prof_enable(bool on, double min_bytes);
+int prof_summary(std::vector<std::string> &names, std::vector<double> &ms, std::vector<double> &calls, std::vector<double> &bytes);
+
 // ---- stream-ordered device buffer --------------------------------------------------------------------------
 void *dev_alloc(size_t bytes);
 void dev_free(void *p);

@@ -66,6 +66,55 @@ void dev_free(void *p) {
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
+// kernel-class profiler
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+struct ProfRec { const char *cls; double bytes; cudaEvent_t e0, e1; };
+struct Profiler {
+  bool on = false;
+  double min_bytes = 0;
+  std::vector<ProfRec> recs;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pool;  // recycled event pairs
+} g_prof;
+}  // namespace
+
+void prof_enable(bool on, double min_bytes) {
+  for (ProfRec &r : g_prof.recs) g_prof.pool.emplace_back(r.e0, r.e1);
+  g_prof.recs.clear();
+  g_prof.on = on;
+  g_prof.min_bytes = min_bytes;
+}
+ProfScope::ProfScope(const char *cls, double bytes) {
+  if (!g_prof.on || bytes < g_prof.min_bytes || g_prof.recs.size() >= 65536) return;
+  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(stream(), &st) != cudaSuccess || st != cudaStreamCaptureStatusNone) { cudaGetLastError(); return; }
+  ProfRec r;
+  r.cls = cls;
+  r.bytes = bytes;
+  if (!g_prof.pool.empty()) { r.e0 = g_prof.pool.back().first; r.e1 = g_prof.pool.back().second; g_prof.pool.pop_back(); }
+  else { B200_CUDA(cudaEventCreate(&r.e0)); B200_CUDA(cudaEventCreate(&r.e1)); }
+  B200_CUDA(cudaEventRecord(r.e0, stream()));
+  slot = (int)g_prof.recs.size();
+  g_prof.recs.push_back(r);
+}
+ProfScope::~ProfScope() {
+  if (slot >= 0) cudaEventRecord(g_prof.recs[slot].e1, stream());
+}
+int prof_summary(std::vector<std::string> &names, std::vector<double> &ms, std::vector<double> &calls, std::vector<double> &bytes) {
+  names.clear(); ms.clear(); calls.clear(); bytes.clear();
+  if (ctx().initialised) B200_CUDA(cudaStreamSynchronize(stream()));
+  for (ProfRec &r : g_prof.recs) {
+    float t = 0;
+    if (cudaEventElapsedTime(&t, r.e0, r.e1) != cudaSuccess) { cudaGetLastError(); continue; }
+    size_t k = 0;
+    for (; k < names.size(); ++k) if (names[k] == r.cls) break;
+    if (k == names.size()) { names.push_back(r.cls); ms.push_back(0); calls.push_back(0); bytes.push_back(0); }
+    ms[k] += t; calls[k] += 1; bytes[k] += r.bytes;
+  }
+  return (int)names.size();
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
 // NCCL through dlopen
 // ---------------------------------------------------------------------------------------------------------------------
 struct Id128 { char b[128]; };  // ncclUniqueId (passed by value to ncclCommInitRank)

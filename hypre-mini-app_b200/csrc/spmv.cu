@@ -226,9 +226,28 @@ void maybe_build_sell(const DCsr &A, DSell &S) {
   if (ok) build_sell(A, S);
 }
 
+// algorithmic bytes of one SpMV-class pass: 12 B/nnz + row pointer + y write + x read once, plus the
+// epilogue's extra vectors; the same figure for both layouts (SELL padding is not counted as useful traffic)
+static double spmv_bytes(const DCsr &A, SpmvMode mode, const SpmvArgs &a) {
+  double nr = A.nr, nc = A.nc, b = 12.0 * (double)A.nnz + 12.0 * nr + 8.0 * nc;
+  if (a.xs) b += 8.0 * nc;
+  switch (mode) {
+    case SPMV_AX: break;
+    case SPMV_RES: b += 8.0 * nr + (a.d ? 8.0 * nr : 0.0); break;
+    case SPMV_JAC: b += 16.0 * nr + (a.cf ? 4.0 * nr : 0.0); break;
+    case SPMV_ADD: b += 8.0 * nr; break;
+    case SPMV_CHEB: b += 16.0 * nr + (a.g ? 8.0 * nr : 0.0); break;
+  }
+  return b;
+}
+
 void spmv(const DCsr &A, const DSell *S, const SpmvPlan &plan, SpmvMode mode, const SpmvArgs &a) {
   if (A.nr == 0) return;
-  if (plan.use_sell && S && S->valid()) {
+  static const char *const cls_sell[5] = {"spmv_sell32_ax", "spmv_sell32_res", "spmv_sell32_jac", "spmv_sell32_add", "spmv_sell32_cheb"};
+  static const char *const cls_csr[5] = {"spmv_csrvec_ax", "spmv_csrvec_res", "spmv_csrvec_jac", "spmv_csrvec_add", "spmv_csrvec_cheb"};
+  const bool sell = plan.use_sell && S && S->valid();
+  ProfScope prof(sell ? cls_sell[mode] : cls_csr[mode], spmv_bytes(A, mode, a));
+  if (sell) {
     switch (mode) {
       case SPMV_AX: launch_sell<SPMV_AX>(*S, a); break;
       case SPMV_RES: launch_sell<SPMV_RES>(*S, a); break;

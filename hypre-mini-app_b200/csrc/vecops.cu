@@ -200,11 +200,13 @@ void vec_copy(double *dst, const double *src, i64 n) {
 }
 void vec_scale(double *x, double a, i64 n) {
   if (n <= 0) return;
+  ProfScope prof("scale", 16.0 * (double)n);
   k_scale<<<stream_grid(n), VB, 0, stream()>>>(x, a, n);
   count_launch();
 }
 void vec_axpy(double a, const double *x, double *y, i64 n) {
   if (n <= 0) return;
+  ProfScope prof("axpy", 24.0 * (double)n);
   k_axpy<<<stream_grid(n), VB, 0, stream()>>>(a, x, y, n);
   count_launch();
 }
@@ -215,6 +217,7 @@ void vec_axpby(double a, const double *x, double b, double *y, i64 n) {
 }
 void vec_pointwise_div(double *out, const double *f, const double *d, double w, const int *cf, int pt, i64 n) {
   if (n <= 0) return;
+  ProfScope prof("pointwise_div", 24.0 * (double)n);
   k_pdiv<<<stream_grid(n), VB, 0, stream()>>>(out, f, d, w, cf, pt, n);
   count_launch();
 }
@@ -229,6 +232,7 @@ void multi_dot(DotWork &w, const double *V, i64 ld, int k, const double *x, i64 
   int grid = stream_grid(n > 0 ? n : 1, 8);
   ensure_work(w, grid, 8);
   unsigned int *t = ticket_ptr();
+  ProfScope prof("multi_dot", 8.0 * (double)n * (k + (k + 7) / 8));
   for (int j0 = 0; j0 < k; j0 += 8) {
     int kv = (k - j0 < 8) ? (k - j0) : 8;
     const double *Vj = V + (i64)j0 * ld;
@@ -246,6 +250,7 @@ void multi_axpy_norm(DotWork &w, const double *V, i64 ld, int k, const double *h
   B200_REQUIRE((ld & 1) == 0 && ((uintptr_t)V & 15) == 0 && ((uintptr_t)x & 15) == 0, "multi_axpy_norm: unaligned vectors");
   int grid = stream_grid(n > 0 ? n : 1, 8);
   ensure_work(w, grid, 8);
+  ProfScope prof("multi_axpy_norm", 8.0 * (double)n * (k + 2));
   k_multi_axpy_norm<<<grid, VB, 0, stream()>>>(V, ld, k, h, x, n, w.partial.p, norm2_out, ticket_ptr());
   count_launch();
   B200_KERNEL_CHECK();
@@ -254,6 +259,7 @@ void multi_axpy_norm(DotWork &w, const double *V, i64 ld, int k, const double *h
 void lin_comb(double *out, const double *V, i64 ld, int k, const double *coef_dev, i64 n) {
   B200_REQUIRE(k <= 128, "lin_comb: k > 128");
   if (n <= 0) return;
+  ProfScope prof("lin_comb", 8.0 * (double)n * (k + 1));
   k_lin_comb<<<stream_grid(n), VB, 0, stream()>>>(out, V, ld, k, coef_dev, n);
   count_launch();
   B200_KERNEL_CHECK();

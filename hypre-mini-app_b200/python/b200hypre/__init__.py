@@ -144,6 +144,21 @@ def launch_count():
     return int(lib().b200hypre_launch_count())
 
 
+def profile_enable(on=True, min_bytes=0.0):
+    L = lib()
+    L.b200hypre_profile_enable.argtypes = [I32, F64]
+    check(L.b200hypre_profile_enable(1 if on else 0, float(min_bytes)), "profile_enable")
+
+
+def profile_summary():
+    """{class: (total_ms, calls, algorithmic_bytes)} of the scopes recorded since profile_enable"""
+    names = C.create_string_buffer(4096)
+    ms, calls, nbytes = np.zeros(64), np.zeros(64), np.zeros(64)
+    n = lib().b200hypre_profile_summary(names, 4096, _ptr(ms), _ptr(calls), _ptr(nbytes), 64)
+    keys = names.value.decode().split(";") if n else []
+    return {k: (float(ms[i]), int(calls[i]), float(nbytes[i])) for i, k in enumerate(keys)}
+
+
 def stream_ptr():
     return lib().b200hypre_stream()
 
@@ -222,6 +237,10 @@ class IJVector:
         out = np.zeros(self.n)
         check(lib().HYPRE_IJVectorGetValues(self.h, self.n, None, _ptr(out)), "IJVectorGetValues")
         return out
+
+    def get_values_ptr(self, out_ptr):
+        """all local values into a caller buffer (host, e.g. pinned, or device address)"""
+        check(lib().HYPRE_IJVectorGetValues(self.h, self.n, None, VP(out_ptr)), "IJVectorGetValues")
 
     def object(self):
         o = VP()

@@ -84,6 +84,8 @@ class HypreSystem:
             self._load_generator(ls, 27 if kind == "build_27pt_stencil" else 7)
         elif kind == "csr":
             self._load_csr(ls)
+        elif kind == "coo":
+            self._load_coo(ls)
         else:
             raise ValueError(f"linear_system type '{kind}': use the C++ hypre_app for file formats")
 
@@ -109,6 +111,18 @@ class HypreSystem:
         synchronize()
         coo.free()
         self._timer("Build 27Pt Stencil HYPRE matrix", t0)
+
+    def _load_coo(self, ls):
+        """COO triplets (global ids, one entry per 'row') + rhs given as raw HOST or DEVICE addresses: exactly what
+        hypre_matrix_set_values / hypre_vector_set_values hand to the IJ interface (HypreSystem.cpp:897-1015)"""
+        self.global_rows = ls["global_rows"]
+        self._init_system(ls["row_start"], ls["row_start"] + ls["n_local"] - 1)
+        t0 = time.perf_counter()
+        self.A.set_values_ptr(ls["nnz"], ls["rows"], ls["cols"], ls["vals"])
+        self._timer("Build HYPRE matrix", t0)
+        t0 = time.perf_counter()
+        self.b.set_values_ptr(ls["n_local"], 0, ls["rhs"])
+        self._timer("Build HYPRE vector", t0)
 
     def _load_csr(self, ls):
         """global CSR given as host arrays (tests): every rank keeps its block rows (HypreSystem.cpp:525-544)"""

@@ -57,6 +57,10 @@ HYPRE_Real b200hypre_gmres_solve_seconds(HYPRE_Solver gmres);
 
 /* ---- instrumentation ------------------------------------------------------------------------------------------------------- */
 unsigned long long b200hypre_launch_count(void);   /* kernels launched by the library so far */
+/* kernel-class timing with CUDA events on the library stream: scopes whose algorithmic byte count is >= min_bytes are
+ * recorded while enabled; summary returns ';'-joined class names with total ms, call count and algorithmic bytes */
+HYPRE_Int b200hypre_profile_enable(HYPRE_Int on, double min_bytes);
+HYPRE_Int b200hypre_profile_summary(char *names, HYPRE_Int names_cap, double *ms, double *calls, double *bytes, HYPRE_Int cap);
 void *b200hypre_stream(void);                      /* cudaStream_t every kernel of the library is launched on */
 HYPRE_Int b200hypre_device_synchronize(void);
 void *b200hypre_vector_data(HYPRE_ParVector v);    /* device pointer of the local part */
