@@ -141,6 +141,8 @@ void ij_vector_get(IJVector &v, i64 n, const i64 *idx, double *out);
 // ---- setup building blocks (amg_setup.cu), exposed for tests through include/b200hypre.h ----------------------------
 void csr_transpose(const DCsr &A, DCsr &T);
 void csr_spgemm(const DCsr &A, const DCsr &B, DCsr &C, bool diag_first);
+void build_interp(const DCsr &Aext, const int *Sptr, const int *Scol, i64 S_nnz, const int *cf, const int *f2c, int n_own, int n_rows,
+                  double tf, int pmax, DCsr &P);
 
 // ---- generator (generator.cu): laplace_3d_weak_scaling semantics --------------------------------------------------------
 // fills device COO (global ids) + rhs for this rank's box; returns nnz.  Arrays are allocated by the callee.

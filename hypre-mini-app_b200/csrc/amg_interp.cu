@@ -1,0 +1,413 @@
+// amg_interp.cu -- extended+i interpolation (interp_type 6) with truncation, one thread GROUP per row.
+// Replaces hypre_BoomerAMGBuildExtPIInterp + hypre_BoomerAMGInterpTruncation reached from HYPRE_BoomerAMGSetup
+// (/root/reference/src/HypreSystem.cpp:197,212,232 set the options, :323 via :692 runs it); formula and entry order:
+// SURVEY.md A.5.  hypre itself is not in /root/reference.
+//
+// The row function rows::interp_row (amg_rows.cuh) is the sequential definition: C-hat_i is discovered in the order
+// "strong neighbours of i in storage order, and for a strong F neighbour its strong C neighbours in storage order";
+// every weight is a sum whose terms arrive in (entry of row i, entry of the neighbour row) order.  The group kernel
+// below produces bit-identical rows with G lanes working on one row:
+//   * discovery: the outer loop over the strong neighbours stays sequential; the lanes run across the strength row of
+//     one F neighbour, membership is a shared-memory hash probe, and new C points take their list positions from a
+//     ballot prefix, i.e. in storage order;
+//   * weights: the loop over the entries of row i stays sequential; inside one entry the lanes run across the
+//     neighbour row, where every term goes to a different C-hat slot (columns of one row are distinct), so each slot
+//     still receives its terms in the sequential order and no floating-point atomics are needed.  The per-neighbour
+//     denominator is summed in storage order by walking the ballot mask of the contributing lanes;
+//   * truncation (trunc_factor, P_max_elmts with hypre's qsort2abs tie order) is done by the first lane on the
+//     shared-memory list.
+// Rows are tiered by |C-hat|: (G, list capacity) = (8, 32) when strength rows are short, then (32, 128); the few rows
+// beyond that run rows::interp_row itself with a global-memory scratch list.  Compiled with -fmad=false (the
+// operation order of every value that feeds a discrete decision is part of the parity contract).
+#include "amg.h"
+#include "amg_rows.cuh"
+#include <cub/cub.cuh>
+
+namespace b200 {
+
+namespace {
+
+template <int G>
+__device__ __forceinline__ unsigned group_mask() {
+  if (G >= 32) return 0xffffffffu;
+  return ((1u << (G & 31)) - 1u) << (((threadIdx.x & 31) / G) * G);
+}
+
+template <int H>
+__device__ __forceinline__ unsigned slot_of(int key) {
+  return (((unsigned)key * 2654435761u) >> 7) & (unsigned)(H - 1);
+}
+template <int H>
+__device__ __forceinline__ int h_probe(const int *keys, const short *spos, int key) {
+  unsigned h = slot_of<H>(key);
+  while (true) {
+    int k = keys[h];
+    if (k == key) return spos[h];
+    if (k == -1) return -1;
+    h = (h + 1) & (unsigned)(H - 1);
+  }
+}
+template <int H>
+__device__ __forceinline__ void h_insert(int *keys, short *spos, int key, int pos) {  // key is known to be absent
+  unsigned h = slot_of<H>(key);
+  while (true) {
+    int old = atomicCAS(keys + h, -1, key);
+    if (old == -1) { spos[h] = (short)pos; return; }
+    h = (h + 1) & (unsigned)(H - 1);
+  }
+}
+
+// lraw: |C-hat_i| before truncation; -1 = not computed yet (the row did not fit the tiers tried so far).
+// COUNT: rows with lraw == -1 are processed, lraw / len are written.  FILL: rows with lo < lraw <= CAP.
+template <int G, int H, int CAP, bool COUNT>
+__global__ void __launch_bounds__(256) k_interp_grp(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__ Scol,
+                                                    const int *__restrict__ cf, const int *__restrict__ f2c, int n_own, int n_rows,
+                                                    double tf, int pmax, int lo, int *lraw, int *len, const int *__restrict__ Pptr,
+                                                    int *Pcol, double *Pval) {
+  constexpr int GROUPS = 256 / G;
+  __shared__ int s_keys[GROUPS][H];
+  __shared__ short s_pos[GROUPS][H];
+  __shared__ int s_lc[GROUPS][CAP];
+  __shared__ double s_lv[GROUPS][CAP];
+  const int g = threadIdx.x / G, lane = threadIdx.x % G;
+  const int i = blockIdx.x * GROUPS + g;
+  if (i >= n_rows) return;
+  const unsigned gm = group_mask<G>();
+  const unsigned lane_lt = gm & ((1u << (threadIdx.x & 31)) - 1u);
+  const int first_lane = (threadIdx.x & 31) - lane;
+  if (COUNT) {
+    if (lraw[i] != -1) return;
+  } else {
+    int l = lraw[i];
+    if (!(l > lo && l <= CAP)) return;
+  }
+  const int cfi = cf[i];
+  if (cfi >= 0) {
+    if (lane == 0) {
+      if (COUNT) { lraw[i] = 0; len[i] = 1; }
+      else { int b = Pptr[i]; Pcol[b] = f2c[i]; Pval[b] = 1.0; }
+    }
+    return;
+  }
+  if (cfi == -3) {
+    if (COUNT && lane == 0) { lraw[i] = 0; len[i] = 0; }
+    return;
+  }
+  if (!COUNT && Pptr[i + 1] == Pptr[i]) return;
+  int *keys = s_keys[g];
+  short *spos = s_pos[g];
+  int *lc = s_lc[g];
+  double *lv = s_lv[g];
+  for (int s = lane; s < H; s += G) keys[s] = -1;
+  __syncwarp(gm);
+
+  // ---- discovery of C-hat_i ---------------------------------------------------------------------------------------
+  int L = 0;
+  bool any_off = false, ovf = false;
+  const int sb = Sptr[i], se = Sptr[i + 1];
+  for (int kk = sb; kk < se && !ovf; ++kk) {
+    const int i1 = Scol[kk];
+    const int c1 = cf[i1];
+    if (c1 >= 0) {
+      if (h_probe<H>(keys, spos, i1) < 0) {
+        if (L == CAP) { ovf = true; break; }
+        __syncwarp(gm);  // every lane has finished probing before the table changes
+        if (lane == 0) { h_insert<H>(keys, spos, i1, L); lc[L] = i1; }
+        any_off |= (i1 >= n_own);
+        ++L;
+        __syncwarp(gm);
+      }
+    } else if (c1 != -3) {
+      const int b2 = Sptr[i1], e2 = Sptr[i1 + 1];
+      for (int base = b2; base < e2; base += G) {
+        const int k2 = base + lane;
+        int k1 = -1;
+        bool isnew = false;
+        if (k2 < e2) {
+          k1 = Scol[k2];
+          if (cf[k1] >= 0) isnew = (h_probe<H>(keys, spos, k1) < 0);
+        }
+        const unsigned nm = __ballot_sync(gm, isnew) & gm;
+        const int cnt = __popc(nm);
+        if (cnt) {
+          if (L + cnt > CAP) { ovf = true; break; }
+          if (isnew) {
+            int pos = L + __popc(nm & lane_lt);
+            h_insert<H>(keys, spos, k1, pos);
+            lc[pos] = k1;
+          }
+          any_off |= ((__ballot_sync(gm, isnew && k1 >= n_own) & gm) != 0u);
+          L += cnt;
+          __syncwarp(gm);
+        }
+      }
+    }
+  }
+  if (ovf) return;  // lraw stays -1: the next tier takes the row
+  const bool full = !COUNT || tf != 0.0;
+  if (!full) {
+    if (lane == 0) { lraw[i] = L; len[i] = (pmax > 0 && L > pmax) ? pmax : L; }
+    return;
+  }
+  if (any_off) {  // stable partition: own-range C points first (P_diag before P_offd); positions change -> rebuild the table
+    int *tmp = reinterpret_cast<int *>(lv);
+    int nown = 0;
+    for (int base = 0; base < L; base += G) {
+      int k = base + lane;
+      bool own = (k < L) && (lc[k] < n_own);
+      nown += __popc(__ballot_sync(gm, own) & gm);
+    }
+    int co = 0, cx = 0;
+    for (int base = 0; base < L; base += G) {
+      int k = base + lane;
+      bool valid = k < L;
+      int v = valid ? lc[k] : 0;
+      bool own = valid && v < n_own, off = valid && !own;
+      unsigned mo = __ballot_sync(gm, own) & gm, mx = __ballot_sync(gm, off) & gm;
+      if (own) tmp[co + __popc(mo & lane_lt)] = v;
+      if (off) tmp[nown + cx + __popc(mx & lane_lt)] = v;
+      co += __popc(mo);
+      cx += __popc(mx);
+    }
+    __syncwarp(gm);
+    for (int s = lane; s < H; s += G) keys[s] = -1;
+    __syncwarp(gm);
+    for (int k = lane; k < L; k += G) { int v = tmp[k]; lc[k] = v; }
+    __syncwarp(gm);
+    for (int k = lane; k < L; k += G) h_insert<H>(keys, spos, lc[k], k);
+    __syncwarp(gm);
+  }
+
+  // ---- weights --------------------------------------------------------------------------------------------------------
+  for (int k = lane; k < L; k += G) lv[k] = 0.0;
+  __syncwarp(gm);
+  const int ab = A.ptr[i], ae = A.ptr[i + 1];
+  double diagonal = A.val[ab];
+  int sp = sb;
+  for (int jj = ab + 1; jj < ae; ++jj) {
+    const int i1 = A.col[jj];
+    const double aij = A.val[jj];
+    const bool strong = (sp < se) && (Scol[sp] == i1);
+    if (strong) ++sp;
+    const int pos = h_probe<H>(keys, spos, i1);
+    if (pos >= 0) {
+      if (lane == 0) lv[pos] = lv[pos] + aij;
+      __syncwarp(gm);
+      continue;
+    }
+    const int c1 = cf[i1];
+    if (strong && c1 < 0 && c1 != -3) {
+      const int b1 = A.ptr[i1], e1 = A.ptr[i1 + 1];
+      const double sgn = (A.val[b1] < 0) ? -1.0 : 1.0;
+      double sum = 0.0;
+      for (int base = b1 + 1; base < e1; base += G) {
+        const int j1 = base + lane;
+        bool m = false;
+        double a = 0.0;
+        if (j1 < e1) {
+          a = A.val[j1];
+          if ((sgn * a) < 0) {
+            int i2 = A.col[j1];
+            m = (i2 == i) || (h_probe<H>(keys, spos, i2) >= 0);
+          }
+        }
+        unsigned mm = __ballot_sync(gm, m) & gm;
+        while (mm) {  // storage-order sum of the contributing entries
+          int src = __ffs(mm) - 1;
+          mm &= mm - 1;
+          sum = sum + __shfl_sync(gm, a, src);
+        }
+      }
+      if (sum != 0.0) {
+        const double distribute = aij / sum;
+        for (int base = b1 + 1; base < e1; base += G) {
+          const int j1 = base + lane;
+          bool is_i = false;
+          double t = 0.0;
+          if (j1 < e1) {
+            double a = A.val[j1];
+            if ((sgn * a) < 0) {
+              int i2 = A.col[j1];
+              t = distribute * a;
+              int p2 = h_probe<H>(keys, spos, i2);
+              if (p2 >= 0) lv[p2] = lv[p2] + t;
+              is_i = (i2 == i);
+            }
+          }
+          unsigned mi = __ballot_sync(gm, is_i) & gm;
+          if (mi) diagonal = diagonal + __shfl_sync(gm, t, __ffs(mi) - 1);
+        }
+      } else {
+        diagonal = diagonal + aij;
+      }
+      __syncwarp(gm);
+    } else if (c1 != -3) {
+      diagonal = diagonal + aij;
+    }
+  }
+  __syncwarp(gm);
+  if (diagonal != 0.0) {
+    const double md = -diagonal;
+    for (int k = lane; k < L; k += G) lv[k] = lv[k] / md;
+  }
+  __syncwarp(gm);
+
+  // ---- truncation (sequential on the first lane: the sums and the sort are order dependent) -----------------------------
+  int n_out = L;
+  if (lane == 0) {
+    if (tf > 0.0 && n_out > 0) {
+      double max_coef = 0.0, row_sum = 0.0, scale = 0.0;
+      for (int k = 0; k < n_out; ++k) { double a = fabs(lv[k]); max_coef = (a > max_coef) ? a : max_coef; }
+      max_coef = max_coef * tf;
+      int w = 0;
+      for (int k = 0; k < n_out; ++k) {
+        row_sum = row_sum + lv[k];
+        if (fabs(lv[k]) >= max_coef) { scale = scale + lv[k]; lc[w] = lc[k]; lv[w] = lv[k]; ++w; }
+      }
+      n_out = w;
+      if (scale != 0.0 && scale != row_sum) {
+        double f = row_sum / scale;
+        for (int k = 0; k < n_out; ++k) lv[k] = lv[k] * f;
+      }
+    }
+    if (pmax > 0 && n_out > pmax) {
+      double row_sum = 0.0, scale = 0.0;
+      for (int k = 0; k < n_out; ++k) row_sum = row_sum + lv[k];
+      rows::qsort2abs(lc, lv, n_out);
+      for (int k = 0; k < pmax; ++k) scale = scale + lv[k];
+      n_out = pmax;
+      if (scale != 0.0 && scale != row_sum) {
+        double f = row_sum / scale;
+        for (int k = 0; k < n_out; ++k) lv[k] = lv[k] * f;
+      }
+      if (any_off) {  // re-split, each part keeping the sorted order
+        for (int k = 1; k < n_out; ++k) {
+          int v = lc[k];
+          double x = lv[k];
+          if (v < n_own) {
+            int p = k;
+            while (p > 0 && lc[p - 1] >= n_own) { lc[p] = lc[p - 1]; lv[p] = lv[p - 1]; --p; }
+            lc[p] = v;
+            lv[p] = x;
+          }
+        }
+      }
+    }
+  }
+  __syncwarp(gm);
+  n_out = __shfl_sync(gm, n_out, first_lane);
+  if (COUNT) {
+    if (lane == 0) { lraw[i] = L; len[i] = n_out; }
+    return;
+  }
+  const int b = Pptr[i];
+  for (int k = lane; k < n_out; k += G) {
+    Pcol[b + k] = f2c[lc[k]];
+    Pval[b + k] = lv[k];
+  }
+}
+
+// rows that did not fit any tier: the sequential row function with a global-memory scratch list of `cap` entries per row
+__global__ void k_interp_ovf(rows::Csr A, const int *Sptr, const int *Scol, const int *cf, const int *f2c, int n_own, double tf,
+                             int pmax, const int *rows_list, int nrows, int *sc, double *sv, int cap, int *len, const int *Pptr,
+                             int *Pcol, double *Pval, int *err) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nrows) return;
+  int i = rows_list[t];
+  int *lc = sc + (size_t)t * cap;
+  double *lv = sv + (size_t)t * cap;
+  if (Pptr == nullptr) {
+    int L = rows::interp_row(A, Sptr, Scol, cf, f2c, n_own, i, tf, pmax, tf == 0.0, lc, lv, lc, lv, cap);
+    if (L < 0) { *err = 1; L = 0; }
+    len[i] = L;
+  } else {
+    int b = Pptr[i];
+    if (Pptr[i + 1] > b) rows::interp_row(A, Sptr, Scol, cf, f2c, n_own, i, tf, pmax, false, Pcol + b, Pval + b, lc, lv, cap);
+  }
+}
+__global__ void k_collect_todo(int n, const int *lraw, int *count, int *list, int cap) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && lraw[i] == -1) {
+    int p = atomicAdd(count, 1);
+    if (p < cap) list[p] = i;
+  }
+}
+
+template <class T>
+T fetch1(const T *dev) {
+  T h;
+  B200_CUDA(cudaMemcpyAsync(&h, dev, sizeof(T), cudaMemcpyDeviceToHost, stream()));
+  B200_CUDA(cudaStreamSynchronize(stream()));
+  return h;
+}
+
+template <bool COUNT>
+void launch_tiers(bool small_tier, const rows::Csr &A, const int *Sptr, const int *Scol, const int *cf, const int *f2c, int n_own,
+                  int n_rows, double tf, int pmax, int *lraw, int *len, const int *Pptr, int *Pcol, double *Pval) {
+  int lo = -1;
+  if (small_tier) {
+    k_interp_grp<8, 64, 32, COUNT><<<div_up(n_rows, 32), 256, 0, stream()>>>(A, Sptr, Scol, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw,
+                                                                           len, Pptr, Pcol, Pval);
+    count_launch();
+    lo = 32;
+  }
+  k_interp_grp<32, 256, 128, COUNT><<<div_up(n_rows, 8), 256, 0, stream()>>>(A, Sptr, Scol, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw,
+                                                                            len, Pptr, Pcol, Pval);
+  count_launch();
+  B200_KERNEL_CHECK();
+}
+
+}  // namespace
+
+// Interpolation rows [0, n_rows) of the (extended) level: A, S, cf, f2c are indexed by extended fine ids, ids below
+// n_own are this rank's own points; f2c gives the output column of a C point.  P.nc must be set by the caller.
+void build_interp(const DCsr &Aext, const int *Sptr, const int *Scol, i64 S_nnz, const int *cf, const int *f2c, int n_own, int n_rows,
+                  double tf, int pmax, DCsr &P) {
+  rows::Csr A{Aext.nr, Aext.nc, Aext.ptr.p, Aext.col.p, Aext.val.p};
+  P.nr = n_rows;
+  P.ptr.alloc((size_t)n_rows + 1);
+  if (n_rows == 0) { P.nnz = 0; P.ptr.zero(); return; }
+  const bool small_tier = (double)S_nnz <= 8.0 * (double)Aext.nr;
+  DVec<int> lraw((size_t)n_rows), len((size_t)n_rows + 1);
+  B200_CUDA(cudaMemsetAsync(lraw.p, 0xFF, sizeof(int) * (size_t)n_rows, stream()));
+  B200_CUDA(cudaMemsetAsync(len.p + n_rows, 0, sizeof(int), stream()));
+  launch_tiers<true>(small_tier, A, Sptr, Scol, cf, f2c, n_own, n_rows, tf, pmax, lraw.p, len.p, nullptr, nullptr, nullptr);
+  // rows beyond the last tier
+  DVec<int> todo_count(1), todo((size_t)65536), err(1);
+  todo_count.zero();
+  err.zero();
+  k_collect_todo<<<div_up(n_rows, 256), 256, 0, stream()>>>(n_rows, lraw.p, todo_count.p, todo.p, 65536);
+  count_launch();
+  int novf = fetch1(todo_count.p);
+  B200_REQUIRE(novf <= 65536, "interpolation: too many rows exceed the shared-memory C-hat capacity");
+  const int ocap = 4096;
+  DVec<int> sc;
+  DVec<double> sv;
+  if (novf > 0) {
+    sc.alloc((size_t)novf * ocap);
+    sv.alloc((size_t)novf * ocap);
+    k_interp_ovf<<<div_up(novf, 64), 64, 0, stream()>>>(A, Sptr, Scol, cf, f2c, n_own, tf, pmax, todo.p, novf, sc.p, sv.p, ocap, len.p,
+                                                        nullptr, nullptr, nullptr, err.p);
+    count_launch();
+    B200_REQUIRE(fetch1(err.p) == 0, "interpolation: C-hat larger than 4096 entries");
+  }
+  {
+    size_t tb = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tb, len.p, P.ptr.p, n_rows + 1, stream());
+    DVec<char> tmp(tb);
+    cub::DeviceScan::ExclusiveSum(tmp.p, tb, len.p, P.ptr.p, n_rows + 1, stream());
+    count_launch(2);
+  }
+  P.nnz = fetch1(P.ptr.p + n_rows);
+  P.col.alloc((size_t)std::max<i64>(P.nnz, 1));
+  P.val.alloc((size_t)std::max<i64>(P.nnz, 1));
+  launch_tiers<false>(small_tier, A, Sptr, Scol, cf, f2c, n_own, n_rows, tf, pmax, lraw.p, len.p, P.ptr.p, P.col.p, P.val.p);
+  if (novf > 0) {
+    k_interp_ovf<<<div_up(novf, 64), 64, 0, stream()>>>(A, Sptr, Scol, cf, f2c, n_own, tf, pmax, todo.p, novf, sc.p, sv.p, ocap, len.p,
+                                                        P.ptr.p, P.col.p, P.val.p, err.p);
+    count_launch();
+  }
+  B200_KERNEL_CHECK();
+}
+
+}  // namespace b200

@@ -7,14 +7,7 @@
 // Compiled with -fmad=false: the operation order of every value that feeds a discrete decision is part of the
 // parity contract with the CPU oracle.
 //
-// SpGEMM (csr_spgemm): Gustavson order.  A group of G threads owns one output row; the k loop over the row of A is
-// sequential, the lanes run across the entries of row k of B, each (k, j) product is added to the hash slot of
-// column j (no two lanes touch the same slot inside one k), so the sum for every output entry is accumulated in
-// exactly the order of the sequential algorithm -- bit-identical to the oracle, no floating-point atomics.
-// Pass 1 (symbolic) counts distinct columns per row with a shared-memory hash; pass 2 (numeric) accumulates, compacts
-// and writes the row in canonical order (diagonal first for square operators, then ascending column).  Rows are
-// binned by min(sum of B row lengths, #columns) (pass 1) / by exact nnz (pass 2) into shared-memory tables of 128,
-// 1024 and 8192/32768 slots; anything larger uses a global-memory table.
+// Interpolation lives in amg_interp.cu, transposition and the Galerkin SpGEMM in spgemm.cu.
 #include "amg.h"
 #include "amg_rows.cuh"
 #include <cub/cub.cuh>
@@ -124,54 +117,6 @@ __global__ void k_fold_sf(int n, const int *cf_raw, int *cf) {
   if (i < n) cf[i] = (cf_raw[i] == -3) ? -1 : cf_raw[i];
 }
 
-// ---- interpolation ------------------------------------------------------------------------------------------------
-constexpr int ICAP = 128;
-__global__ void __launch_bounds__(128) k_interp_count(rows::Csr A, const int *Sptr, const int *Scol, const int *cf, const int *f2c,
-                                                      int n_own, double tf, int pmax, int *len, int *ovf_count, int *ovf_rows) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i == A.nr) len[i] = 0;
-  if (i >= A.nr) return;
-  int lc[ICAP];
-  double lv[ICAP];
-  int L = rows::interp_row(A, Sptr, Scol, cf, f2c, n_own, i, tf, pmax, tf == 0.0, lc, lv, lc, lv, ICAP);
-  if (L < 0) { ovf_rows[atomicAdd(ovf_count, 1)] = i; L = 0; }
-  len[i] = L;
-}
-__global__ void __launch_bounds__(128) k_interp_fill(rows::Csr A, const int *Sptr, const int *Scol, const int *cf, const int *f2c,
-                                                     int n_own, double tf, int pmax, const int *Pptr, int *Pcol, double *Pval,
-                                                     const signed char *is_ovf) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= A.nr) return;
-  if (is_ovf && is_ovf[i]) return;
-  int lc[ICAP];
-  double lv[ICAP];
-  int b = Pptr[i];
-  if (Pptr[i + 1] == b) return;
-  rows::interp_row(A, Sptr, Scol, cf, f2c, n_own, i, tf, pmax, false, Pcol + b, Pval + b, lc, lv, ICAP);
-}
-// overflow rows: scratch in global memory, capacity cap per row
-__global__ void k_interp_ovf(rows::Csr A, const int *Sptr, const int *Scol, const int *cf, const int *f2c, int n_own, double tf,
-                             int pmax, const int *rows_list, int nrows, int *sc, double *sv, int cap, int *len, const int *Pptr,
-                             int *Pcol, double *Pval, int *err) {
-  int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= nrows) return;
-  int i = rows_list[t];
-  int *lc = sc + (size_t)t * cap;
-  double *lv = sv + (size_t)t * cap;
-  if (Pptr == nullptr) {
-    int L = rows::interp_row(A, Sptr, Scol, cf, f2c, n_own, i, tf, pmax, tf == 0.0, lc, lv, lc, lv, cap);
-    if (L < 0) { *err = 1; L = 0; }
-    len[i] = L;
-  } else {
-    int b = Pptr[i];
-    if (Pptr[i + 1] > b) rows::interp_row(A, Sptr, Scol, cf, f2c, n_own, i, tf, pmax, false, Pcol + b, Pval + b, lc, lv, cap);
-  }
-}
-__global__ void k_mark(const int *list, int n, signed char *flag) {
-  int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t < n) flag[list[t]] = 1;
-}
-
 // ---- smoother diagonal / dense coarse matrix ------------------------------------------------------------------------
 __global__ void k_smoother_diag(rows::Csr A, int relax_type, double *d) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -208,305 +153,7 @@ __global__ void k_ge_factor(double *A, int n) {
   }
 }
 
-// ---- transposition: stable counting sort by column (CUB radix sort on the column key) -------------------------------
-__global__ void k_expand_rows(int nr, const int *ptr, int *rowidx) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= nr) return;
-  for (int k = ptr[i]; k < ptr[i + 1]; ++k) rowidx[k] = i;
-}
-__global__ void k_iota(int *a, i64 n) {
-  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
-  if (k < n) a[k] = (int)k;
-}
-__global__ void k_transpose_gather(i64 nnz, const int *perm, const int *rowidx, const double *val, int *tcol, double *tval) {
-  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= nnz) return;
-  int src = perm[k];
-  tcol[k] = rowidx[src];
-  tval[k] = val[src];
-}
-__global__ void k_hist(const int *col, i64 nnz, int *cnt) {
-  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
-  if (k < nnz) atomicAdd(cnt + col[k], 1);
-}
-
-// ---- SpGEMM ---------------------------------------------------------------------------------------------------------
-template <int G>
-__device__ __forceinline__ void gsync(unsigned mask) {
-  if (G <= 32) __syncwarp(mask);
-  else __syncthreads();
-}
-__device__ __forceinline__ int hash_insert(int *keys, int H, int c, bool &isnew) {
-  unsigned h = (((unsigned)c * 2654435761u) >> 11) & (unsigned)(H - 1);
-  while (true) {
-    int old = atomicCAS(keys + h, -1, c);
-    if (old == -1) { isnew = true; return (int)h; }
-    if (old == c) { isnew = false; return (int)h; }
-    h = (h + 1) & (unsigned)(H - 1);
-  }
-}
-
-// one output row handled by the G threads of a group.  keys/vals: hash table of H slots; lk/lv: compaction list.
-template <int G, bool NUMERIC>
-__device__ __forceinline__ void spgemm_row(const rows::Csr &A, const rows::Csr &B, int row, int lane, unsigned mask, int *keys,
-                                           double *vals, int H, int *cnt, int *lk, double *lv, const int *Cptr, int *Ccol,
-                                           double *Cval, int *nnz_out, int diag_col) {
-  for (int s = lane; s < H; s += G) {
-    keys[s] = -1;
-    if (NUMERIC) vals[s] = 0.0;
-  }
-  if (lane == 0) *cnt = 0;
-  gsync<G>(mask);
-  int ab = A.ptr[row], ae = A.ptr[row + 1];
-  for (int ka = ab; ka < ae; ++ka) {
-    int k = A.col[ka];
-    double a = NUMERIC ? A.val[ka] : 0.0;
-    int bb = B.ptr[k], be = B.ptr[k + 1];
-    for (int kb = bb + lane; kb < be; kb += G) {
-      bool isnew;
-      int slot = hash_insert(keys, H, B.col[kb], isnew);
-      if (NUMERIC) {
-        double prod = __dmul_rn(a, B.val[kb]);
-        vals[slot] = __dadd_rn(vals[slot], prod);
-      } else if (isnew) {
-        atomicAdd(cnt, 1);
-      }
-    }
-    if (NUMERIC) gsync<G>(mask);
-  }
-  gsync<G>(mask);
-  if (!NUMERIC) {
-    if (lane == 0) nnz_out[row] = *cnt;
-    gsync<G>(mask);
-    return;
-  }
-  for (int s = lane; s < H; s += G) {
-    int c = keys[s];
-    if (c != -1) {
-      int p = atomicAdd(cnt, 1);
-      lk[p] = c;
-      lv[p] = vals[s];
-    }
-  }
-  gsync<G>(mask);
-  int n = *cnt;
-  int base = Cptr[row];
-  for (int t = lane; t < n; t += G) {
-    int c = lk[t];
-    int key = (c == diag_col) ? -1 : c;
-    int rank = 0;
-    for (int u = 0; u < n; ++u) {
-      int cu = lk[u];
-      int ku = (cu == diag_col) ? -1 : cu;
-      rank += (ku < key) ? 1 : 0;
-    }
-    Ccol[base + rank] = c;
-    Cval[base + rank] = lv[t];
-  }
-  gsync<G>(mask);
-}
-
-// shared-memory table kernels.  G threads per row, blockDim.x / G rows per block.
-template <int G, bool NUMERIC>
-__global__ void k_spgemm_smem(rows::Csr A, rows::Csr B, const int *row_list, int nrows, int H, const int *Cptr, int *Ccol,
-                              double *Cval, int *nnz_out, int diag_first) {
-  extern __shared__ __align__(16) unsigned char smem[];
-  const int groups = blockDim.x / G;
-  const int g = threadIdx.x / G, lane = threadIdx.x % G;
-  // per group: cnt (int, padded to 8 B) | [vals H doubles | lv H doubles] | keys H ints | [lk H ints]
-  size_t per = 8 + (NUMERIC ? ((size_t)H * 8 * 2 + (size_t)H * 4 * 2) : (size_t)H * 4);
-  unsigned char *base = smem + per * g;
-  int *cnt = (int *)base;
-  double *vals = (double *)(base + 8);
-  double *lv = vals + (NUMERIC ? H : 0);
-  int *keys = (int *)(base + 8 + (NUMERIC ? (size_t)H * 16 : 0));
-  int *lk = keys + H;
-  unsigned mask = 0xffffffffu;
-  if constexpr (G < 32) mask = ((1u << G) - 1u) << ((threadIdx.x & 31) / G * G);
-  int idx = blockIdx.x * groups + g;
-  if (G > 32) {  // block per row: every thread must take part in __syncthreads
-    if (idx >= nrows) return;  // uniform for the whole block (groups == 1)
-  } else if (idx >= nrows) return;
-  int row = row_list[idx];
-  spgemm_row<G, NUMERIC>(A, B, row, lane, mask, keys, vals, H, cnt, lk, lv, Cptr, Ccol, Cval, nnz_out, diag_first ? row : -2);
-}
-
-// global-memory table kernel: one block per row slot, grid-stride over the bin
-template <bool NUMERIC>
-__global__ void k_spgemm_gmem(rows::Csr A, rows::Csr B, const int *row_list, int nrows, int H, int *gkeys, double *gvals, int *glk,
-                              double *glv, const int *Cptr, int *Ccol, double *Cval, int *nnz_out, int diag_first) {
-  __shared__ int cnt;
-  int *keys = gkeys + (size_t)blockIdx.x * H;
-  double *vals = NUMERIC ? gvals + (size_t)blockIdx.x * H : nullptr;
-  int *lk = NUMERIC ? glk + (size_t)blockIdx.x * H : nullptr;
-  double *lv = NUMERIC ? glv + (size_t)blockIdx.x * H : nullptr;
-  for (int idx = blockIdx.x; idx < nrows; idx += gridDim.x) {
-    int row = row_list[idx];
-    spgemm_row<256, NUMERIC>(A, B, row, threadIdx.x, 0, keys, vals, H, &cnt, lk, lv, Cptr, Ccol, Cval, nnz_out,
-                              diag_first ? row : -2);
-  }
-}
-__global__ void k_spgemm_bound(rows::Csr A, rows::Csr B, int *bound) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= A.nr) return;
-  i64 s = 0;
-  for (int k = A.ptr[i]; k < A.ptr[i + 1]; ++k) {
-    int c = A.col[k];
-    s += B.ptr[c + 1] - B.ptr[c];
-  }
-  if (s > B.nc) s = B.nc;
-  bound[i] = (int)s;
-}
-// bin rows by size: bin b holds rows with lim[b-1] < size <= lim[b]; size 0 rows go nowhere
-__global__ void k_bin_count(int n, const int *size, int l0, int l1, int l2, int *counts) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  __shared__ int sc[4];
-  if (threadIdx.x < 4) sc[threadIdx.x] = 0;
-  __syncthreads();
-  if (i < n) {
-    int s = size[i];
-    if (s > 0) atomicAdd(&sc[s <= l0 ? 0 : (s <= l1 ? 1 : (s <= l2 ? 2 : 3))], 1);
-  }
-  __syncthreads();
-  if (threadIdx.x < 4 && sc[threadIdx.x]) atomicAdd(counts + threadIdx.x, sc[threadIdx.x]);
-}
-__global__ void k_bin_fill(int n, const int *size, int l0, int l1, int l2, const int *offsets, int *cursor, int *list, int *maxsz) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  int s = size[i];
-  if (s <= 0) return;
-  int b = s <= l0 ? 0 : (s <= l1 ? 1 : (s <= l2 ? 2 : 3));
-  int p = atomicAdd(cursor + b, 1);
-  list[offsets[b] + p] = i;
-  if (b == 3) atomicMax(maxsz, s);
-}
-
-struct Bins {
-  DVec<int> list;
-  int count[4] = {0, 0, 0, 0}, offset[4] = {0, 0, 0, 0};
-  int max_size = 0;
-};
-void make_bins(int n, const int *size, int l0, int l1, int l2, Bins &b) {
-  DVec<int> d(16);
-  d.zero();
-  k_bin_count<<<div_up(n, 256), 256, 0, stream()>>>(n, size, l0, l1, l2, d.p);
-  std::vector<int> h = d.to_host();
-  int off = 0;
-  for (int k = 0; k < 4; ++k) { b.count[k] = h[k]; b.offset[k] = off; off += h[k]; }
-  b.list.alloc(off > 0 ? off : 1);
-  std::vector<int> hd(16, 0);
-  for (int k = 0; k < 4; ++k) hd[4 + k] = b.offset[k];
-  d.from_host(hd);
-  k_bin_fill<<<div_up(n, 256), 256, 0, stream()>>>(n, size, l0, l1, l2, d.p + 4, d.p + 8, b.list.p, d.p + 12);
-  b.max_size = d.to_host()[12];
-  count_launch(2);
-}
-
-inline int next_pow2(i64 v) {
-  int p = 1;
-  while (p < v) p <<= 1;
-  return p;
-}
-
-template <bool NUMERIC>
-void spgemm_pass(const DCsr &A, const DCsr &B, const Bins &bins, const int *Cptr, int *Ccol, double *Cval, int *nnz_out,
-                 bool diag_first, int H2) {
-  rows::Csr a = rv(A), b = rv(B);
-  auto smem_bytes = [](int groups, int H) { return (size_t)groups * (8 + (NUMERIC ? (size_t)H * 24 : (size_t)H * 4)); };
-  // bin 0: warp per row, H = 128, 8 rows per block
-  if (bins.count[0]) {
-    auto kern = k_spgemm_smem<32, NUMERIC>;
-    size_t sm = smem_bytes(8, 128);
-    kern<<<div_up(bins.count[0], 8), 256, sm, stream()>>>(a, b, bins.list.p + bins.offset[0], bins.count[0], 128, Cptr, Ccol, Cval,
-                                                          nnz_out, diag_first);
-    count_launch();
-  }
-  // bin 1: warp per row, H = 1024, 4 rows per block
-  if (bins.count[1]) {
-    auto kern = k_spgemm_smem<32, NUMERIC>;
-    size_t sm = smem_bytes(4, 1024);
-    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    kern<<<div_up(bins.count[1], 4), 128, sm, stream()>>>(a, b, bins.list.p + bins.offset[1], bins.count[1], 1024, Cptr, Ccol, Cval,
-                                                          nnz_out, diag_first);
-    count_launch();
-  }
-  // bin 2: block per row, H2 slots (8192 numeric / 32768 symbolic)
-  if (bins.count[2]) {
-    auto kern = k_spgemm_smem<256, NUMERIC>;
-    size_t sm = smem_bytes(1, H2);
-    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    kern<<<bins.count[2], 256, sm, stream()>>>(a, b, bins.list.p + bins.offset[2], bins.count[2], H2, Cptr, Ccol, Cval, nnz_out,
-                                               diag_first);
-    count_launch();
-  }
-  // bin 3: global-memory tables
-  if (bins.count[3]) {
-    int H = next_pow2(2 * (i64)bins.max_size);
-    int grid = std::min(bins.count[3], 2 * ctx().sm_count);
-    DVec<int> gk((size_t)grid * H), glk;
-    DVec<double> gv, glv;
-    if (NUMERIC) { gv.alloc((size_t)grid * H); glk.alloc((size_t)grid * H); glv.alloc((size_t)grid * H); }
-    k_spgemm_gmem<NUMERIC><<<grid, 256, 0, stream()>>>(a, b, bins.list.p + bins.offset[3], bins.count[3], H, gk.p, gv.p, glk.p,
-                                                       glv.p, Cptr, Ccol, Cval, nnz_out, diag_first);
-    count_launch();
-    B200_CUDA(cudaStreamSynchronize(stream()));
-  }
-  B200_KERNEL_CHECK();
-}
-
 }  // namespace
-
-void csr_transpose(const DCsr &A, DCsr &T) {
-  T.nr = A.nc;
-  T.nc = A.nr;
-  T.nnz = A.nnz;
-  T.ptr.alloc((size_t)T.nr + 1);
-  T.col.alloc((size_t)A.nnz);
-  T.val.alloc((size_t)A.nnz);
-  DVec<int> cnt((size_t)T.nr + 1);
-  cnt.zero();
-  if (A.nnz == 0) { T.ptr.zero(); return; }
-  k_hist<<<div_up(A.nnz, 256), 256, 0, stream()>>>(A.col.p, A.nnz, cnt.p);
-  exclusive_scan(cnt.p, T.ptr.p, (i64)T.nr + 1);
-  DVec<int> rowidx((size_t)A.nnz), iota((size_t)A.nnz), perm((size_t)A.nnz), keys_out((size_t)A.nnz);
-  k_expand_rows<<<div_up(A.nr, 256), 256, 0, stream()>>>(A.nr, A.ptr.p, rowidx.p);
-  k_iota<<<div_up(A.nnz, 256), 256, 0, stream()>>>(iota.p, A.nnz);
-  int bits = 1;
-  while ((1LL << bits) < A.nc) ++bits;
-  size_t tb = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, tb, A.col.p, keys_out.p, iota.p, perm.p, (int)A.nnz, 0, bits, stream());
-  DVec<char> tmp(tb);
-  cub::DeviceRadixSort::SortPairs(tmp.p, tb, A.col.p, keys_out.p, iota.p, perm.p, (int)A.nnz, 0, bits, stream());
-  k_transpose_gather<<<div_up(A.nnz, 256), 256, 0, stream()>>>(A.nnz, perm.p, rowidx.p, A.val.p, T.col.p, T.val.p);
-  count_launch(6);
-  B200_KERNEL_CHECK();
-}
-
-void csr_spgemm(const DCsr &A, const DCsr &B, DCsr &C, bool diag_first) {
-  B200_REQUIRE(A.nc == B.nr, "csr_spgemm: dimension mismatch");
-  C.nr = A.nr;
-  C.nc = B.nc;
-  C.ptr.alloc((size_t)C.nr + 1);
-  if (A.nr == 0) { C.nnz = 0; return; }
-  DVec<int> bound((size_t)A.nr), nnz_row((size_t)A.nr + 1);
-  nnz_row.zero();
-  k_spgemm_bound<<<div_up(A.nr, 256), 256, 0, stream()>>>(rv(A), rv(B), bound.p);
-  count_launch();
-  {
-    Bins bins;
-    make_bins(A.nr, bound.p, 64, 512, 16384, bins);
-    spgemm_pass<false>(A, B, bins, nullptr, nullptr, nullptr, nnz_row.p, diag_first, 32768);
-  }
-  exclusive_scan(nnz_row.p, C.ptr.p, (i64)C.nr + 1);
-  C.nnz = fetch(C.ptr.p + C.nr);
-  C.col.alloc((size_t)C.nnz);
-  C.val.alloc((size_t)C.nnz);
-  {
-    Bins bins;
-    make_bins(A.nr, nnz_row.p, 64, 512, 4096, bins);
-    spgemm_pass<true>(A, B, bins, C.ptr.p, C.col.p, C.val.p, nullptr, diag_first, 8192);
-  }
-}
 
 // =====================================================================================================================
 // setup driver
@@ -680,51 +327,9 @@ bool coarsen_level(Amg &amg, AmgLevel &L, AmgLevel &Lc) {
   // interpolation (extended+i) + truncation
   {
     PhaseTimer t(amg, "interp");
-    DVec<int> len((size_t)n + 1), ovf_count(1), ovf_rows((size_t)n);
-    ovf_count.zero();
-    k_interp_count<<<div_up((i64)n + 1, 128), 128, 0, stream()>>>(a, L.Sptr.p, L.Scol.p, L.cf_raw.p, f2c.p, n, o.trunc_factor,
-                                                                   o.p_max_elmts, len.p, ovf_count.p, ovf_rows.p);
-    count_launch();
-    int novf = fetch(ovf_count.p);
-    DVec<signed char> is_ovf;
-    DVec<int> sc;
-    DVec<double> sv;
-    const int ocap = 4096;
-    DVec<int> err(1);
-    err.zero();
-    if (novf > 0) {
-      B200_REQUIRE(novf <= 65536, "interpolation: too many rows exceed the in-register C-hat capacity");
-      is_ovf.alloc((size_t)n);
-      is_ovf.zero();
-      k_mark<<<div_up(novf, 256), 256, 0, stream()>>>(ovf_rows.p, novf, is_ovf.p);
-      sc.alloc((size_t)novf * ocap);
-      sv.alloc((size_t)novf * ocap);
-      k_interp_ovf<<<div_up(novf, 64), 64, 0, stream()>>>(a, L.Sptr.p, L.Scol.p, L.cf_raw.p, f2c.p, n, o.trunc_factor, o.p_max_elmts,
-                                                          ovf_rows.p, novf, sc.p, sv.p, ocap, len.p, nullptr, nullptr, nullptr, err.p);
-      count_launch(2);
-      B200_REQUIRE(fetch(err.p) == 0, "interpolation: C-hat larger than 4096 entries");
-    }
     DCsr &P = L.P.diag;
-    P.nr = n;
     P.nc = nc;
-    P.ptr.alloc((size_t)n + 1);
-    exclusive_scan(len.p, P.ptr.p, (i64)n + 1);
-    P.nnz = fetch(P.ptr.p + n);
-    P.col.alloc((size_t)P.nnz);
-    P.val.alloc((size_t)P.nnz);
-    k_interp_fill<<<div_up(n, 128), 128, 0, stream()>>>(a, L.Sptr.p, L.Scol.p, L.cf_raw.p, f2c.p, n, o.trunc_factor, o.p_max_elmts,
-                                                        P.ptr.p, P.col.p, P.val.p, novf > 0 ? is_ovf.p : nullptr);
-    count_launch();
-    if (novf > 0) {
-      k_interp_ovf<<<div_up(novf, 64), 64, 0, stream()>>>(a, L.Sptr.p, L.Scol.p, L.cf_raw.p, f2c.p, n, o.trunc_factor, o.p_max_elmts,
-                                                          ovf_rows.p, novf, sc.p, sv.p, ocap, len.p, P.ptr.p, P.col.p, P.val.p, err.p);
-      count_launch();
-    }
-    B200_KERNEL_CHECK();
-    if (o.trunc_factor > 0.0) {
-      // rows may have become shorter than the counted length only if counting and filling disagree; they run the same
-      // code on the same data, so lengths are identical by construction.
-    }
+    build_interp(A, L.Sptr.p, L.Scol.p, L.S_nnz, L.cf_raw.p, f2c.p, n, n, o.trunc_factor, o.p_max_elmts, P);
     L.cf.alloc((size_t)n);
     k_fold_sf<<<g, 256, 0, stream()>>>(n, L.cf_raw.p, L.cf.p);
     count_launch();
