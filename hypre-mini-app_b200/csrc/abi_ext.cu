@@ -75,6 +75,10 @@ HYPRE_Int b200hypre_comm_init(HYPRE_Int rank, HYPRE_Int nranks, const void *id12
   API_ARG(nranks == 1 || id128, "b200hypre_comm_init: the NCCL id is required when nranks > 1");
   API_BEGIN comm_init(rank, nranks, id128); API_END
 }
+HYPRE_Int b200hypre_comm_init_shm(HYPRE_Int rank, HYPRE_Int nranks, const char *name, size_t slot_bytes) {
+  API_ARG(nranks == 1 || name, "b200hypre_comm_init_shm: segment name required when nranks > 1");
+  API_BEGIN comm_init_shm(rank, nranks, name, slot_bytes); API_END
+}
 HYPRE_Int b200hypre_comm_init_from_env(void) { API_BEGIN comm_init_from_env(); API_END }
 HYPRE_Int b200hypre_comm_finalize(void) { API_BEGIN comm_finalize(); API_END }
 HYPRE_Int b200hypre_comm_rank(void) { return ctx().rank; }
@@ -167,9 +171,10 @@ HYPRE_Int b200hypre_amg_level_get(HYPRE_Solver amg, HYPRE_Int level, HYPRE_Int w
     std::vector<int> sp = L.Sptr.to_host();
     if (ptr) memcpy(ptr, sp.data(), sizeof(int) * sp.size());
     if (col) {
-      B200_REQUIRE(ctx().nranks == 1, "S inspection is single-rank only");
+      // merged numbering: own columns first, then the halo columns of A (multi-rank)
       std::vector<int> sc = L.Scol.to_host();
-      for (i64 k = 0; k < L.S_nnz; ++k) col[k] = L.A->col_start + sc[k];
+      const int nown = L.A->n_cols_local;
+      for (i64 k = 0; k < L.S_nnz; ++k) col[k] = sc[k] < nown ? L.A->col_start + sc[k] : L.A->col_map_offd[sc[k] - nown];
     }
   } else parcsr_to_host(*pick(h, level, which), ptr, col, val);
   API_END
@@ -191,7 +196,7 @@ HYPRE_Int b200hypre_amg_level_smoother(HYPRE_Solver amg, HYPRE_Int level, HYPRE_
   AmgHandle *h = as_amg(amg);
   B200_REQUIRE(level >= 0 && level < (int)h->amg.lev.size(), "level out of range");
   std::vector<double> v = h->amg.lev[level]->dsm.to_host();
-  memcpy(d, v.data(), sizeof(double) * v.size());
+  memcpy(d, v.data(), sizeof(double) * std::min<size_t>(v.size(), (size_t)h->amg.lev[level]->A->n));
   API_END
 }
 HYPRE_Int b200hypre_amg_level_cheby(HYPRE_Solver amg, HYPRE_Int level, HYPRE_Real *out6) {

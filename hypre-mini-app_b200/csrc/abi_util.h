@@ -39,6 +39,7 @@ AmgHandle *as_amg(HYPRE_Solver s);
 bool precond_zero_guess_hint();
 void comm_get_unique_id(void *out128);
 void comm_init(int rank, int nranks, const void *id128);
+void comm_init_shm(int rank, int nranks, const char *name, size_t slot_bytes);
 void comm_init_from_env();
 void comm_finalize();
 void process_grid(int nprocs, int *px, int *py, int *pz);

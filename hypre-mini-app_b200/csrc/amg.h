@@ -76,8 +76,8 @@ struct Amg {
   AmgOptions opt;
   std::vector<std::unique_ptr<AmgLevel>> lev;
   // coarsest level: dense LU (unpivoted Gaussian elimination multipliers + U), SURVEY.md A.9
-  DVec<double> ge_lu;
-  int ge_n = 0;
+  DVec<double> ge_lu, ge_f;       // ge_f: gathered right-hand side of the coarsest level (multi-rank)
+  int ge_n = 0, ge_row_start = 0;
   bool setup_done = false;
   DotWork dw;
   double setup_seconds = 0;

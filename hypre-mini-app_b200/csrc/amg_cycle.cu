@@ -16,12 +16,14 @@ namespace b200 {
 
 namespace {
 
-__global__ void k_ge_solve(const double *__restrict__ LU, int n, const double *__restrict__ f, double *__restrict__ x) {
+// x_out[0 .. n_out) = solution entries [out_start, out_start + n_out) (this rank's rows of the replicated coarse solve)
+__global__ void k_ge_solve(const double *__restrict__ LU, int n, const double *__restrict__ f, double *__restrict__ x, int out_start,
+                           int n_out) {
   extern __shared__ double xs[];
   for (int i = threadIdx.x; i < n; i += blockDim.x) xs[i] = f[i];
   __syncthreads();
   if (n == 1) {
-    if (threadIdx.x == 0) { double a = LU[0]; x[0] = (a != 0.0) ? xs[0] / a : xs[0]; }
+    if (threadIdx.x == 0 && n_out > 0) { double a = LU[0]; x[0] = (a != 0.0) ? xs[0] / a : xs[0]; }
     return;
   }
   for (int k = 0; k < n - 1; ++k) {
@@ -50,7 +52,7 @@ __global__ void k_ge_solve(const double *__restrict__ LU, int n, const double *_
     if (a != 0.0) xs[0] /= a;
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < n; i += blockDim.x) x[i] = xs[i];
+  for (int i = threadIdx.x; i < n_out; i += blockDim.x) x[i] = xs[out_start + i];
 }
 
 struct LevelBufs {  // ping-pong state of one level during a cycle
@@ -142,7 +144,14 @@ void level_down(Amg &amg, int l, std::vector<LevelBufs> &bufs) {
   int n = L.A->n;
   if (l == nl - 1) {
     if (amg.ge_n > 0) {
-      k_ge_solve<<<1, 256, sizeof(double) * amg.ge_n, stream()>>>(amg.ge_lu.p, amg.ge_n, b.f, b.cur);
+      const double *f = b.f;
+      if (ctx().nranks > 1) {  // gather the coarsest right-hand side: disjoint rows, zero elsewhere, so the sum is exact
+        amg.ge_f.zero();
+        if (n) vec_copy(amg.ge_f.p + amg.ge_row_start, b.f, n);
+        allreduce_sum_dev(amg.ge_f.p, amg.ge_n);
+        f = amg.ge_f.p;
+      }
+      k_ge_solve<<<1, 256, sizeof(double) * amg.ge_n, stream()>>>(amg.ge_lu.p, amg.ge_n, f, b.cur, amg.ge_row_start, n);
       count_launch();
     } else {
       if (o.num_sweeps[1] == 0) vec_fill(b.cur, 0.0, n);

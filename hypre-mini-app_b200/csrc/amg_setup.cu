@@ -16,6 +16,9 @@
 
 namespace b200 {
 
+bool coarsen_level_dist(Amg &amg, AmgLevel &L, AmgLevel &Lc);   // amg_dist.cu
+void smoother_diag_dist(ParCsr &A, int relax_type, double *d);
+
 namespace {
 
 inline rows::Csr rv(const DCsr &A) { return rows::Csr{A.nr, A.nc, A.ptr.p, A.col.p, A.val.p}; }
@@ -126,10 +129,14 @@ __global__ void k_inv_sqrt_diag(rows::Csr A, double *d) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < A.nr) d[i] = 1.0 / sqrt(A.val[A.ptr[i]]);
 }
-__global__ void k_dense_fill(rows::Csr A, double *D) {
+// rows of this rank into the dense global matrix (gn x gn): diag block columns are col_start + c, offd through the column map
+__global__ void k_dense_fill_par(int n, CsrView Dg, CsrView Of, i64 row_start, i64 col_start, const i64 *colmap, int gn, double *D) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= A.nr) return;
-  for (int k = A.ptr[i]; k < A.ptr[i + 1]; ++k) D[(size_t)i * A.nr + A.col[k]] = A.val[k];
+  if (i >= n) return;
+  size_t base = (size_t)(row_start + i) * gn;
+  for (int k = Dg.ptr[i]; k < Dg.ptr[i + 1]; ++k) D[base + (size_t)(col_start + Dg.col[k])] = Dg.val[k];
+  if (Of.ptr)
+    for (int k = Of.ptr[i]; k < Of.ptr[i + 1]; ++k) D[base + (size_t)colmap[Of.col[k]]] = Of.val[k];
 }
 // unpivoted Gaussian elimination run once: multipliers are stored below the diagonal so that the
 // solve applies exactly the operations of the per-solve elimination to the right-hand side.
@@ -399,7 +406,8 @@ void amg_setup(Amg &amg, ParCsr &A) {
     bool last = (level >= o.max_levels - 1) || (fine <= o.max_coarse_size);
     if (!last) {
       std::unique_ptr<AmgLevel> Lc(new AmgLevel());
-      if (coarsen_level(amg, L, *Lc)) amg.lev.push_back(std::move(Lc));
+      const bool ok = (ctx().nranks > 1) ? coarsen_level_dist(amg, L, *Lc) : coarsen_level(amg, L, *Lc);
+      if (ok) amg.lev.push_back(std::move(Lc));
       else last = true;
     }
     if (last) break;
@@ -417,9 +425,9 @@ void amg_setup(Amg &amg, ParCsr &A) {
       int rt = o.relax_type[1];
       if (rt == 16) cheby_setup(amg, L);
       else {
-        L.dsm.alloc(n);
-        if (n) k_smoother_diag<<<div_up(n, 256), 256, 0, stream()>>>(rv(Al.diag), rt, L.dsm.p);
-        count_launch();
+        L.dsm.alloc((size_t)std::max(n, 1));
+        if (ctx().nranks > 1) smoother_diag_dist(Al, rt, L.dsm.p);
+        else if (n) { k_smoother_diag<<<div_up(n, 256), 256, 0, stream()>>>(rv(Al.diag), rt, L.dsm.p); count_launch(); }
       }
       i64 ld = ((i64)n + 1) & ~1LL;
       L.u.alloc(ld); L.f.alloc(ld); L.r.alloc(ld); L.t0.alloc(ld); L.t1.alloc(ld);
@@ -429,14 +437,27 @@ void amg_setup(Amg &amg, ParCsr &A) {
     // coarsest: dense LU
     AmgLevel &C = *amg.lev[nl - 1];
     int n = C.A->n;
+    i64 gn = C.A->g_rows;
     amg.ge_n = 0;
-    if (!(nl == 1 && o.max_levels == 1) && n > 0 && n <= 2048 && ctx().nranks == 1) {
-      amg.ge_n = n;
-      amg.ge_lu.alloc((size_t)n * n);
+    amg.ge_row_start = 0;
+    if (!(nl == 1 && o.max_levels == 1) && gn > 0 && gn <= 2048) {
+      // every rank holds the whole (tiny) coarsest operator densely: rows are disjoint, so the sum over ranks is exact
+      amg.ge_n = (int)gn;
+      amg.ge_row_start = (int)C.A->row_start;
+      amg.ge_lu.alloc((size_t)gn * gn);
       amg.ge_lu.zero();
-      k_dense_fill<<<div_up(n, 128), 128, 0, stream()>>>(rv(C.A->diag), amg.ge_lu.p);
-      k_ge_factor<<<1, 256, 0, stream()>>>(amg.ge_lu.p, n);
-      count_launch(2);
+      amg.ge_f.alloc((size_t)gn);
+      DVec<i64> dmap;
+      dmap.from_host(C.A->col_map_offd.data(), C.A->col_map_offd.size());
+      if (n) {
+        k_dense_fill_par<<<div_up(n, 128), 128, 0, stream()>>>(n, C.A->diag.view(),
+                                                             C.A->offd.nnz > 0 ? C.A->offd.view() : CsrView{0, 0, nullptr, nullptr, nullptr},
+                                                             C.A->row_start, C.A->col_start, dmap.p, (int)gn, amg.ge_lu.p);
+        count_launch();
+      }
+      for (i64 off = 0; off < gn * gn; off += 1 << 20) allreduce_sum_dev(amg.ge_lu.p + off, (int)std::min<i64>(1 << 20, gn * gn - off));
+      k_ge_factor<<<1, 256, 0, stream()>>>(amg.ge_lu.p, (int)gn);
+      count_launch();
     }
     B200_KERNEL_CHECK();
   }

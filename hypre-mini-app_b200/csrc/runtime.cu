@@ -173,6 +173,29 @@ double *scratch() {
 }
 }  // namespace
 
+// host-staged shared-memory transport for N ranks on one GPU (comm_shm.cu)
+bool shm_active();
+void shm_init(int rank, int nranks, const char *name, size_t slot_bytes);
+void shm_finalize();
+void shm_allreduce_host(void *buf, int count, int kind);
+void shm_allgather_host(const void *in, void *out, size_t bytes);
+void shm_allreduce_dev(double *buf, int count, cudaStream_t s);
+void shm_allgather_dev(const void *in, void *out, size_t bytes, cudaStream_t s);
+void shm_exchange_dev(int nsend, const int *send_rank, const void *const *send_ptr, const size_t *send_bytes, int nrecv,
+                      const int *recv_rank, void *const *recv_ptr, const size_t *recv_bytes, cudaStream_t s);
+
+void comm_init_shm(int rank, int nranks, const char *name, size_t slot_bytes) {
+  ensure_init();
+  Context &c = ctx();
+  B200_REQUIRE(nranks >= 1 && rank >= 0 && rank < nranks, "comm_init_shm: bad rank / size");
+  c.rank = rank;
+  c.nranks = nranks;
+  if (nranks == 1) return;
+  const char *mb = getenv("B200_SHM_SLOT_MB");
+  if (mb && atoi(mb) > 0) slot_bytes = (size_t)atoi(mb) << 20;
+  shm_init(rank, nranks, name, slot_bytes);
+}
+
 void comm_get_unique_id(void *out128) {
   nccl_load();
   B200_NCCL(g_nccl.GetUniqueId(out128));
@@ -196,6 +219,7 @@ void comm_init(int rank, int nranks, const void *id128) {
 void comm_finalize() {
   Context &c = ctx();
   if (c.nccl) { g_nccl.CommDestroy(c.nccl); c.nccl = nullptr; }
+  shm_finalize();
   c.rank = 0;
   c.nranks = 1;
 }
@@ -259,12 +283,14 @@ void comm_init_from_env() {
 void allreduce_sum_dev(double *buf, int count) {
   Context &c = ctx();
   if (c.nranks == 1 || count <= 0) return;
+  if (shm_active()) { shm_allreduce_dev(buf, count, stream()); return; }
   B200_NCCL(g_nccl.AllReduce(buf, buf, (size_t)count, NCCL_F64, NCCL_SUM, c.nccl, stream()));
 }
 void allreduce_sum_host(double *buf, int count) {
   Context &c = ctx();
   if (c.nranks == 1 || count <= 0) return;
   B200_REQUIRE(count <= 512, "allreduce_sum_host: count > 512");
+  if (shm_active()) { shm_allreduce_host(buf, count, 0); return; }
   double *d = scratch();
   B200_CUDA(cudaMemcpyAsync(d, buf, count * sizeof(double), cudaMemcpyHostToDevice, stream()));
   B200_NCCL(g_nccl.AllReduce(d, d, (size_t)count, NCCL_F64, NCCL_SUM, c.nccl, stream()));
@@ -275,6 +301,7 @@ static void allreduce_host_i64(i64 *buf, int count, int op) {
   Context &c = ctx();
   if (c.nranks == 1 || count <= 0) return;
   B200_REQUIRE(count <= 512, "allreduce_host_i64: count > 512");
+  if (shm_active()) { shm_allreduce_host(buf, count, op == NCCL_SUM ? 1 : 2); return; }
   i64 *d = (i64 *)scratch();
   B200_CUDA(cudaMemcpyAsync(d, buf, count * sizeof(i64), cudaMemcpyHostToDevice, stream()));
   B200_NCCL(g_nccl.AllReduce(d, d, (size_t)count, NCCL_INT64, op, c.nccl, stream()));
@@ -296,12 +323,14 @@ void allgather_dev(const void *in, void *out, size_t bytes) {
     if (in != out) B200_CUDA(cudaMemcpyAsync(out, in, bytes, cudaMemcpyDeviceToDevice, stream()));
     return;
   }
+  if (shm_active()) { shm_allgather_dev(in, out, bytes, stream()); return; }
   B200_NCCL(g_nccl.AllGather(in, out, bytes, NCCL_INT8, c.nccl, stream()));
 }
 // host convenience: gathers `count` i64 per rank
 void allgather_host_i64(const i64 *in, i64 *out, int count) {
   Context &c = ctx();
   if (c.nranks == 1) { memcpy(out, in, count * sizeof(i64)); return; }
+  if (shm_active()) { shm_allgather_host(in, out, count * sizeof(i64)); return; }
   DVec<i64> di((size_t)count), dout((size_t)count * c.nranks);
   B200_CUDA(cudaMemcpyAsync(di.p, in, count * sizeof(i64), cudaMemcpyHostToDevice, stream()));
   allgather_dev(di.p, dout.p, count * sizeof(i64));
@@ -314,6 +343,7 @@ void exchange_dev(int nsend, const int *send_rank, const void *const *send_ptr, 
                   const int *recv_rank, void *const *recv_ptr, const size_t *recv_bytes, cudaStream_t s) {
   Context &c = ctx();
   if (c.nranks == 1) return;
+  if (shm_active()) { shm_exchange_dev(nsend, send_rank, send_ptr, send_bytes, nrecv, recv_rank, recv_ptr, recv_bytes, s); return; }
   B200_NCCL(g_nccl.GroupStart());
   for (int k = 0; k < nsend; ++k)
     if (send_bytes[k]) B200_NCCL(g_nccl.Send(send_ptr[k], send_bytes[k], NCCL_INT8, send_rank[k], c.nccl, s));

@@ -361,7 +361,7 @@ void csr_spgemm(const DCsr &A, const DCsr &B, DCsr &C, bool diag_first) {
   C.nr = A.nr;
   C.nc = B.nc;
   C.ptr.alloc((size_t)C.nr + 1);
-  if (A.nr == 0) { C.nnz = 0; return; }
+  if (A.nr == 0) { C.nnz = 0; C.ptr.zero(); return; }
   const double in_bytes = 12.0 * (double)(A.nnz + B.nnz) + 4.0 * (double)(A.nr + B.nr);
   DVec<int> bound((size_t)A.nr), nnz_row((size_t)A.nr + 1);
   nnz_row.zero();

@@ -94,6 +94,13 @@ def comm_init(rank=0, nranks=1, nccl_id=None):
     check(L.b200hypre_comm_init(rank, nranks, buf), "comm_init")
 
 
+def comm_init_shm(rank, nranks, name, slot_bytes=0):
+    """N ranks sharing one GPU (NCCL refuses that): host-staged shared-memory transport, used by the N-rank parity tests"""
+    L = lib()
+    L.b200hypre_comm_init_shm.argtypes = [I32, I32, C.c_char_p, C.c_size_t]
+    check(L.b200hypre_comm_init_shm(rank, nranks, name.encode(), slot_bytes), "comm_init_shm")
+
+
 def get_unique_id():
     buf = (C.c_char * 128)()
     check(lib().b200hypre_get_unique_id(buf), "get_unique_id")

@@ -11,6 +11,9 @@ extern "C" {
 /* ---- ranks: one process per GPU (replaces MPI_Init / MPI_Comm_rank / MPI_Comm_size, main.cpp:33-45) ------------------ */
 HYPRE_Int b200hypre_get_unique_id(void *out128);                     /* rank 0: 128-byte NCCL id to ship to the others */
 HYPRE_Int b200hypre_comm_init(HYPRE_Int rank, HYPRE_Int nranks, const void *id128);   /* id may be NULL when nranks == 1 */
+/* N ranks sharing ONE GPU (NCCL refuses that): host-staged shared-memory transport, for parity tests of the N-rank path on a
+ * single-GPU box; `name` is a POSIX shm name ("/b200hypre-<id>") common to all ranks, slot_bytes the per-rank mailbox (0 = 64 MiB) */
+HYPRE_Int b200hypre_comm_init_shm(HYPRE_Int rank, HYPRE_Int nranks, const char *name, size_t slot_bytes);
 HYPRE_Int b200hypre_comm_init_from_env(void);                        /* RANK / WORLD_SIZE / LOCAL_RANK / MASTER_ADDR / MASTER_PORT */
 HYPRE_Int b200hypre_comm_finalize(void);
 HYPRE_Int b200hypre_comm_rank(void);

