@@ -18,6 +18,7 @@ def main():
     cfg = json.loads(sys.argv[5])
     import b200hypre
     if transport == "nccl":
+        rank, nranks = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))

@@ -22,6 +22,22 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 VAL_RTOL = 1e-10
 
 
+def run_ranks_nccl(nranks, cfg, timeout=600):
+    """one rank per GPU under torchrun, NCCL transport (needs >= nranks GPUs)"""
+    port = 29000 + (os.getpid() % 500)
+    with tempfile.TemporaryDirectory() as tmp:
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nranks}", "--master-addr", "127.0.0.1",
+               "--master-port", str(port), os.path.join(HERE, "mr_worker.py"), "-1", str(nranks), "nccl", tmp, json.dumps(cfg)]
+        p = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=timeout)
+        assert p.returncode == 0, p.stdout[-4000:]
+        return [dict(np.load(os.path.join(tmp, f"rank{r}.npz"))) for r in range(nranks)]
+
+
+def n_gpus():
+    import torch
+    return torch.cuda.device_count()
+
+
 def run_ranks(nranks, cfg, timeout=600):
     name = "/b200hypre-" + uuid.uuid4().hex[:12]
     with tempfile.TemporaryDirectory() as tmp:
@@ -91,6 +107,20 @@ CASES = [
 def test_multirank_hierarchy_and_solve(b200, n, grid, stencil, theta):
     nranks = grid[0] * grid[1] * grid[2]
     res = run_ranks(nranks, settings(n, grid, stencil, strong_threshold=theta))
+    compare_with_oracle(res, n, grid, stencil, theta)
+
+
+@pytest.mark.parametrize("n,grid,stencil,theta", [((16, 16, 16), (2, 1, 1), 7, 0.25), ((10, 10, 10), (2, 2, 2), 27, 0.25)])
+def test_multigpu_nccl_hierarchy_and_solve(b200, n, grid, stencil, theta):
+    """the same comparison with one rank per GPU over NCCL; skipped on boxes with fewer GPUs than ranks"""
+    nranks = grid[0] * grid[1] * grid[2]
+    if n_gpus() < nranks:
+        pytest.skip(f"needs {nranks} GPUs")
+    res = run_ranks_nccl(nranks, settings(n, grid, stencil, strong_threshold=theta))
+    compare_with_oracle(res, n, grid, stencil, theta)
+
+
+def compare_with_oracle(res, n, grid, stencil, theta):
     o = Oracle(strong_threshold=theta)
     o.threads(8)
     o.gen_laplace(n, p=grid, stencil=stencil)
