@@ -79,6 +79,26 @@ HYPRE_Int b200hypre_comm_init_shm(HYPRE_Int rank, HYPRE_Int nranks, const char *
   API_ARG(nranks == 1 || name, "b200hypre_comm_init_shm: segment name required when nranks > 1");
   API_BEGIN comm_init_shm(rank, nranks, name, slot_bytes); API_END
 }
+HYPRE_Int b200hypre_device_info(char *name, HYPRE_Int name_cap, int *device, int *count, int *cc_major, int *cc_minor, double *free_gb,
+                                double *total_gb) {
+  API_BEGIN
+  ensure_init();
+  cudaDeviceProp prop;
+  int dev = 0, cnt = 0;
+  size_t fr = 0, tot = 0;
+  B200_CUDA(cudaGetDevice(&dev));
+  B200_CUDA(cudaGetDeviceCount(&cnt));
+  B200_CUDA(cudaGetDeviceProperties(&prop, dev));
+  B200_CUDA(cudaMemGetInfo(&fr, &tot));
+  if (name && name_cap > 0) { strncpy(name, prop.name, name_cap - 1); name[name_cap - 1] = 0; }
+  if (device) *device = dev;
+  if (count) *count = cnt;
+  if (cc_major) *cc_major = prop.major;
+  if (cc_minor) *cc_minor = prop.minor;
+  if (free_gb) *free_gb = fr / 1.e9;
+  if (total_gb) *total_gb = tot / 1.e9;
+  API_END
+}
 HYPRE_Int b200hypre_comm_init_from_env(void) { API_BEGIN comm_init_from_env(); API_END }
 HYPRE_Int b200hypre_comm_finalize(void) { API_BEGIN comm_finalize(); API_END }
 HYPRE_Int b200hypre_comm_rank(void) { return ctx().rank; }

@@ -233,6 +233,10 @@ void comm_init_from_env() {
   int ndev = 1;
   B200_CUDA(cudaGetDeviceCount(&ndev));
   B200_CUDA(cudaSetDevice((lr ? atoi(lr) : rank) % ndev));
+  if (const char *shm = getenv("B200_COMM_SHM")) {  // N ranks on one GPU (tests): host-staged transport, comm_shm.cu
+    comm_init_shm(rank, nranks, shm, 0);
+    return;
+  }
   const char *addr = getenv("MASTER_ADDR");
   const char *port = getenv("MASTER_PORT");
   int p = (port ? atoi(port) : 29500) + 23;

@@ -58,6 +58,10 @@ HYPRE_Int b200hypre_gmres_set_orthogonalization(HYPRE_Solver gmres, HYPRE_Int ki
 HYPRE_Int b200hypre_gmres_get_history(HYPRE_Solver gmres, HYPRE_Real *out, HYPRE_Int cap);   /* returns the history length */
 HYPRE_Real b200hypre_gmres_solve_seconds(HYPRE_Solver gmres);
 
+/* device name / compute capability / memory of the device this rank runs on (the checkMemory() print, HypreSystem.cpp:638-671) */
+HYPRE_Int b200hypre_device_info(char *name, HYPRE_Int name_cap, int *device, int *count, int *cc_major, int *cc_minor, double *free_gb,
+                                double *total_gb);
+
 /* ---- instrumentation ------------------------------------------------------------------------------------------------------- */
 unsigned long long b200hypre_launch_count(void);   /* kernels launched by the library so far */
 /* kernel-class timing with CUDA events on the library stream: scopes whose algorithmic byte count is >= min_bytes are

@@ -1,0 +1,220 @@
+"""GPU tests of hypre_app (the C++ host twin of the reference's main.cpp / HypreSystem over the C ABI): MatrixMarket and
+HYPRE-IJ load paths, the generator, complex -> real expansion, the all-close check against a reference solution,
+AMG level dumps, CSV timers, and a 2-rank run (ranks share cuda:0 over the shm transport)."""
+import os
+import re
+import subprocess
+import uuid
+
+import numpy as np
+import pytest
+import scipy.sparse as sp
+import scipy.sparse.linalg as spla
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "hypre-mini-app_b200", "bin", "hypre_app")
+
+
+@pytest.fixture(scope="module")
+def app():
+    if not os.path.exists(BIN):
+        subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "hypre-mini-app_b200")])
+        subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "hypre-mini-app_b200", "app")])
+    return BIN
+
+
+def laplace3d(n):
+    e = np.ones(n)
+    t = sp.diags([-e[:-1], 2 * e, -e[:-1]], [-1, 0, 1])
+    i = sp.identity(n)
+    return (sp.kron(sp.kron(i, i), t) + sp.kron(sp.kron(i, t), i) + sp.kron(sp.kron(t, i), i)).tocsr()
+
+
+def write_mm_matrix(path, A, complex_vals=False, shuffle=None):
+    A = A.tocoo()
+    idx = np.arange(A.nnz) if shuffle is None else shuffle.permutation(A.nnz)
+    with open(path, "w") as f:
+        f.write(f"%%MatrixMarket matrix coordinate {'complex' if complex_vals else 'real'} general\n% written by the test\n")
+        f.write(f"{A.shape[0]} {A.shape[1]} {A.nnz}\n")
+        for k in idx:
+            v = A.data[k]
+            if complex_vals:
+                f.write(f"{A.row[k] + 1} {A.col[k] + 1} {v.real:.17g} {v.imag:.17g}\n")
+            else:
+                f.write(f"{A.row[k] + 1} {A.col[k] + 1} {v:.17g}\n")
+
+
+def write_mm_vector(path, v, complex_vals=False):
+    with open(path, "w") as f:
+        f.write(f"%%MatrixMarket matrix array {'complex' if complex_vals else 'real'} general\n%\n{len(v)} 1\n")
+        for x in v:
+            f.write(f"{x.real:.17g} {x.imag:.17g}\n" if complex_vals else f"{x:.17g}\n")
+
+
+YAML_TMPL = """linear_system:
+{linsys}
+solver_settings:
+  method: gmres
+  preconditioner: {precond}
+  tolerance: 1.0e-10
+  max_iterations: 200
+  kspace: 50
+  print_level: 0
+{solver_extra}
+boomeramg_settings:
+  print_level: 0
+  coarsen_type: 8
+  interp_type: 6
+  relax_type: 18
+  relax_order: 0
+  strong_threshold: 0.25
+"""
+
+
+def run_app(app, workdir, linsys, precond="boomeramg", solver_extra="", nranks=1):
+    y = os.path.join(workdir, "in.yaml")
+    with open(y, "w") as f:
+        f.write(YAML_TMPL.format(linsys="\n".join("  " + l for l in linsys), precond=precond, solver_extra=solver_extra))
+    if nranks == 1:
+        r = subprocess.run([app, y], cwd=workdir, capture_output=True, text=True, timeout=600)
+        return r.returncode, r.stdout + r.stderr
+    name = "/b200app-" + uuid.uuid4().hex[:10]
+    procs = []
+    for k in range(nranks):
+        env = dict(os.environ, RANK=str(k), WORLD_SIZE=str(nranks), LOCAL_RANK="0", B200_COMM_SHM=name)
+        procs.append(subprocess.Popen([app, y], cwd=workdir, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+    outs = [p.communicate(timeout=600)[0] for p in procs]
+    return max(p.returncode for p in procs), outs[0] + "".join(outs[1:])
+
+
+def iterations(out):
+    m = re.search(r"iterations = (\d+)", out)
+    return int(m.group(1))
+
+
+def test_matrix_market_path_with_reference_solution(app, tmp_path):
+    n = 12
+    A = laplace3d(n)
+    rng = np.random.default_rng(7)
+    xref = rng.standard_normal(A.shape[0])
+    b = A @ xref
+    write_mm_matrix(tmp_path / "mat.mm", A, shuffle=rng)   # unsorted file order, as MatrixMarket files may be
+    write_mm_vector(tmp_path / "rhs.mm", b)
+    write_mm_vector(tmp_path / "sln.mm", xref)
+    rc, out = run_app(app, str(tmp_path), ["type: matrix_market", "matrix_file: mat.mm", "rhs_file: rhs.mm", "sln_file: sln.mm",
+                                           "rtol: 1.0e-6", "atol: 1.0e-8", "write_solution: true"],
+                      solver_extra="  csv_profile_file: timers.csv\n  num_tests: 2")
+    assert rc == 0, out
+    assert "allClose=1" in out and "Timer summary" in out and "Preconditioner setup" in out
+    assert iterations(out) < 25
+    # written solution (HYPRE_IJVectorPrint grammar) equals the reference solution
+    sol = np.loadtxt(tmp_path / "IJV0.sln.00000", skiprows=1)
+    assert np.abs(sol[:, 1] - xref).max() < 1e-6
+    csv = (tmp_path / "timers.csv").read_text().splitlines()
+    assert "Solve" in csv[0].split(",") and len(csv) == 3
+
+
+def test_wrong_reference_solution_is_flagged(app, tmp_path):
+    A = laplace3d(8)
+    x = np.ones(A.shape[0])
+    write_mm_matrix(tmp_path / "mat.mm", A)
+    write_mm_vector(tmp_path / "rhs.mm", A @ x)
+    write_mm_vector(tmp_path / "sln.mm", x * 1.01)
+    rc, out = run_app(app, str(tmp_path), ["type: matrix_market", "matrix_file: mat.mm", "rhs_file: rhs.mm", "sln_file: sln.mm"])
+    assert rc == 2 and "allClose=0" in out
+
+
+def test_hypre_ij_path_two_partitions_and_level_dump(app, tmp_path):
+    n = 10
+    A = laplace3d(n).tocsr()
+    N = A.shape[0]
+    x = np.linspace(1.0, 2.0, N)
+    b = A @ x
+    half = N // 2 + 3
+    for p, (lo, hi) in enumerate([(0, half - 1), (half, N - 1)]):
+        with open(tmp_path / f"A.ij.{p:05d}", "w") as f:
+            f.write(f"{lo} {hi} {lo} {hi}\n")
+            for i in range(lo, hi + 1):
+                for k in range(A.indptr[i], A.indptr[i + 1]):
+                    f.write(f"{i} {A.indices[k]} {A.data[k]:.14e}\n")
+        for name, v in (("b.ij", b), ("x.ij", x)):
+            with open(tmp_path / f"{name}.{p:05d}", "w") as f:
+                f.write(f"{lo} {hi}\n")
+                for i in range(lo, hi + 1):
+                    f.write(f"{i} {v[i]:.14e}\n")
+    rc, out = run_app(app, str(tmp_path), ["type: hypre_ij", "matrix_file: A.ij", "rhs_file: b.ij", "sln_file: x.ij", "num_partitions: 2",
+                                           "write_amg_matrices: true", "write_outputs: true"])
+    assert rc == 0, out
+    assert "allClose=1" in out
+    # level 0 dump == input matrix; deeper levels exist and shrink (HypreSystem.cpp:700-714 naming)
+    lvl0 = np.loadtxt(tmp_path / "A_level_0.IJ.00000", skiprows=1)
+    B = sp.csr_matrix((lvl0[:, 2], (lvl0[:, 0].astype(int), lvl0[:, 1].astype(int))), shape=A.shape)
+    assert abs(B - A).max() < 1e-12
+    assert os.path.exists(tmp_path / "A_level_1.IJ.00000")
+    # IJM.mat written by write_outputs round-trips
+    m = np.loadtxt(tmp_path / "IJM.mat.00000", skiprows=1)
+    assert len(m) == A.nnz
+
+
+def test_generator_path_and_no_preconditioner(app, tmp_path):
+    rc, out = run_app(app, str(tmp_path), ["type: build_7pt_stencil", "nx: 16", "ny: 16", "nz: 16", "write_solution: true"])
+    assert rc == 0, out
+    sol = np.loadtxt(tmp_path / "IJV0.sln.00000", skiprows=1)
+    assert np.abs(sol[:, 1] - 1.0).max() < 1e-7   # generator known answer
+    its_amg = iterations(out)
+    rc, out = run_app(app, str(tmp_path), ["type: build_27pt_stencil", "nx: 10", "ny: 10", "nz: 10"], precond="none")
+    assert rc == 0, out
+    assert iterations(out) > its_amg
+
+
+def test_complex_matrix_market_expansion(app, tmp_path):
+    """complex entries become real 2x2 blocks (HypreSystem.cpp:1800-1833): solve (A + iB)(x + iy) = b and compare"""
+    n = 6
+    A = laplace3d(n).astype(complex)
+    A = (A + 0.3j * sp.identity(A.shape[0])).tocsr()
+    rng = np.random.default_rng(3)
+    z = rng.standard_normal(A.shape[0]) + 1j * rng.standard_normal(A.shape[0])
+    b = A @ z
+    write_mm_matrix(tmp_path / "mat.mm", A, complex_vals=True)
+    write_mm_vector(tmp_path / "rhs.mm", b, complex_vals=True)
+    write_mm_vector(tmp_path / "sln.mm", z, complex_vals=True)
+    rc, out = run_app(app, str(tmp_path), ["type: matrix_market", "matrix_file: mat.mm", "rhs_file: rhs.mm", "sln_file: sln.mm",
+                                           "complex_numbers: true", "write_solution: true"])
+    assert rc == 0, out
+    assert "allClose=1" in out
+    sol = np.loadtxt(tmp_path / "IJV0.sln.00000", skiprows=1)[:, 1]
+    assert np.abs(sol[0::2] - z.real).max() < 1e-6 and np.abs(sol[1::2] - z.imag).max() < 1e-6
+
+
+def test_segregated_components_share_one_matrix(app, tmp_path):
+    A = laplace3d(8)
+    rng = np.random.default_rng(5)
+    xs = [rng.standard_normal(A.shape[0]) for _ in range(3)]
+    write_mm_matrix(tmp_path / "mat.mm", A)
+    lines = ["type: matrix_market", "matrix_file: mat.mm", "num_components: 3", "segregated_solve: 1"]
+    for k, x in enumerate(xs):
+        write_mm_vector(tmp_path / f"rhs{k}.mm", A @ x)
+        write_mm_vector(tmp_path / f"sln{k}.mm", x)
+        lines += [f"rhs_file{k}: rhs{k}.mm", f"sln_file{k}: sln{k}.mm"]
+    rc, out = run_app(app, str(tmp_path), lines)
+    assert rc == 0, out
+    assert out.count("allClose=1") == 3
+
+
+def test_two_ranks_matrix_market(app, tmp_path):
+    A = laplace3d(10)
+    rng = np.random.default_rng(11)
+    x = rng.standard_normal(A.shape[0])
+    write_mm_matrix(tmp_path / "mat.mm", A, shuffle=rng)
+    write_mm_vector(tmp_path / "rhs.mm", A @ x)
+    write_mm_vector(tmp_path / "sln.mm", x)
+    rc, out = run_app(app, str(tmp_path), ["type: matrix_market", "matrix_file: mat.mm", "rhs_file: rhs.mm", "sln_file: sln.mm",
+                                           "write_solution: true"], nranks=2)
+    assert rc == 0, out
+    assert "allClose=1" in out
+    s0 = np.loadtxt(tmp_path / "IJV0.sln.00000", skiprows=1)
+    s1 = np.loadtxt(tmp_path / "IJV0.sln.00001", skiprows=1)
+    sol = np.concatenate([s0[:, 1], s1[:, 1]])
+    assert np.abs(sol - x).max() < 1e-6
