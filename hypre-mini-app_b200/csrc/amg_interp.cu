@@ -57,14 +57,31 @@ __device__ __forceinline__ void h_insert(int *keys, short *spos, int key, int po
   }
 }
 
+// group-relative ballot: bit t = predicate of lane t of this group
+template <int G>
+__device__ __forceinline__ unsigned gballot(unsigned gm, int first_lane, bool pred) {
+  unsigned b = __ballot_sync(gm, pred) & gm;
+  return b >> first_lane;
+}
+
 // lraw: |C-hat_i| before truncation; -1 = not computed yet (the row did not fit the tiers tried so far).
-// COUNT: rows with lraw == -1 are processed, lraw / len are written.  FILL: rows with lo < lraw <= CAP.
-template <int G, int H, int CAP, bool COUNT>
+// MODE 0 (count):  rows with lraw == -1; discovery only (valid when trunc_factor == 0); writes lraw / len.
+// MODE 1 (fill):   rows with lo < lraw <= CAP; writes the row at Pptr[i].
+// MODE 2 (single): rows with lraw == -1; whole row in one pass, written at i * pmax (needs pmax > 0: the truncated row has
+//                  at most pmax entries), lraw / len recorded; a compaction kernel builds the CSR afterwards.
+// Scf[k] = cf[Scol[k]] (signed char), precomputed so that a strength row and the markers of its columns arrive together.
+//
+// Latency structure: the strong neighbours of i (discovery) and the entries of row i (weights) are loaded G at a time, one
+// per lane, together with everything that only depends on them (marker, row extents, hash position); the loops that fix
+// the operation order then run over shuffled registers, and the first G entries of the NEXT neighbour row are requested
+// before the current one is processed.
+template <int G, int H, int CAP, int MODE>
 __global__ void __launch_bounds__(256) k_interp_grp(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__ Scol,
-                                                    const int *__restrict__ cf, const int *__restrict__ f2c, int n_own, int n_rows,
-                                                    double tf, int pmax, int lo, int *lraw, int *len, const int *__restrict__ Pptr,
-                                                    int *Pcol, double *Pval) {
+                                                    const signed char *__restrict__ Scf, const int *__restrict__ cf,
+                                                    const int *__restrict__ f2c, int n_own, int n_rows, double tf, int pmax, int lo,
+                                                    int *lraw, int *len, const int *__restrict__ Pptr, int *Pcol, double *Pval) {
   constexpr int GROUPS = 256 / G;
+  constexpr bool COUNT = (MODE == 0);
   __shared__ int s_keys[GROUPS][H];
   __shared__ short s_pos[GROUPS][H];
   __shared__ int s_lc[GROUPS][CAP];
@@ -75,7 +92,7 @@ __global__ void __launch_bounds__(256) k_interp_grp(rows::Csr A, const int *__re
   const unsigned gm = group_mask<G>();
   const unsigned lane_lt = gm & ((1u << (threadIdx.x & 31)) - 1u);
   const int first_lane = (threadIdx.x & 31) - lane;
-  if (COUNT) {
+  if (MODE != 1) {
     if (lraw[i] != -1) return;
   } else {
     int l = lraw[i];
@@ -84,16 +101,16 @@ __global__ void __launch_bounds__(256) k_interp_grp(rows::Csr A, const int *__re
   const int cfi = cf[i];
   if (cfi >= 0) {
     if (lane == 0) {
-      if (COUNT) { lraw[i] = 0; len[i] = 1; }
-      else { int b = Pptr[i]; Pcol[b] = f2c[i]; Pval[b] = 1.0; }
+      if (MODE != 1) { lraw[i] = 0; len[i] = 1; }
+      if (MODE != 0) { size_t b = (MODE == 1) ? (size_t)Pptr[i] : (size_t)i * pmax; Pcol[b] = f2c[i]; Pval[b] = 1.0; }
     }
     return;
   }
   if (cfi == -3) {
-    if (COUNT && lane == 0) { lraw[i] = 0; len[i] = 0; }
+    if (MODE != 1 && lane == 0) { lraw[i] = 0; len[i] = 0; }
     return;
   }
-  if (!COUNT && Pptr[i + 1] == Pptr[i]) return;
+  if (MODE == 1 && Pptr[i + 1] == Pptr[i]) return;
   int *keys = s_keys[g];
   short *spos = s_pos[g];
   int *lc = s_lc[g];
@@ -105,40 +122,66 @@ __global__ void __launch_bounds__(256) k_interp_grp(rows::Csr A, const int *__re
   int L = 0;
   bool any_off = false, ovf = false;
   const int sb = Sptr[i], se = Sptr[i + 1];
-  for (int kk = sb; kk < se && !ovf; ++kk) {
-    const int i1 = Scol[kk];
-    const int c1 = cf[i1];
-    if (c1 >= 0) {
-      if (h_probe<H>(keys, spos, i1) < 0) {
-        if (L == CAP) { ovf = true; break; }
-        __syncwarp(gm);  // every lane has finished probing before the table changes
-        if (lane == 0) { h_insert<H>(keys, spos, i1, L); lc[L] = i1; }
-        any_off |= (i1 >= n_own);
-        ++L;
-        __syncwarp(gm);
-      }
-    } else if (c1 != -3) {
-      const int b2 = Sptr[i1], e2 = Sptr[i1 + 1];
-      for (int base = b2; base < e2; base += G) {
-        const int k2 = base + lane;
-        int k1 = -1;
-        bool isnew = false;
-        if (k2 < e2) {
-          k1 = Scol[k2];
-          if (cf[k1] >= 0) isnew = (h_probe<H>(keys, spos, k1) < 0);
-        }
-        const unsigned nm = __ballot_sync(gm, isnew) & gm;
-        const int cnt = __popc(nm);
-        if (cnt) {
-          if (L + cnt > CAP) { ovf = true; break; }
-          if (isnew) {
-            int pos = L + __popc(nm & lane_lt);
-            h_insert<H>(keys, spos, k1, pos);
-            lc[pos] = k1;
-          }
-          any_off |= ((__ballot_sync(gm, isnew && k1 >= n_own) & gm) != 0u);
-          L += cnt;
+  for (int cb = sb; cb < se && !ovf; cb += G) {
+    const int kk = cb + lane;
+    int i1_l = -1, c1_l = -3, b2_l = 0, e2_l = 0;
+    if (kk < se) {
+      i1_l = Scol[kk];
+      c1_l = Scf[kk];
+      if (c1_l < 0 && c1_l != -3) { b2_l = Sptr[i1_l]; e2_l = Sptr[i1_l + 1]; }
+    }
+    const int nstep = min(G, se - cb);
+    const unsigned fm = gballot<G>(gm, first_lane, c1_l < 0 && c1_l != -3);   // strong F neighbours of this chunk
+    int tnext = fm ? (__ffs(fm) - 1) : -1;
+    int b2n = 0, e2n = 0, k1n = -1, cfkn = 0;
+    if (tnext >= 0) {
+      b2n = __shfl_sync(gm, b2_l, tnext, G);
+      e2n = __shfl_sync(gm, e2_l, tnext, G);
+      if (b2n + lane < e2n) { k1n = Scol[b2n + lane]; cfkn = Scf[b2n + lane]; }
+    }
+    for (int t = 0; t < nstep && !ovf; ++t) {
+      const int c1 = __shfl_sync(gm, c1_l, t, G);
+      if (c1 >= 0) {
+        const int i1 = __shfl_sync(gm, i1_l, t, G);
+        if (h_probe<H>(keys, spos, i1) < 0) {
+          if (L == CAP) { ovf = true; break; }
+          __syncwarp(gm);  // every lane has finished probing before the table changes
+          if (lane == 0) { h_insert<H>(keys, spos, i1, L); lc[L] = i1; }
+          any_off |= (i1 >= n_own);
+          ++L;
           __syncwarp(gm);
+        }
+      } else if (c1 != -3) {
+        const int b2 = b2n, e2 = e2n;
+        int k1 = k1n, cfk = cfkn;
+        const unsigned rest = (t >= 31) ? 0u : (fm & ~((2u << t) - 1u));
+        tnext = rest ? (__ffs(rest) - 1) : -1;
+        k1n = -1;
+        if (tnext >= 0) {   // request the next F neighbour's strength row before working on this one
+          b2n = __shfl_sync(gm, b2_l, tnext, G);
+          e2n = __shfl_sync(gm, e2_l, tnext, G);
+          if (b2n + lane < e2n) { k1n = Scol[b2n + lane]; cfkn = Scf[b2n + lane]; }
+        }
+        for (int base = b2; base < e2; base += G) {
+          if (base != b2) {
+            k1 = -1;
+            if (base + lane < e2) { k1 = Scol[base + lane]; cfk = Scf[base + lane]; }
+          }
+          bool isnew = false;
+          if (k1 >= 0 && cfk >= 0) isnew = (h_probe<H>(keys, spos, k1) < 0);
+          const unsigned nm = __ballot_sync(gm, isnew) & gm;
+          const int cnt = __popc(nm);
+          if (cnt) {
+            if (L + cnt > CAP) { ovf = true; break; }
+            if (isnew) {
+              int pos = L + __popc(nm & lane_lt);
+              h_insert<H>(keys, spos, k1, pos);
+              lc[pos] = k1;
+            }
+            any_off |= ((__ballot_sync(gm, isnew && k1 >= n_own) & gm) != 0u);
+            L += cnt;
+            __syncwarp(gm);
+          }
         }
       }
     }
@@ -183,66 +226,108 @@ __global__ void __launch_bounds__(256) k_interp_grp(rows::Csr A, const int *__re
   __syncwarp(gm);
   const int ab = A.ptr[i], ae = A.ptr[i + 1];
   double diagonal = A.val[ab];
-  int sp = sb;
-  for (int jj = ab + 1; jj < ae; ++jj) {
-    const int i1 = A.col[jj];
-    const double aij = A.val[jj];
-    const bool strong = (sp < se) && (Scol[sp] == i1);
-    if (strong) ++sp;
-    const int pos = h_probe<H>(keys, spos, i1);
-    if (pos >= 0) {
-      if (lane == 0) lv[pos] = lv[pos] + aij;
-      __syncwarp(gm);
-      continue;
+  for (int cb = ab + 1; cb < ae; cb += G) {
+    const int jj = cb + lane;
+    const bool valid = jj < ae;
+    int i1_l = -1, pos_l = -1, kind_l = 3, b1_l = 0, e1_l = 0;
+    double aij_l = 0.0;
+    if (valid) { i1_l = A.col[jj]; aij_l = A.val[jj]; }
+    // strong_l: is the column of this entry in the strength row of i (S rows are subsequences of A rows)
+    bool strong_l = false;
+    for (int scb = sb; scb < se; scb += G) {
+      const int s_l = (scb + lane < se) ? Scol[scb + lane] : -1;
+      const int ns = min(G, se - scb);
+      for (int u = 0; u < ns; ++u) strong_l |= (__shfl_sync(gm, s_l, u, G) == i1_l);
     }
-    const int c1 = cf[i1];
-    if (strong && c1 < 0 && c1 != -3) {
-      const int b1 = A.ptr[i1], e1 = A.ptr[i1 + 1];
-      const double sgn = (A.val[b1] < 0) ? -1.0 : 1.0;
-      double sum = 0.0;
-      for (int base = b1 + 1; base < e1; base += G) {
-        const int j1 = base + lane;
-        bool m = false;
-        double a = 0.0;
-        if (j1 < e1) {
-          a = A.val[j1];
-          if ((sgn * a) < 0) {
-            int i2 = A.col[j1];
-            m = (i2 == i) || (h_probe<H>(keys, spos, i2) >= 0);
-          }
-        }
-        unsigned mm = __ballot_sync(gm, m) & gm;
-        while (mm) {  // storage-order sum of the contributing entries
-          int src = __ffs(mm) - 1;
-          mm &= mm - 1;
-          sum = sum + __shfl_sync(gm, a, src);
-        }
+    if (valid) {
+      pos_l = h_probe<H>(keys, spos, i1_l);
+      if (pos_l >= 0) kind_l = 0;                       // direct: a_ij goes to its own C point
+      else {
+        const int c1 = cf[i1_l];
+        if (strong_l && c1 < 0 && c1 != -3) { kind_l = 1; b1_l = A.ptr[i1_l]; e1_l = A.ptr[i1_l + 1]; }   // distribute over C-hat
+        else if (c1 != -3) kind_l = 2;                  // lumped into the diagonal
       }
-      if (sum != 0.0) {
-        const double distribute = aij / sum;
-        for (int base = b1 + 1; base < e1; base += G) {
-          const int j1 = base + lane;
-          bool is_i = false;
-          double t = 0.0;
-          if (j1 < e1) {
-            double a = A.val[j1];
-            if ((sgn * a) < 0) {
-              int i2 = A.col[j1];
-              t = distribute * a;
-              int p2 = h_probe<H>(keys, spos, i2);
-              if (p2 >= 0) lv[p2] = lv[p2] + t;
-              is_i = (i2 == i);
-            }
-          }
-          unsigned mi = __ballot_sync(gm, is_i) & gm;
-          if (mi) diagonal = diagonal + __shfl_sync(gm, t, __ffs(mi) - 1);
+    }
+    const int nstep = min(G, ae - cb);
+    const unsigned fm = gballot<G>(gm, first_lane, kind_l == 1);
+    int tnext = fm ? (__ffs(fm) - 1) : -1;
+    int b1n = 0, e1n = 0, i2n = -1;
+    double an = 0.0;
+    if (tnext >= 0) {
+      b1n = __shfl_sync(gm, b1_l, tnext, G);
+      e1n = __shfl_sync(gm, e1_l, tnext, G);
+      if (b1n + lane < e1n) { i2n = A.col[b1n + lane]; an = A.val[b1n + lane]; }
+    }
+    for (int t = 0; t < nstep; ++t) {
+      const int kind = __shfl_sync(gm, kind_l, t, G);
+      const double aij = __shfl_sync(gm, aij_l, t, G);
+      if (kind == 0) {
+        const int pos = __shfl_sync(gm, pos_l, t, G);
+        if (lane == 0) lv[pos] = lv[pos] + aij;
+        __syncwarp(gm);
+      } else if (kind == 1) {
+        const int b1 = b1n, e1 = e1n;
+        int i2 = i2n;
+        double a = an;
+        const unsigned rest = (t >= 31) ? 0u : (fm & ~((2u << t) - 1u));
+        tnext = rest ? (__ffs(rest) - 1) : -1;
+        i2n = -1;
+        if (tnext >= 0) {   // request the next neighbour row before working on this one
+          b1n = __shfl_sync(gm, b1_l, tnext, G);
+          e1n = __shfl_sync(gm, e1_l, tnext, G);
+          if (b1n + lane < e1n) { i2n = A.col[b1n + lane]; an = A.val[b1n + lane]; }
         }
-      } else {
+        // lane 0 of the first chunk holds the neighbour's diagonal entry
+        const double dsgn = __shfl_sync(gm, a, 0, G);
+        const double sgn = (dsgn < 0) ? -1.0 : 1.0;
+        const bool one_chunk = (e1 - b1) <= G;
+        double sum = 0.0;
+        int p2 = -1;
+        bool is_i = false, m = false;
+        for (int base = b1; base < e1; base += G) {
+          const int j1 = base + lane;
+          if (base != b1) { i2 = -1; a = 0.0; if (j1 < e1) { i2 = A.col[j1]; a = A.val[j1]; } }
+          m = false; p2 = -1; is_i = false;
+          if (j1 < e1 && j1 > b1 && (sgn * a) < 0) {
+            is_i = (i2 == i);
+            p2 = h_probe<H>(keys, spos, i2);
+            m = is_i || (p2 >= 0);
+          }
+          unsigned mm = __ballot_sync(gm, m) & gm;
+          while (mm) {  // storage-order sum of the contributing entries
+            int src = __ffs(mm) - 1;
+            mm &= mm - 1;
+            sum = sum + __shfl_sync(gm, a, src);
+          }
+        }
+        if (sum != 0.0) {
+          const double distribute = aij / sum;
+          for (int base = b1; base < e1; base += G) {
+            const int j1 = base + lane;
+            if (!one_chunk) {
+              i2 = -1; a = 0.0; m = false; p2 = -1; is_i = false;
+              if (j1 < e1) { i2 = A.col[j1]; a = A.val[j1]; }
+              if (j1 < e1 && j1 > b1 && (sgn * a) < 0) {
+                is_i = (i2 == i);
+                p2 = h_probe<H>(keys, spos, i2);
+                m = is_i || (p2 >= 0);
+              }
+            }
+            double tt = 0.0;
+            if (m) {
+              tt = distribute * a;
+              if (p2 >= 0) lv[p2] = lv[p2] + tt;
+            }
+            unsigned mi = __ballot_sync(gm, m && is_i) & gm;
+            if (mi) diagonal = diagonal + __shfl_sync(gm, tt, __ffs(mi) - 1);
+          }
+        } else {
+          diagonal = diagonal + aij;
+        }
+        __syncwarp(gm);
+      } else if (kind == 2) {
         diagonal = diagonal + aij;
       }
-      __syncwarp(gm);
-    } else if (c1 != -3) {
-      diagonal = diagonal + aij;
     }
   }
   __syncwarp(gm);
@@ -296,11 +381,11 @@ __global__ void __launch_bounds__(256) k_interp_grp(rows::Csr A, const int *__re
   }
   __syncwarp(gm);
   n_out = __shfl_sync(gm, n_out, first_lane);
-  if (COUNT) {
+  if (MODE != 1) {
     if (lane == 0) { lraw[i] = L; len[i] = n_out; }
-    return;
+    if (MODE == 0) return;
   }
-  const int b = Pptr[i];
+  const size_t b = (MODE == 1) ? (size_t)Pptr[i] : (size_t)i * pmax;
   for (int k = lane; k < n_out; k += G) {
     Pcol[b + k] = f2c[lc[k]];
     Pval[b + k] = lv[k];
@@ -341,18 +426,33 @@ T fetch1(const T *dev) {
   return h;
 }
 
-template <bool COUNT>
-void launch_tiers(bool small_tier, const rows::Csr &A, const int *Sptr, const int *Scol, const int *cf, const int *f2c, int n_own,
-                  int n_rows, double tf, int pmax, int *lraw, int *len, const int *Pptr, int *Pcol, double *Pval) {
+__global__ void k_scf(i64 nnz, const int *__restrict__ Scol, const int *__restrict__ cf, signed char *__restrict__ Scf) {
+  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < nnz) Scf[k] = (signed char)cf[Scol[k]];
+}
+// single-pass rows live at i * pmax in the scratch arrays: copy them to their CSR position
+__global__ void k_compact_p(int n_rows, int pmax, const int *__restrict__ lraw, const int *__restrict__ Pptr, const int *__restrict__ tcol,
+                            const double *__restrict__ tval, int *__restrict__ Pcol, double *__restrict__ Pval) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_rows || lraw[i] == -1) return;
+  const int b = Pptr[i], n = Pptr[i + 1] - b;
+  const size_t src = (size_t)i * pmax;
+  for (int k = 0; k < n; ++k) { Pcol[b + k] = tcol[src + k]; Pval[b + k] = tval[src + k]; }
+}
+
+template <int MODE>
+void launch_tiers(bool small_tier, const rows::Csr &A, const int *Sptr, const int *Scol, const signed char *Scf, const int *cf,
+                  const int *f2c, int n_own, int n_rows, double tf, int pmax, int *lraw, int *len, const int *Pptr, int *Pcol,
+                  double *Pval) {
   int lo = -1;
   if (small_tier) {
-    k_interp_grp<8, 64, 32, COUNT><<<div_up(n_rows, 32), 256, 0, stream()>>>(A, Sptr, Scol, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw,
-                                                                           len, Pptr, Pcol, Pval);
+    k_interp_grp<8, 64, 32, MODE><<<div_up(n_rows, 32), 256, 0, stream()>>>(A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo,
+                                                                          lraw, len, Pptr, Pcol, Pval);
     count_launch();
     lo = 32;
   }
-  k_interp_grp<32, 256, 128, COUNT><<<div_up(n_rows, 8), 256, 0, stream()>>>(A, Sptr, Scol, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw,
-                                                                            len, Pptr, Pcol, Pval);
+  k_interp_grp<32, 256, 128, MODE><<<div_up(n_rows, 8), 256, 0, stream()>>>(A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo,
+                                                                           lraw, len, Pptr, Pcol, Pval);
   count_launch();
   B200_KERNEL_CHECK();
 }
@@ -361,6 +461,8 @@ void launch_tiers(bool small_tier, const rows::Csr &A, const int *Sptr, const in
 
 // Interpolation rows [0, n_rows) of the (extended) level: A, S, cf, f2c are indexed by extended fine ids, ids below
 // n_own are this rank's own points; f2c gives the output column of a C point.  P.nc must be set by the caller.
+// With P_max_elmts > 0 every truncated row has at most pmax entries, so the tiers run ONCE writing fixed-stride rows that
+// are compacted afterwards; otherwise a counting pass (discovery only) precedes the fill pass.
 void build_interp(const DCsr &Aext, const int *Sptr, const int *Scol, i64 S_nnz, const int *cf, const int *f2c, int n_own, int n_rows,
                   double tf, int pmax, DCsr &P) {
   rows::Csr A{Aext.nr, Aext.nc, Aext.ptr.p, Aext.col.p, Aext.val.p};
@@ -368,10 +470,24 @@ void build_interp(const DCsr &Aext, const int *Sptr, const int *Scol, i64 S_nnz,
   P.ptr.alloc((size_t)n_rows + 1);
   if (n_rows == 0) { P.nnz = 0; P.ptr.zero(); return; }
   const bool small_tier = (double)S_nnz <= 8.0 * (double)Aext.nr;
+  const bool single = pmax > 0;
+  DVec<signed char> Scf((size_t)std::max<i64>(S_nnz, 1));
+  if (S_nnz > 0) {
+    k_scf<<<div_up(S_nnz, 256), 256, 0, stream()>>>(S_nnz, Scol, cf, Scf.p);
+    count_launch();
+  }
   DVec<int> lraw((size_t)n_rows), len((size_t)n_rows + 1);
   B200_CUDA(cudaMemsetAsync(lraw.p, 0xFF, sizeof(int) * (size_t)n_rows, stream()));
   B200_CUDA(cudaMemsetAsync(len.p + n_rows, 0, sizeof(int), stream()));
-  launch_tiers<true>(small_tier, A, Sptr, Scol, cf, f2c, n_own, n_rows, tf, pmax, lraw.p, len.p, nullptr, nullptr, nullptr);
+  DVec<int> tcol;
+  DVec<double> tval;
+  if (single) {
+    tcol.alloc((size_t)n_rows * pmax);
+    tval.alloc((size_t)n_rows * pmax);
+    launch_tiers<2>(small_tier, A, Sptr, Scol, Scf.p, cf, f2c, n_own, n_rows, tf, pmax, lraw.p, len.p, nullptr, tcol.p, tval.p);
+  } else {
+    launch_tiers<0>(small_tier, A, Sptr, Scol, Scf.p, cf, f2c, n_own, n_rows, tf, pmax, lraw.p, len.p, nullptr, nullptr, nullptr);
+  }
   // rows beyond the last tier
   DVec<int> todo_count(1), todo((size_t)65536), err(1);
   todo_count.zero();
@@ -401,7 +517,12 @@ void build_interp(const DCsr &Aext, const int *Sptr, const int *Scol, i64 S_nnz,
   P.nnz = fetch1(P.ptr.p + n_rows);
   P.col.alloc((size_t)std::max<i64>(P.nnz, 1));
   P.val.alloc((size_t)std::max<i64>(P.nnz, 1));
-  launch_tiers<false>(small_tier, A, Sptr, Scol, cf, f2c, n_own, n_rows, tf, pmax, lraw.p, len.p, P.ptr.p, P.col.p, P.val.p);
+  if (single) {
+    k_compact_p<<<div_up(n_rows, 256), 256, 0, stream()>>>(n_rows, pmax, lraw.p, P.ptr.p, tcol.p, tval.p, P.col.p, P.val.p);
+    count_launch();
+  } else {
+    launch_tiers<1>(small_tier, A, Sptr, Scol, Scf.p, cf, f2c, n_own, n_rows, tf, pmax, lraw.p, len.p, P.ptr.p, P.col.p, P.val.p);
+  }
   if (novf > 0) {
     k_interp_ovf<<<div_up(novf, 64), 64, 0, stream()>>>(A, Sptr, Scol, cf, f2c, n_own, tf, pmax, todo.p, novf, sc.p, sv.p, ocap, len.p,
                                                         P.ptr.p, P.col.p, P.val.p, err.p);

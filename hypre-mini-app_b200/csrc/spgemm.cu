@@ -78,6 +78,53 @@ __device__ __forceinline__ void spgemm_row(const rows::Csr &A, const rows::Csr &
   gsync<G>(mask);
   const int ab = A.ptr[row], ae = A.ptr[row + 1];
   int mine = 0;
+  if constexpr (G <= 32) {
+    // Latency restructuring: the entries of the A row are loaded G at a time, one per lane, together with the extent of
+    // the B row each of them selects (independent loads, one round trip for the whole chunk).  The k loop itself stays
+    // sequential -- it fixes the floating-point order -- but gets its operands by shuffle, and the first G entries of the
+    // NEXT B row are requested before the current row is accumulated, so the loop exposes about one memory latency per
+    // chunk instead of three per k.
+    for (int base = ab; base < ae; base += G) {
+      const int ka = base + lane;
+      int k_l = 0, bb_l = 0, be_l = 0;
+      double a_l = 0.0;
+      if (ka < ae) {
+        k_l = A.col[ka];
+        if (NUMERIC) a_l = A.val[ka];
+        bb_l = B.ptr[k_l];
+        be_l = B.ptr[k_l + 1];
+      }
+      const int nstep = min(G, ae - base);
+      int bb = __shfl_sync(mask, bb_l, 0, G), be = __shfl_sync(mask, be_l, 0, G);
+      int c_cur = -1;
+      double v_cur = 0.0;
+      if (bb + lane < be) { c_cur = B.col[bb + lane]; if (NUMERIC) v_cur = B.val[bb + lane]; }
+      for (int t = 0; t < nstep; ++t) {
+        const double a = NUMERIC ? __shfl_sync(mask, a_l, t, G) : 0.0;
+        int bbn = 0, ben = 0, c_nxt = -1;
+        double v_nxt = 0.0;
+        if (t + 1 < nstep) {
+          bbn = __shfl_sync(mask, bb_l, t + 1, G);
+          ben = __shfl_sync(mask, be_l, t + 1, G);
+          if (bbn + lane < ben) { c_nxt = B.col[bbn + lane]; if (NUMERIC) v_nxt = B.val[bbn + lane]; }
+        }
+        if (c_cur >= 0) {
+          bool isnew;
+          int slot = hash_insert(keys, H, c_cur, isnew);
+          if (NUMERIC) vals[slot] = __dadd_rn(vals[slot], __dmul_rn(a, v_cur));
+          else mine += isnew ? 1 : 0;
+        }
+        for (int kb = bb + G + lane; kb < be; kb += G) {  // B rows longer than the group
+          bool isnew;
+          int slot = hash_insert(keys, H, B.col[kb], isnew);
+          if (NUMERIC) vals[slot] = __dadd_rn(vals[slot], __dmul_rn(a, B.val[kb]));
+          else mine += isnew ? 1 : 0;
+        }
+        if (NUMERIC) __syncwarp(mask);
+        bb = bbn; be = ben; c_cur = c_nxt; v_cur = v_nxt;
+      }
+    }
+  } else {
   for (int ka = ab; ka < ae; ++ka) {
     const int k = A.col[ka];
     const double a = NUMERIC ? A.val[ka] : 0.0;
@@ -93,6 +140,7 @@ __device__ __forceinline__ void spgemm_row(const rows::Csr &A, const rows::Csr &
       }
     }
     if (NUMERIC) gsync<G>(mask);
+  }
   }
   if constexpr (!NUMERIC) {
     if (G <= 32) {
@@ -185,7 +233,7 @@ __global__ void k_spgemm_bound(rows::Csr A, rows::Csr B, int *bound) {
 }
 
 // ---- row binning: bin b holds the rows with lim[b-1] < size <= lim[b]; rows of size 0 go nowhere; bin NB = the rest ------
-constexpr int NB = 5;
+constexpr int NB = 7;
 struct BinLimits { int lim[NB]; };
 __device__ __forceinline__ int bin_of(int s, const BinLimits &L) {
   int b = NB;
@@ -370,7 +418,7 @@ void csr_spgemm(const DCsr &A, const DCsr &B, DCsr &C, bool diag_first) {
     k_spgemm_bound<<<div_up(A.nr, 256), 256, 0, stream()>>>(rv(A), rv(B), bound.p);
     count_launch();
     Bins bins;
-    BinLimits L{{32, 128, 512, 2048, 16384}};
+    BinLimits L{{16, 32, 64, 128, 512, 2048, 16384}};
     make_bins(A.nr, bound.p, L, bins);
     spgemm_pass<false>(A, B, bins, L, nullptr, nullptr, nullptr, nnz_row.p, diag_first);
   }
@@ -384,7 +432,7 @@ void csr_spgemm(const DCsr &A, const DCsr &B, DCsr &C, bool diag_first) {
   {
     ProfScope prof("spgemm_numeric", in_bytes + 12.0 * (double)C.nnz + 4.0 * C.nr);
     Bins bins;
-    BinLimits L{{32, 128, 512, 2048, 4096}};
+    BinLimits L{{16, 32, 64, 128, 256, 1024, 4096}};
     make_bins(A.nr, nnz_row.p, L, bins);
     spgemm_pass<true>(A, B, bins, L, C.ptr.p, C.col.p, C.val.p, nullptr, diag_first);
   }

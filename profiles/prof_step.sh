@@ -12,7 +12,7 @@ CMD="python bench.py --size 256 --steps 1 --warmup 1 --no-e2e --no-cpu-baseline"
 $CMD > gpurun_out/plain_$TAG.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 8000 --csv --log-file gpurun_out/launches_$TAG.csv $CMD > gpurun_out/ncu_list_$TAG.log 2>&1
 if [ -n "$RE" ]; then
-  ncu --set full --clock-control none --import-source on -k regex:$RE -s $SKIP -c $CNT -f -o gpurun_out/prof_$TAG $CMD > gpurun_out/ncu_full_$TAG.log 2>&1
+  ncu --set full --clock-control none --import-source on -k "regex:$RE" -s $SKIP -c $CNT -f -o gpurun_out/prof_$TAG $CMD > gpurun_out/ncu_full_$TAG.log 2>&1
 fi
 tail -2 gpurun_out/plain_$TAG.log | cut -c1-600
 tail -3 gpurun_out/ncu_list_$TAG.log gpurun_out/ncu_full_$TAG.log 2>/dev/null
