@@ -1,0 +1,131 @@
+"""Synthetic matrices of BASELINE.json configs[3] and configs[4] (SURVEY.md §8d inputs 4 and 5), scaled by `n`.
+
+TEST / BENCH INPUT GENERATORS ONLY (numpy + scipy on the host); the product reads these systems through the IJ path
+(HypreSystem.cpp:897-1015 semantics) or from MatrixMarket / HYPRE-IJ text written by `write_matrix_market` /
+`write_hypre_ij` (formats: SURVEY.md Appendix C).
+
+* poisson27_hex(n): nalu-wind-like pressure Poisson.  Trilinear-hexahedron Galerkin Laplacian (2x2x2 Gauss) on the
+  n^3 interior nodes of an (n+2)^3 grid with homogeneous Dirichlet boundary; interior nodes displaced by
+  0.2 h U(-1,1) (default_rng(20260)).  27-point stencil, nnz = (3n-2)^3, symmetric positive definite, positive and
+  negative off-diagonals.  rhs = A 1.
+* momentum3(n): nalu-wind-like momentum.  n^3 nodes x 3 DOF, node-blocked 3x3, 7-point first-order upwind
+  advection-diffusion at cell Peclet 2 with velocity (1, 0.5, 0.25) + 0.1 U(-1,1) (default_rng(20261)), a time term
+  on the diagonal, and a weak constant inter-component coupling.  Nonsymmetric, nnz = 9 (7 n^3 - 6 n^2).  rhs = A 1.
+"""
+import numpy as np
+import scipy.sparse as sp
+
+
+def _hex_element_matrices(X):
+    """X: (ne, 8, 3) node coordinates in the usual (xi, eta, zeta) corner order -> (ne, 8, 8) stiffness matrices"""
+    s = np.array([[-1, -1, -1], [1, -1, -1], [1, 1, -1], [-1, 1, -1], [-1, -1, 1], [1, -1, 1], [1, 1, 1], [-1, 1, 1]], dtype=np.float64)
+    g = 1.0 / np.sqrt(3.0)
+    K = np.zeros((X.shape[0], 8, 8))
+    for gx in (-g, g):
+        for gy in (-g, g):
+            for gz in (-g, g):
+                q = np.array([gx, gy, gz])
+                f = 1.0 + s * q  # (8, 3)
+                dN = np.empty((8, 3))
+                dN[:, 0] = s[:, 0] * f[:, 1] * f[:, 2] / 8.0
+                dN[:, 1] = s[:, 1] * f[:, 0] * f[:, 2] / 8.0
+                dN[:, 2] = s[:, 2] * f[:, 0] * f[:, 1] / 8.0
+                J = np.einsum("eai,aj->eij", X, dN)  # dx_i / dxi_j
+                det = np.linalg.det(J)
+                Ji = np.linalg.inv(J)
+                G = np.einsum("aj,eji->eai", dN, Ji)  # dN_a / dx_i
+                K += np.einsum("eai,ebi,e->eab", G, G, det)
+    return K
+
+
+def poisson27_hex(n, seed=20260, jitter=0.2):
+    m = n + 2
+    h = 1.0 / (m - 1)
+    ax = np.arange(m) * h
+    Z, Y, Xc = np.meshgrid(ax, ax, ax, indexing="ij")  # node id = (k * m + j) * m + i
+    xyz = np.stack([Xc, Y, Z], axis=-1)
+    rng = np.random.default_rng(seed)
+    disp = jitter * h * rng.uniform(-1.0, 1.0, size=(n, n, n, 3))
+    xyz[1:-1, 1:-1, 1:-1, :] += disp
+    xyz = xyz.reshape(-1, 3)
+    e = np.arange(m - 1)
+    ek, ej, ei = np.meshgrid(e, e, e, indexing="ij")
+    base = ((ek * m + ej) * m + ei).ravel()
+    off = np.array([0, 1, m + 1, m, m * m, m * m + 1, m * m + m + 1, m * m + m])
+    conn = base[:, None] + off[None, :]
+    K = _hex_element_matrices(xyz[conn])
+    rows = np.repeat(conn, 8, axis=1).ravel()
+    cols = np.tile(conn, (1, 8)).ravel()
+    A = sp.coo_matrix((K.ravel(), (rows, cols)), shape=(m ** 3, m ** 3)).tocsr()
+    inner = np.zeros((m, m, m), dtype=bool)
+    inner[1:-1, 1:-1, 1:-1] = True
+    keep = np.flatnonzero(inner.ravel())
+    A = A[keep][:, keep].tocsr()
+    A = A / h  # O(1) entries
+    A.sort_indices()
+    b = A @ np.ones(A.shape[0])
+    return A, b
+
+
+def momentum3(n, seed=20261, peclet=2.0, coupling=0.05, time_term=0.5):
+    rng = np.random.default_rng(seed)
+    u0 = np.array([1.0, 0.5, 0.25])
+    vel = u0[None, :] + 0.1 * rng.uniform(-1.0, 1.0, size=(n ** 3, 3))
+    nu = np.linalg.norm(u0) / peclet  # h = 1
+    idx = np.arange(n ** 3)
+    i, j, k = idx % n, (idx // n) % n, idx // (n * n)
+    coord = (i, j, k)
+    stride = (1, n, n * n)
+    rows, cols, vals = [], [], []
+    diag = np.full(n ** 3, time_term)
+    for d in range(3):
+        u = vel[:, d]
+        lo = nu + np.maximum(u, 0.0)  # coefficient magnitude on the (i - 1) neighbour (upwind for u > 0)
+        hi = nu + np.maximum(-u, 0.0)
+        diag += lo + hi
+        has_lo = coord[d] > 0
+        has_hi = coord[d] < n - 1
+        rows += [idx[has_lo], idx[has_hi]]
+        cols += [idx[has_lo] - stride[d], idx[has_hi] + stride[d]]
+        vals += [-lo[has_lo], -hi[has_hi]]
+    rows.append(idx); cols.append(idx); vals.append(diag)
+    S = sp.coo_matrix((np.concatenate(vals), (np.concatenate(rows), np.concatenate(cols))), shape=(n ** 3, n ** 3)).tocsr()
+    M = np.array([[1.0, coupling, -coupling], [-coupling, 1.0, coupling], [coupling, -coupling, 1.0]])
+    A = sp.kron(S, sp.csr_matrix(M), format="csr")  # node-blocked: row = 3 * node + dof
+    A.sort_indices()
+    b = A @ np.ones(A.shape[0])
+    return A, b
+
+
+def write_matrix_market(A, b, mat_path, rhs_path):
+    """MatrixMarket coordinate real general matrix + array rhs, 1-based"""
+    A = A.tocoo()
+    with open(mat_path, "w") as f:
+        f.write("%%MatrixMarket matrix coordinate real general\n")
+        f.write(f"{A.shape[0]} {A.shape[1]} {A.nnz}\n")
+        for r, c, v in zip(A.row, A.col, A.data):
+            f.write(f"{r + 1} {c + 1} {v:.17g}\n")
+    with open(rhs_path, "w") as f:
+        f.write("%%MatrixMarket matrix array real general\n")
+        f.write(f"{len(b)} 1\n")
+        for v in b:
+            f.write(f"{v:.17g}\n")
+
+
+def write_hypre_ij(A, b, mat_prefix, rhs_prefix, nparts=1):
+    """HYPRE IJ text files `<prefix>.<part 5 digits>`, 0-based ids (HypreSystem.cpp:1138-1318 reads these)"""
+    A = A.tocsr()
+    n = A.shape[0]
+    q, r = divmod(n, nparts)
+    for p in range(nparts):
+        lo = q * p + min(p, r)
+        hi = q * (p + 1) + min(p + 1, r) - 1
+        with open(f"{mat_prefix}.{p:05d}", "w") as f:
+            f.write(f"{lo} {hi} {lo} {hi}\n")
+            for i in range(lo, hi + 1):
+                for kk in range(A.indptr[i], A.indptr[i + 1]):
+                    f.write(f"{i} {A.indices[kk]} {A.data[kk]:.17g}\n")
+        with open(f"{rhs_prefix}.{p:05d}", "w") as f:
+            f.write(f"{lo} {hi}\n")
+            for i in range(lo, hi + 1):
+                f.write(f"{i} {b[i]:.17g}\n")
