@@ -270,6 +270,30 @@ HYPRE_Real b200hypre_gmres_solve_seconds(HYPRE_Solver gmres) {
   try { return as_gmres(gmres)->g.solve_seconds; } catch (const std::exception &e) { set_error(HYPRE_ERROR_ARG, e.what()); return -1.0; }
 }
 unsigned long long b200hypre_launch_count(void) { return ctx().launches; }
+// out[0..3] = bytes the library's stream-ordered pool holds from the driver (now / high-water) and bytes in use (now / high)
+HYPRE_Int b200hypre_pool_stats(unsigned long long *out) {
+  API_BEGIN
+  ensure_init();
+  cudaMemPool_t pool;
+  B200_CUDA(cudaDeviceGetDefaultMemPool(&pool, ctx().device));
+  unsigned long long v[4] = {0, 0, 0, 0};
+  B200_CUDA(cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReservedMemCurrent, &v[0]));
+  B200_CUDA(cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReservedMemHigh, &v[1]));
+  B200_CUDA(cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemCurrent, &v[2]));
+  B200_CUDA(cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemHigh, &v[3]));
+  for (int k = 0; k < 4; ++k) out[k] = v[k];
+  API_END
+}
+// grows the pool to at least `bytes` in one piece (the memory stays with the library: release threshold = max)
+HYPRE_Int b200hypre_pool_reserve(unsigned long long bytes) {
+  API_BEGIN
+  ensure_init();
+  void *p = nullptr;
+  B200_CUDA(cudaMallocAsync(&p, (size_t)bytes, stream()));
+  B200_CUDA(cudaFreeAsync(p, stream()));
+  B200_CUDA(cudaStreamSynchronize(stream()));
+  API_END
+}
 HYPRE_Int b200hypre_profile_enable(HYPRE_Int on, double min_bytes) {
   API_BEGIN ensure_init(); prof_enable(on != 0, min_bytes); API_END
 }

@@ -59,6 +59,15 @@ struct AmgOptions {
   double non_galerkin_tol = 0.0;
 };
 
+// wavefront schedule of one Gauss-Seidel pass (gs.cu): rows of the set sorted by dependency level
+struct GsPlan {
+  int n = 0, dir = 0, depth = 0, width = 0, rows = 0, cap = 1;
+  DVec<signed char> mask;         // 1 = row is updated by this pass
+  DVec<int> order, lvl_off;       // rows by wavefront; wavefront l = order[lvl_off[l] .. lvl_off[l+1])
+  DVec<unsigned long long> bar;   // grid-barrier counter
+  bool built = false;
+};
+
 struct AmgLevel {
   ParCsr *A = nullptr;            // level 0: borrowed from the caller; others: owned (A_own)
   std::unique_ptr<ParCsr> A_own;
@@ -70,6 +79,7 @@ struct AmgLevel {
   double cheby_max = 0, cheby_min = 0;
   std::vector<double> cheby_coef;
   DVec<double> u, f, r, t0, t1;   // work vectors of the cycle
+  GsPlan gs[3][2];                // [all | C | F points][forward | backward], built for the Gauss-Seidel smoothers only
 };
 
 struct Amg {
@@ -90,6 +100,12 @@ struct Amg {
   ~Amg();
 };
 
+bool is_gs_relax(int relax_type);
+bool is_l1_gs_relax(int relax_type);
+void gs_smoother_diag(ParCsr &A, int relax_type, double *d);
+void build_gs_plan(ParCsr &A, const DCsr &T, const int *cf, const double *dsm, int points, int dir, GsPlan &plan);
+void gs_sweep(ParCsr &A, GsPlan &plan, bool l1, const double *dsm, const double *f, const double *uin, double *uout);
+void gs_halo(ParCsr &A, const double *u);
 void amg_setup(Amg &amg, ParCsr &A);
 void amg_vcycle(Amg &amg, const double *rhs, double *z);   // z = M^{-1} rhs, zero initial guess
 void amg_solve(Amg &amg, ParCsr &A, const double *b, double *x, int *iters, double *relres);  // BoomerAMG as a solver
@@ -140,7 +156,8 @@ void ij_vector_get(IJVector &v, i64 n, const i64 *idx, double *out);
 
 // ---- setup building blocks (amg_setup.cu), exposed for tests through include/b200hypre.h ----------------------------
 void csr_transpose(const DCsr &A, DCsr &T);
-void csr_spgemm(const DCsr &A, const DCsr &B, DCsr &C, bool diag_first);
+// sorted = false: rows of C are written in no particular order (enough for the intermediate Q = A P of the Galerkin product)
+void csr_spgemm(const DCsr &A, const DCsr &B, DCsr &C, bool diag_first, bool sorted = true);
 void build_interp(const DCsr &Aext, const int *Sptr, const int *Scol, i64 S_nnz, const int *cf, const int *f2c, int n_own, int n_rows,
                   double tf, int pmax, DCsr &P);
 

@@ -94,6 +94,26 @@ void relax_sweep(Amg &amg, AmgLevel &L, LevelBufs &b, int rtype, bool down, bool
     }
     return;
   }
+  if (is_gs_relax(rtype)) {
+    // hybrid Gauss-Seidel (gs.cu): every pass reads b.cur and writes b.other; the halo is gathered once per call
+    const bool fwd = (rtype != 4 && rtype != 14), bwd = (rtype == 4 || rtype == 14 || rtype == 6 || rtype == 8);
+    const bool l1 = is_l1_gs_relax(rtype);
+    const int npass = (o.relax_order == 1) ? 2 : 1;
+    for (int pass = 0; pass < npass; ++pass) {
+      int pt = 0;
+      if (npass == 2) pt = down ? (pass == 0 ? 1 : -1) : (pass == 0 ? -1 : 1);
+      const int ps = (pt == 0) ? 0 : (pt == 1 ? 1 : 2);
+      if (zero_guess && pass == 0) vec_fill(b.cur, 0.0, n);
+      gs_halo(A, b.cur);
+      for (int dir = 0; dir < 2; ++dir) {
+        if (dir == 0 ? !fwd : !bwd) continue;
+        B200_REQUIRE(L.gs[ps][dir].built, "Gauss-Seidel plan missing for this level (internal error)");
+        gs_sweep(A, L.gs[ps][dir], l1, L.dsm.p, b.f, b.cur, b.other);
+        std::swap(b.cur, b.other);
+      }
+    }
+    return;
+  }
   // Jacobi-type
   int npass = (o.relax_order == 1) ? 2 : 1;
   for (int pass = 0; pass < npass; ++pass) {
@@ -111,7 +131,12 @@ void relax_sweep(Amg &amg, AmgLevel &L, LevelBufs &b, int rtype, bool down, bool
   }
 }
 
-int flips_per_sweep(const AmgOptions &o, int rtype) { return rtype == 16 ? 0 : (o.relax_order == 1 ? 2 : 1); }
+int flips_per_sweep(const AmgOptions &o, int rtype) {
+  if (rtype == 16) return 0;
+  const int npass = (o.relax_order == 1) ? 2 : 1;
+  if (is_gs_relax(rtype)) return npass * ((rtype == 6 || rtype == 8) ? 2 : 1);
+  return npass;
+}
 
 void init_bufs(Amg &amg, const double *rhs, double *z, std::vector<LevelBufs> &bufs) {
   const AmgOptions &o = amg.opt;

@@ -835,7 +835,7 @@ bool coarsen_level_dist(Amg &amg, AmgLevel &L, AmgLevel &Lc) {
       B200_REQUIRE(fetch1(bad.p) == 0, "A*P: column renumbering failed");
       DCsr Pext;
       stack_rows(n, Pm.ptr.p, Pm.col.p, Pm.val.p, Pm.nnz, extP, Nq, nc + nxq, true, Pext);
-      csr_spgemm(Am, Pext, Q, false);
+      csr_spgemm(Am, Pext, Q, false, false);
     }
     // A_c = R_merged * Q_ext
     {

@@ -348,15 +348,22 @@ bool coarsen_level(Amg &amg, AmgLevel &L, AmgLevel &Lc) {
   // R = P^T, Q = A P, A_c = R Q
   {
     PhaseTimer t(amg, "rap");
-    csr_transpose(L.P.diag, L.R.diag);
+    {
+      PhaseTimer t1(amg, "rap.transpose");
+      csr_transpose(L.P.diag, L.R.diag);
+    }
     L.R.n = nc;
     L.R.n_cols_local = n;
     L.R.g_rows = gnc;
     L.R.g_cols = gn;
     DCsr Q;
-    csr_spgemm(A, L.P.diag, Q, false);
+    {
+      PhaseTimer t2(amg, "rap.AP");
+      csr_spgemm(A, L.P.diag, Q, false, false);
+    }
     Lc.A_own.reset(new ParCsr());
     Lc.A = Lc.A_own.get();
+    PhaseTimer t3(amg, "rap.RQ");
     csr_spgemm(L.R.diag, Q, Lc.A->diag, true);
     Lc.A->n = nc;
     Lc.A->n_cols_local = nc;
@@ -392,8 +399,11 @@ void amg_setup(Amg &amg, ParCsr &A) {
                "BoomerAMG: only coarsen_type 8 (PMIS; 10/HMIS is mapped to PMIS) is built in this round");
   B200_REQUIRE(o.interp_type == 6 || o.max_levels == 1, "BoomerAMG: only interp_type 6 (extended+i) is built in this round");
   for (int k = 0; k < 3; ++k)
-    B200_REQUIRE(o.relax_type[k] == 18 || o.relax_type[k] == 7 || o.relax_type[k] == 16,
-                 "BoomerAMG: relax_type must be 7 (Jacobi), 18 (l1-Jacobi) or 16 (Chebyshev) in this round");
+    B200_REQUIRE(o.relax_type[k] == 18 || o.relax_type[k] == 7 || o.relax_type[k] == 16 || is_gs_relax(o.relax_type[k]),
+                 "BoomerAMG: relax_type must be 7 (Jacobi), 18 (l1-Jacobi), 16 (Chebyshev) or hybrid Gauss-Seidel (3, 4, 6, 8, 13, 14)");
+  B200_REQUIRE(o.relax_type[1] == o.relax_type[2] || (is_gs_relax(o.relax_type[1]) && is_gs_relax(o.relax_type[2]) &&
+                                                      is_l1_gs_relax(o.relax_type[1]) == is_l1_gs_relax(o.relax_type[2])),
+               "BoomerAMG: down and up smoothers must share their diagonal scaling (same relax_type family)");
   if (amg.graph_exec) { cudaGraphExecDestroy(amg.graph_exec); amg.graph_exec = nullptr; }
   amg.setup_phase_ms.clear();
   amg.lev.clear();
@@ -424,7 +434,10 @@ void amg_setup(Amg &amg, ParCsr &A) {
       if (l < nl - 1) { L.P.finalize_spmv(); L.R.finalize_spmv(); }
       int rt = o.relax_type[1];
       if (rt == 16) cheby_setup(amg, L);
-      else {
+      else if (is_gs_relax(rt)) {
+        L.dsm.alloc((size_t)std::max(n, 1));
+        gs_smoother_diag(Al, rt, L.dsm.p);
+      } else {
         L.dsm.alloc((size_t)std::max(n, 1));
         if (ctx().nranks > 1) smoother_diag_dist(Al, rt, L.dsm.p);
         else if (n) { k_smoother_diag<<<div_up(n, 256), 256, 0, stream()>>>(rv(Al.diag), rt, L.dsm.p); count_launch(); }
@@ -433,6 +446,34 @@ void amg_setup(Amg &amg, ParCsr &A) {
       L.u.alloc(ld); L.f.alloc(ld); L.r.alloc(ld); L.t0.alloc(ld); L.t1.alloc(ld);
       L.u.zero(); L.f.zero(); L.r.zero(); L.t0.zero(); L.t1.zero();
       if (L.cf.n == 0 && n) { L.cf.alloc(n); std::vector<int> ones(n, 1); L.cf.from_host(ones); }
+      if (is_gs_relax(rt) || is_gs_relax(o.relax_type[2])) {
+        // wavefront schedules of the Gauss-Seidel passes this level will run (gs.cu); the coarsest level is only smoothed
+        // when it is not solved directly
+        const bool smoothed = (l < nl - 1) || (nl == 1 && o.max_levels == 1) || Al.g_rows > 2048 || Al.g_rows == 0;
+        if (smoothed && n) {
+          DCsr pat, T;
+          pat.nr = Al.diag.nr; pat.nc = Al.diag.nc; pat.nnz = Al.diag.nnz;
+          pat.ptr.alloc(Al.diag.ptr.n); pat.col.alloc(Al.diag.col.n);
+          B200_CUDA(cudaMemcpyAsync(pat.ptr.p, Al.diag.ptr.p, sizeof(int) * Al.diag.ptr.n, cudaMemcpyDeviceToDevice, stream()));
+          B200_CUDA(cudaMemcpyAsync(pat.col.p, Al.diag.col.p, sizeof(int) * Al.diag.col.n, cudaMemcpyDeviceToDevice, stream()));
+          csr_transpose(pat, T);
+          bool need_dir[2] = {false, false};
+          for (int k = 1; k <= 2; ++k) {
+            int t = o.relax_type[k];
+            if (!is_gs_relax(t)) continue;
+            if (t != 4 && t != 14) need_dir[0] = true;
+            if (t == 4 || t == 14 || t == 6 || t == 8) need_dir[1] = true;
+          }
+          for (int ps = 0; ps < 3; ++ps) {
+            if ((o.relax_order == 1) != (ps != 0)) continue;
+            for (int dir = 0; dir < 2; ++dir)
+              if (need_dir[dir]) {
+                build_gs_plan(Al, T, L.cf.p, L.dsm.p, ps == 0 ? 0 : (ps == 1 ? 1 : -1), dir, L.gs[ps][dir]);
+                L.gs[ps][dir].built = true;
+              }
+          }
+        }
+      }
     }
     // coarsest: dense LU
     AmgLevel &C = *amg.lev[nl - 1];

@@ -1,0 +1,233 @@
+// gs.cu -- hybrid Gauss-Seidel smoothers of BoomerAMG (relax_type 3, 4, 6, 8, 13, 14) with the exact sequential
+// semantics of the CPU algorithm, executed wavefront by wavefront.
+// Replaces hypre_BoomerAMGRelax for the Gauss-Seidel family reached from HYPRE_BoomerAMGSolve; relax_type 8 with
+// relax_order 1 is the mini-app's DEFAULT smoother (/root/reference/src/HypreSystem.cpp:138,156).  Definition:
+// SURVEY.md A.7 -- Gauss-Seidel over a rank's own rows in index order (3 / 13 forward, 4 / 14 backward, 6 / 8 forward
+// then backward), off-rank columns frozen at their values before the call (one halo exchange per call), optional C/F
+// masking; 3 / 4 / 6: u_i = (f_i - sum_{j != i} a_ij u_j) / a_ii, 8 / 13 / 14: u_i += (f_i - sum_j a_ij u_j) / l1_i with
+// hypre's truncated l1 norm  |a_ii| + 1/2 sum_offd |a_ij|  (reset to |a_ii| when <= 4/3 |a_ii|).
+//
+// B200 formulation.  A sequential sweep is a longest-path problem on the dependency graph "row i needs the new value of
+// every updated row j that precedes it and appears in row i"; rows on the same wavefront level are independent.
+//   setup  (build_gs_plan): in-degrees from the rows, then Kahn's peeling in ONE persistent kernel (frontier queue in
+//          global memory, the transposed pattern gives the dependants, software grid barrier between wavefronts).
+//          The queue is the row permutation "sorted by wavefront", the frontier boundaries are the level offsets.
+//   sweep  (gs_sweep): ONE persistent kernel per direction; wavefront l = rows order[off[l] .. off[l+1]), one thread per
+//          row, grid barrier between wavefronts.  Values are read from `uout` for rows already updated in this sweep
+//          and from `uin` otherwise (out of place: a nonsymmetric pattern cannot create a write-after-read hazard), the
+//          row sum runs in storage order (diag block, then offd block) with unfused multiply / subtract like the oracle.
+// The grid never exceeds the number of co-resident blocks, so the software barrier cannot deadlock.
+#include "amg.h"
+#include <algorithm>
+
+namespace b200 {
+
+void halo_exchange_begin(ParCsr &A, const double *x, const double *xs);
+void halo_exchange_end(ParCsr &A);
+
+namespace {
+
+constexpr int GS_THREADS = 256;
+
+__device__ __forceinline__ void grid_barrier(unsigned long long *bar, unsigned nblocks, unsigned long long &epoch) {
+  epoch += 1;
+  if (nblocks == 1) { __syncthreads(); return; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(bar, 1ull);
+    const unsigned long long target = epoch * nblocks;
+    while (*(volatile unsigned long long *)bar < target) { }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ bool in_set(const int *cf, const double *d, const int *ptr, int i, int points) {
+  if (points != 0 && cf[i] != points) return false;
+  return ptr[i + 1] > ptr[i] && d[i] != 0.0;
+}
+
+// mask[i] = 1 when row i is updated by the sweep; indeg[i] = number of updated rows that precede i (in sweep direction)
+// among the columns of row i, -1 for rows outside the set
+__global__ void k_gs_indeg(int n, const int *__restrict__ ptr, const int *__restrict__ col, const int *__restrict__ cf,
+                           const double *__restrict__ d, int points, int dir, signed char *mask, int *indeg, int *ctr) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  bool member = false;
+  if (i < n) {
+    member = in_set(cf, d, ptr, i, points);
+    int c = -1;
+    if (member) {
+      c = 0;
+      for (int k = ptr[i]; k < ptr[i + 1]; ++k) {
+        int j = col[k];
+        if ((dir == 0 ? j < i : j > i) && in_set(cf, d, ptr, j, points)) ++c;
+      }
+    }
+    mask[i] = member ? 1 : 0;
+    indeg[i] = c;
+  }
+  int cnt = __syncthreads_count(member);
+  if (threadIdx.x == 0 && cnt) atomicAdd(ctr + 5, cnt);   // number of rows in the set
+}
+// ctr[0] = queue tail (seeds on entry of k_gs_kahn, all scheduled rows on exit), ctr[1..3] = per-level append counters
+// (rotating), ctr[4] = depth (output), ctr[5] = rows in the set
+__global__ void k_gs_seed(int n, const int *indeg, int *order, int *ctr) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && indeg[i] == 0) order[atomicAdd(ctr, 1)] = i;
+}
+__global__ void __launch_bounds__(GS_THREADS) k_gs_kahn(const int *__restrict__ Tptr, const int *__restrict__ Tcol, int dir, int *indeg,
+                                                        int *order, int *ctr, int *lvl_off, unsigned long long *bar, unsigned nblocks) {
+  const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gthreads = gridDim.x * blockDim.x;
+  unsigned long long epoch = 0;
+  int head = 0, tail = __ldcg(ctr), lvl = 0;
+  if (gtid == 0) lvl_off[0] = 0;
+  while (head < tail) {
+    int *cnt = ctr + 1 + (lvl % 3);
+    if (gtid == 0) ctr[1 + ((lvl + 1) % 3)] = 0;   // last read after the barrier of level lvl - 2
+    for (int idx = head + gtid; idx < tail; idx += gthreads) {
+      const int i = __ldcg(order + idx);
+      for (int k = Tptr[i]; k < Tptr[i + 1]; ++k) {
+        const int j = Tcol[k];
+        if (dir == 0 ? j > i : j < i) {
+          if (__ldcg(indeg + j) > 0 && atomicSub(indeg + j, 1) == 1) order[tail + atomicAdd(cnt, 1)] = j;
+        }
+      }
+    }
+    grid_barrier(bar, nblocks, epoch);
+    head = tail;
+    tail += __ldcg(cnt);
+    ++lvl;
+    if (gtid == 0) lvl_off[lvl] = head;
+  }
+  if (gtid == 0) { ctr[4] = lvl; ctr[0] = tail; }
+}
+
+// one Gauss-Seidel pass over the rows of a plan
+template <bool L1>
+__global__ void __launch_bounds__(GS_THREADS) k_gs_sweep(int n, CsrView D, CsrView O, const int *__restrict__ order,
+                                                         const int *__restrict__ lvl_off, int depth,
+                                                         const signed char *__restrict__ mask, int dir, const double *__restrict__ dsm,
+                                                         const double *__restrict__ f, const double *__restrict__ uin, double *uout,
+                                                         const double *__restrict__ halo, unsigned long long *bar, unsigned nblocks) {
+  const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gthreads = gridDim.x * blockDim.x;
+  for (int i = gtid; i < n; i += gthreads)
+    if (!mask[i]) uout[i] = uin[i];          // rows outside the set keep their value (never read from uout)
+  unsigned long long epoch = 0;
+  for (int l = 0; l < depth; ++l) {
+    const int lb = lvl_off[l], le = lvl_off[l + 1];
+    for (int idx = lb + gtid; idx < le; idx += gthreads) {
+      const int i = order[idx];
+      const int b = D.ptr[i], e = D.ptr[i + 1];
+      double res = f[i];
+      for (int q = L1 ? b : b + 1; q < e; ++q) {
+        const int c = D.col[q];
+        const bool done = mask[c] && (dir == 0 ? c < i : c > i);
+        const double v = done ? __ldcg(uout + c) : uin[c];
+        res = __dsub_rn(res, __dmul_rn(D.val[q], v));
+      }
+      if (O.ptr != nullptr)
+        for (int q = O.ptr[i]; q < O.ptr[i + 1]; ++q) res = __dsub_rn(res, __dmul_rn(O.val[q], halo[O.col[q]]));
+      uout[i] = L1 ? __dadd_rn(uin[i], __ddiv_rn(res, dsm[i])) : __ddiv_rn(res, D.val[b]);
+    }
+    if (l + 1 < depth) grid_barrier(bar, nblocks, epoch);
+  }
+}
+
+// smoother diagonal of the Gauss-Seidel family: a_ii (3 / 4 / 6) or hypre's truncated l1 norm (8 / 13 / 14)
+__global__ void k_gs_diag(int n, CsrView D, CsrView O, int l1, double *d) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int b = D.ptr[i], e = D.ptr[i + 1];
+  if (b == e) { d[i] = 1.0; return; }
+  double dg = D.val[b];
+  if (!l1) { d[i] = dg; return; }
+  double ad = fabs(dg), s = ad;
+  if (O.ptr != nullptr)
+    for (int k = O.ptr[i]; k < O.ptr[i + 1]; ++k) s = s + 0.5 * fabs(O.val[k]);
+  if (s <= 4.0 / 3.0 * ad) s = ad;
+  d[i] = (dg < 0) ? -s : s;
+}
+
+int max_resident_blocks(const void *kernel) {
+  int per_sm = 0;
+  B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, GS_THREADS, 0));
+  per_sm = std::max(1, std::min(per_sm, 4));
+  return per_sm * ctx().sm_count;
+}
+
+}  // namespace
+
+bool is_gs_relax(int t) { return t == 3 || t == 4 || t == 6 || t == 8 || t == 13 || t == 14; }
+bool is_l1_gs_relax(int t) { return t == 8 || t == 13 || t == 14; }
+
+void gs_smoother_diag(ParCsr &A, int relax_type, double *d) {
+  if (A.n == 0) return;
+  CsrView O = A.offd.nnz > 0 ? A.offd.view() : CsrView{0, 0, nullptr, nullptr, nullptr};
+  k_gs_diag<<<div_up(A.n, 256), 256, 0, stream()>>>(A.n, A.diag.view(), O, is_l1_gs_relax(relax_type) ? 1 : 0, d);
+  count_launch();
+}
+
+// T: transposed pattern of A.diag (dependants of a row)
+void build_gs_plan(ParCsr &A, const DCsr &T, const int *cf, const double *dsm, int points, int dir, GsPlan &plan) {
+  const int n = A.n;
+  plan.n = n;
+  plan.dir = dir;
+  plan.depth = 0;
+  plan.width = 0;
+  plan.mask.alloc((size_t)std::max(n, 1));
+  plan.order.alloc((size_t)std::max(n, 1));
+  plan.lvl_off.alloc((size_t)n + 2);
+  plan.bar.alloc(2);
+  plan.cap = std::min(max_resident_blocks((const void *)k_gs_sweep<true>), max_resident_blocks((const void *)k_gs_sweep<false>));
+  if (n == 0) return;
+  DVec<int> indeg((size_t)n), ctr(8);
+  ctr.zero();
+  plan.bar.zero();
+  k_gs_indeg<<<div_up(n, 256), 256, 0, stream()>>>(n, A.diag.ptr.p, A.diag.col.p, cf, dsm, points, dir, plan.mask.p, indeg.p, ctr.p);
+  k_gs_seed<<<div_up(n, 256), 256, 0, stream()>>>(n, indeg.p, plan.order.p, ctr.p);
+  static int cap = 0;
+  if (!cap) cap = max_resident_blocks((const void *)k_gs_kahn);
+  const int nblocks = std::max(1, std::min(cap, div_up(n, GS_THREADS)));
+  k_gs_kahn<<<nblocks, GS_THREADS, 0, stream()>>>(T.ptr.p, T.col.p, dir, indeg.p, plan.order.p, ctr.p, plan.lvl_off.p,
+                                                  plan.bar.p, (unsigned)nblocks);
+  count_launch(3);
+  B200_KERNEL_CHECK();
+  std::vector<int> h = ctr.to_host();
+  plan.depth = h[4];
+  plan.rows = h[5];
+  B200_REQUIRE(h[0] == h[5], "Gauss-Seidel plan: dependency cycle (internal error)");
+  if (plan.depth > 0) {
+    std::vector<int> off((size_t)plan.depth + 1);
+    B200_CUDA(cudaMemcpyAsync(off.data(), plan.lvl_off.p, sizeof(int) * (plan.depth + 1), cudaMemcpyDeviceToHost, stream()));
+    B200_CUDA(cudaStreamSynchronize(stream()));
+    for (int l = 0; l < plan.depth; ++l) plan.width = std::max(plan.width, off[l + 1] - off[l]);
+    B200_REQUIRE(off[plan.depth] == plan.rows, "Gauss-Seidel plan: level offsets inconsistent (internal error)");
+  }
+}
+
+void gs_sweep(ParCsr &A, GsPlan &plan, bool l1, const double *dsm, const double *f, const double *uin, double *uout) {
+  const int n = A.n;
+  if (n == 0) return;
+  const int cap = plan.cap;   // queried at plan time (no runtime API calls here: the sweep may be captured into a CUDA graph)
+  const int want = std::max(div_up(std::max(plan.width, 1), GS_THREADS), plan.depth > 0 ? 1 : div_up(n, GS_THREADS));
+  const int nblocks = std::max(1, std::min(cap, want));
+  CsrView O = A.offd.nnz > 0 ? A.offd.view() : CsrView{0, 0, nullptr, nullptr, nullptr};
+  B200_CUDA(cudaMemsetAsync(plan.bar.p, 0, sizeof(unsigned long long), stream()));
+  if (l1)
+    k_gs_sweep<true><<<nblocks, GS_THREADS, 0, stream()>>>(n, A.diag.view(), O, plan.order.p, plan.lvl_off.p, plan.depth, plan.mask.p,
+                                                           plan.dir, dsm, f, uin, uout, A.x_halo.p, plan.bar.p, (unsigned)nblocks);
+  else
+    k_gs_sweep<false><<<nblocks, GS_THREADS, 0, stream()>>>(n, A.diag.view(), O, plan.order.p, plan.lvl_off.p, plan.depth, plan.mask.p,
+                                                            plan.dir, dsm, f, uin, uout, A.x_halo.p, plan.bar.p, (unsigned)nblocks);
+  count_launch();
+}
+
+// gathers the halo values of u (the state before the sweep) when the matrix is distributed
+void gs_halo(ParCsr &A, const double *u) {
+  if (ctx().nranks <= 1) return;
+  halo_exchange_begin(A, u, nullptr);
+  halo_exchange_end(A);
+}
+
+}  // namespace b200

@@ -69,7 +69,7 @@ __device__ __forceinline__ int hash_insert(int *keys, int H, int c, bool &isnew)
 template <int G, bool NUMERIC>
 __device__ __forceinline__ void spgemm_row(const rows::Csr &A, const rows::Csr &B, int row, int lane, unsigned mask, int *keys,
                                            double *vals, int H, int *cnt, int *lk, double *lv, const int *Cptr, int *Ccol,
-                                           double *Cval, int *nnz_out, int diag_col) {
+                                           double *Cval, int *nnz_out, int diag_col, bool sorted) {
   for (int s = lane; s < H; s += G) {
     keys[s] = -1;
     if (NUMERIC) vals[s] = 0.0;
@@ -155,27 +155,45 @@ __device__ __forceinline__ void spgemm_row(const rows::Csr &A, const rows::Csr &
     }
     return;
   } else {
+  const int base = Cptr[row];
+  if (!sorted) {
+    // intermediate product (Q = A P): the consumer R * Q accumulates over the entries of R's rows, at most one term per
+    // Q row for any output entry, so the order inside a Q row is irrelevant and the row is written as it is compacted
+    for (int s = lane; s < H; s += G) {
+      int c = keys[s];
+      if (c != -1) {
+        int p = atomicAdd(cnt, 1);
+        Ccol[base + p] = c;
+        Cval[base + p] = vals[s];
+      }
+    }
+    gsync<G>(mask);
+    return;
+  }
+  // compaction; the list holds sort keys (the diagonal column becomes -1 so that it ranks first)
   for (int s = lane; s < H; s += G) {
     int c = keys[s];
     if (c != -1) {
       int p = atomicAdd(cnt, 1);
-      lk[p] = c;
+      lk[p] = (c == diag_col) ? -1 : c;
       lv[p] = vals[s];
     }
   }
   gsync<G>(mask);
   const int n = *cnt;
-  const int base = Cptr[row];
+  if (lane == 0 && (n & 1)) lk[n] = 0x7fffffff;   // pad to an even length (capacity H / 2 is even, n odd < H / 2)
+  gsync<G>(mask);
+  // rank = number of smaller keys (keys are distinct); two keys per shared-memory load
   for (int t = lane; t < n; t += G) {
-    int c = lk[t];
-    int key = (c == diag_col) ? -1 : c;
+    const int key = lk[t];
     int rank = 0;
-    for (int u = 0; u < n; ++u) {
-      int cu = lk[u];
-      int ku = (cu == diag_col) ? -1 : cu;
-      rank += (ku < key) ? 1 : 0;
+#pragma unroll 4
+    for (int u = 0; u < n; u += 2) {
+      const int2 kk = *reinterpret_cast<const int2 *>(lk + u);
+      rank += (kk.x < key) ? 1 : 0;
+      rank += (kk.y < key) ? 1 : 0;
     }
-    Ccol[base + rank] = c;
+    Ccol[base + rank] = (key == -1) ? diag_col : key;
     Cval[base + rank] = lv[t];
   }
   gsync<G>(mask);
@@ -185,7 +203,7 @@ __device__ __forceinline__ void spgemm_row(const rows::Csr &A, const rows::Csr &
 // shared-memory table kernels.  G threads per row, blockDim.x / G rows per block.
 template <int G, bool NUMERIC>
 __global__ void k_spgemm_smem(rows::Csr A, rows::Csr B, const int *row_list, int nrows, int H, const int *Cptr, int *Ccol,
-                              double *Cval, int *nnz_out, int diag_first) {
+                              double *Cval, int *nnz_out, int diag_first, int sorted) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int groups = blockDim.x / G;
   const int g = threadIdx.x / G, lane = threadIdx.x % G;
@@ -202,13 +220,13 @@ __global__ void k_spgemm_smem(rows::Csr A, rows::Csr B, const int *row_list, int
   int idx = blockIdx.x * groups + g;
   if (idx >= nrows) return;  // G > 32: groups == 1, uniform for the whole block
   int row = row_list[idx];
-  spgemm_row<G, NUMERIC>(A, B, row, lane, mask, keys, vals, H, cnt, lk, lv, Cptr, Ccol, Cval, nnz_out, diag_first ? row : -2);
+  spgemm_row<G, NUMERIC>(A, B, row, lane, mask, keys, vals, H, cnt, lk, lv, Cptr, Ccol, Cval, nnz_out, diag_first ? row : -2, sorted != 0);
 }
 
 // global-memory table kernel: one table per block, grid-stride over the bin
 template <bool NUMERIC>
 __global__ void k_spgemm_gmem(rows::Csr A, rows::Csr B, const int *row_list, int nrows, int H, int *gkeys, double *gvals, int *glk,
-                              double *glv, const int *Cptr, int *Ccol, double *Cval, int *nnz_out, int diag_first) {
+                              double *glv, const int *Cptr, int *Ccol, double *Cval, int *nnz_out, int diag_first, int sorted) {
   __shared__ int cnt;
   int *keys = gkeys + (size_t)blockIdx.x * H;
   double *vals = NUMERIC ? gvals + (size_t)blockIdx.x * H : nullptr;
@@ -217,7 +235,7 @@ __global__ void k_spgemm_gmem(rows::Csr A, rows::Csr B, const int *row_list, int
   for (int idx = blockIdx.x; idx < nrows; idx += gridDim.x) {
     int row = row_list[idx];
     spgemm_row<256, NUMERIC>(A, B, row, threadIdx.x, 0, keys, vals, H, &cnt, lk, lv, Cptr, Ccol, Cval, nnz_out,
-                              diag_first ? row : -2);
+                              diag_first ? row : -2, sorted != 0);
   }
 }
 __global__ void k_spgemm_bound(rows::Csr A, rows::Csr B, int *bound) {
@@ -307,20 +325,20 @@ inline int next_pow2(i64 v) {
 
 template <int G, bool NUMERIC>
 void launch_smem(const rows::Csr &a, const rows::Csr &b, const int *list, int count, int H, int gpb, size_t smem, const int *Cptr,
-                 int *Ccol, double *Cval, int *nnz_out, bool diag_first) {
+                 int *Ccol, double *Cval, int *nnz_out, bool diag_first, bool sorted) {
   auto kern = k_spgemm_smem<G, NUMERIC>;
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     attr_set = true;
   }
-  kern<<<div_up(count, gpb), gpb * G, smem, stream()>>>(a, b, list, count, H, Cptr, Ccol, Cval, nnz_out, diag_first ? 1 : 0);
+  kern<<<div_up(count, gpb), gpb * G, smem, stream()>>>(a, b, list, count, H, Cptr, Ccol, Cval, nnz_out, diag_first ? 1 : 0, sorted ? 1 : 0);
   count_launch();
 }
 
 template <bool NUMERIC>
 void spgemm_pass(const DCsr &A, const DCsr &B, const Bins &bins, const BinLimits &L, const int *Cptr, int *Ccol, double *Cval,
-                 int *nnz_out, bool diag_first) {
+                 int *nnz_out, bool diag_first, bool sorted) {
   rows::Csr a = rv(A), b = rv(B);
   // lanes per row from the mean row length of B
   double mean_b = B.nr > 0 ? (double)B.nnz / B.nr : 1.0;
@@ -343,11 +361,11 @@ void spgemm_pass(const DCsr &A, const DCsr &B, const Bins &bins, const BinLimits
     }
     size_t smem = per * gpb;
     switch (G) {
-      case 4: launch_smem<4, NUMERIC>(a, b, list, bins.count[k], H, gpb, smem, Cptr, Ccol, Cval, nnz_out, diag_first); break;
-      case 8: launch_smem<8, NUMERIC>(a, b, list, bins.count[k], H, gpb, smem, Cptr, Ccol, Cval, nnz_out, diag_first); break;
-      case 16: launch_smem<16, NUMERIC>(a, b, list, bins.count[k], H, gpb, smem, Cptr, Ccol, Cval, nnz_out, diag_first); break;
-      case 32: launch_smem<32, NUMERIC>(a, b, list, bins.count[k], H, gpb, smem, Cptr, Ccol, Cval, nnz_out, diag_first); break;
-      default: launch_smem<256, NUMERIC>(a, b, list, bins.count[k], H, 1, per, Cptr, Ccol, Cval, nnz_out, diag_first); break;
+      case 4: launch_smem<4, NUMERIC>(a, b, list, bins.count[k], H, gpb, smem, Cptr, Ccol, Cval, nnz_out, diag_first, sorted); break;
+      case 8: launch_smem<8, NUMERIC>(a, b, list, bins.count[k], H, gpb, smem, Cptr, Ccol, Cval, nnz_out, diag_first, sorted); break;
+      case 16: launch_smem<16, NUMERIC>(a, b, list, bins.count[k], H, gpb, smem, Cptr, Ccol, Cval, nnz_out, diag_first, sorted); break;
+      case 32: launch_smem<32, NUMERIC>(a, b, list, bins.count[k], H, gpb, smem, Cptr, Ccol, Cval, nnz_out, diag_first, sorted); break;
+      default: launch_smem<256, NUMERIC>(a, b, list, bins.count[k], H, 1, per, Cptr, Ccol, Cval, nnz_out, diag_first, sorted); break;
     }
   }
   if (bins.count[NB]) {  // global-memory tables
@@ -357,7 +375,7 @@ void spgemm_pass(const DCsr &A, const DCsr &B, const Bins &bins, const BinLimits
     DVec<double> gv, glv;
     if (NUMERIC) { gv.alloc((size_t)grid * H); glk.alloc((size_t)grid * H); glv.alloc((size_t)grid * H); }
     k_spgemm_gmem<NUMERIC><<<grid, 256, 0, stream()>>>(a, b, bins.list.p + bins.offset[NB], bins.count[NB], H, gk.p, gv.p, glk.p,
-                                                       glv.p, Cptr, Ccol, Cval, nnz_out, diag_first);
+                                                       glv.p, Cptr, Ccol, Cval, nnz_out, diag_first, sorted ? 1 : 0);
     count_launch();
     B200_CUDA(cudaStreamSynchronize(stream()));
   }
@@ -404,7 +422,7 @@ void csr_transpose(const DCsr &A, DCsr &T) {
   B200_KERNEL_CHECK();
 }
 
-void csr_spgemm(const DCsr &A, const DCsr &B, DCsr &C, bool diag_first) {
+void csr_spgemm(const DCsr &A, const DCsr &B, DCsr &C, bool diag_first, bool sorted) {
   B200_REQUIRE(A.nc == B.nr, "csr_spgemm: dimension mismatch");
   C.nr = A.nr;
   C.nc = B.nc;
@@ -420,7 +438,7 @@ void csr_spgemm(const DCsr &A, const DCsr &B, DCsr &C, bool diag_first) {
     Bins bins;
     BinLimits L{{16, 32, 64, 128, 512, 2048, 16384}};
     make_bins(A.nr, bound.p, L, bins);
-    spgemm_pass<false>(A, B, bins, L, nullptr, nullptr, nullptr, nnz_row.p, diag_first);
+    spgemm_pass<false>(A, B, bins, L, nullptr, nullptr, nullptr, nnz_row.p, diag_first, sorted);
   }
   exclusive_scan(nnz_row.p, C.ptr.p, (i64)C.nr + 1);
   int last = 0;
@@ -434,7 +452,7 @@ void csr_spgemm(const DCsr &A, const DCsr &B, DCsr &C, bool diag_first) {
     Bins bins;
     BinLimits L{{16, 32, 64, 128, 256, 1024, 4096}};
     make_bins(A.nr, nnz_row.p, L, bins);
-    spgemm_pass<true>(A, B, bins, L, C.ptr.p, C.col.p, C.val.p, nullptr, diag_first);
+    spgemm_pass<true>(A, B, bins, L, C.ptr.p, C.col.p, C.val.p, nullptr, diag_first, sorted);
   }
 }
 

@@ -151,6 +151,19 @@ def launch_count():
     return int(lib().b200hypre_launch_count())
 
 
+def pool_stats():
+    """bytes of the library's device memory pool: reserved now / high-water, in use now / high-water"""
+    out = (C.c_ulonglong * 4)()
+    check(lib().b200hypre_pool_stats(out), "pool_stats")
+    return {"reserved": int(out[0]), "reserved_high": int(out[1]), "used": int(out[2]), "used_high": int(out[3])}
+
+
+def pool_reserve(nbytes):
+    L = lib()
+    L.b200hypre_pool_reserve.argtypes = [C.c_ulonglong]
+    check(L.b200hypre_pool_reserve(int(nbytes)), "pool_reserve")
+
+
 def profile_enable(on=True, min_bytes=0.0):
     L = lib()
     L.b200hypre_profile_enable.argtypes = [I32, F64]

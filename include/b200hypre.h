@@ -64,6 +64,10 @@ HYPRE_Int b200hypre_device_info(char *name, HYPRE_Int name_cap, int *device, int
 
 /* ---- instrumentation ------------------------------------------------------------------------------------------------------- */
 unsigned long long b200hypre_launch_count(void);   /* kernels launched by the library so far */
+/* device memory pool of the library (stream-ordered, never shrinks): out[0..3] = reserved now / high, used now / high */
+HYPRE_Int b200hypre_pool_stats(unsigned long long *out);
+/* pre-grow the pool to `bytes` in one piece (what HYPRE_SetGPUMemoryPoolSize is for, /root/reference/src/main.cpp:104) */
+HYPRE_Int b200hypre_pool_reserve(unsigned long long bytes);
 /* kernel-class timing with CUDA events on the library stream: scopes whose algorithmic byte count is >= min_bytes are
  * recorded while enabled; summary returns ';'-joined class names with total ms, call count and algorithmic bytes */
 HYPRE_Int b200hypre_profile_enable(HYPRE_Int on, double min_bytes);

@@ -618,14 +618,31 @@ static void interp_extpi(const Csr &A, const Csr &S, const std::vector<int> &cf,
 // ---------------------------------------------------------------------------------------------------------
 // smoother data
 // ---------------------------------------------------------------------------------------------------------
-static void l1_norms(const Csr &A, int relax_type, std::vector<double> &l1) {
+static inline bool is_gs(int t) { return t == 3 || t == 4 || t == 6 || t == 8 || t == 13 || t == 14; }
+static inline bool is_l1_gs(int t) { return t == 8 || t == 13 || t == 14; }
+
+// part: virtual-rank row partition (entries with a column outside the owner's range form the offd block)
+static void l1_norms(const Csr &A, int relax_type, const std::vector<int> &part, std::vector<double> &l1) {
   l1.assign(A.nr, 0.0);
+  std::vector<int> owner_lo(A.nr, 0), owner_hi(A.nr, A.nr);
+  for (size_t r = 0; r + 1 < part.size(); ++r)
+    for (int i = part[r]; i < part[r + 1]; ++i) { owner_lo[i] = part[r]; owner_hi[i] = part[r + 1]; }
 #pragma omp parallel for schedule(static)
   for (int i = 0; i < A.nr; ++i) {
     int b = A.ptr[i], e = A.ptr[i + 1];
     if (b == e) { l1[i] = 1.0; continue; }
     double d = A.val[b];
-    if (relax_type == 7) { l1[i] = d; continue; }
+    if (relax_type == 7 || relax_type == 3 || relax_type == 4 || relax_type == 6) { l1[i] = d; continue; }
+    if (is_l1_gs(relax_type)) {
+      // A.7: hypre_ParCSRComputeL1Norms option 4 (truncated, for Gauss-Seidel): |a_ii| + 1/2 sum_offd |a_ij|,
+      // reset to |a_ii| when it does not exceed 4/3 |a_ii|; negated for a negative diagonal
+      double ad = std::fabs(d), s = ad;
+      for (int k = b; k < e; ++k)
+        if (A.col[k] < owner_lo[i] || A.col[k] >= owner_hi[i]) s += 0.5 * std::fabs(A.val[k]);
+      if (s <= 4.0 / 3.0 * ad) s = ad;
+      l1[i] = (d < 0) ? -s : s;
+      continue;
+    }
     double s = 0.0;
     for (int k = b; k < e; ++k) s += std::fabs(A.val[k]);
     l1[i] = (d < 0) ? -s : s;
@@ -788,7 +805,7 @@ static void amg_setup(Sys &s) {
     Level &L = s.lev[l];
     int n = L.A.nr;
     if (o.relax_type == 16) cheby_setup(L, o);
-    else l1_norms(L.A, o.relax_type, L.l1);
+    else l1_norms(L.A, o.relax_type, L.part, L.l1);
     if (l > 0) { L.u.assign(n, 0.0); L.f.assign(n, 0.0); }
     L.vtemp.assign(n, 0.0);
     L.tmp.assign(n, 0.0);
@@ -866,6 +883,41 @@ static void relax(Level &L, const Options &o, double *u, const double *f, int po
     }
 #pragma omp parallel for schedule(static)
     for (int i = 0; i < n; ++i) u[i] = (zero_guess ? 0.0 : u[i]) + L.ds[i] * v[i];
+    return;
+  }
+  if (is_gs(o.relax_type)) {
+    // A.7 hybrid Gauss-Seidel (hypre_BoomerAMGRelaxHybridGaussSeidel_core, one thread per rank): Gauss-Seidel inside a
+    // rank's own rows, the values of off-rank columns frozen at their state before the sweep (one halo exchange per
+    // call, also for the symmetric variants).  relax 3 forward, 4 backward, 6 forward+backward: u_i = (f_i - sum_{j!=i}
+    // a_ij u_j) / a_ii; relax 13 / 14 / 8 the same orders with the l1 scaling: u_i += (f_i - sum_j a_ij u_j) / l1_i.
+    // Sums run in row storage order (diag block, then offd block).  relax_weight = omega = 1 (the mini-app sets neither).
+    const int t = o.relax_type;
+    const bool l1s = is_l1_gs(t), fwd = (t != 4 && t != 14), bwd = (t == 4 || t == 14 || t == 6 || t == 8);
+    std::vector<double> uold;
+    if (zero_guess) std::fill(u, u + n, 0.0);
+    int np = (int)L.part.size() - 1;
+    if (np > 1) uold.assign(u, u + n);
+    auto row = [&](int i, int lo, int hi) {
+      if (points != 0 && L.cf[i] != points) return;
+      int b = A.ptr[i], e = A.ptr[i + 1];
+      if (b == e) return;
+      double res = f[i];
+      if (l1s) {
+        if (L.l1[i] == 0.0) return;
+        for (int q = b; q < e; ++q) { int c = A.col[q]; res -= A.val[q] * ((c >= lo && c < hi) ? u[c] : uold[c]); }
+        u[i] += res / L.l1[i];
+      } else {
+        if (A.val[b] == 0.0) return;
+        for (int q = b + 1; q < e; ++q) { int c = A.col[q]; res -= A.val[q] * ((c >= lo && c < hi) ? u[c] : uold[c]); }
+        u[i] = res / A.val[b];
+      }
+    };
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int r = 0; r < np; ++r) {
+      int lo = L.part[r], hi = L.part[r + 1];
+      if (fwd) for (int i = lo; i < hi; ++i) row(i, lo, hi);
+      if (bwd) for (int i = hi - 1; i >= lo; --i) row(i, lo, hi);
+    }
     return;
   }
   // Jacobi-type (relax 7 / 18): u <- u + w (f - A u) ./ d, out of place
