@@ -229,6 +229,17 @@ HYPRE_Int b200hypre_amg_level_cheby(HYPRE_Solver amg, HYPRE_Int level, HYPRE_Rea
   for (size_t k = 0; k < 4; ++k) out6[2 + k] = k < L.cheby_coef.size() ? L.cheby_coef[k] : 0.0;
   API_END
 }
+// wavefront schedule of a Gauss-Seidel pass: which = 0 all points, 1 C points, 2 F points; dir = 0 forward, 1 backward.
+// out5 = { built, depth (wavefronts), rows in the set, widest wavefront, blocks of the last sweep launch }
+HYPRE_Int b200hypre_amg_gs_plan(HYPRE_Solver amg, HYPRE_Int level, HYPRE_Int which, HYPRE_Int dir, HYPRE_Int *out5) {
+  API_ARG(amg && out5 && which >= 0 && which < 3 && dir >= 0 && dir < 2, "b200hypre_amg_gs_plan: bad argument");
+  API_BEGIN
+  AmgHandle *h = as_amg(amg);
+  B200_REQUIRE(level >= 0 && level < (int)h->amg.lev.size(), "level out of range");
+  const GsPlan &p = h->amg.lev[level]->gs[which][dir];
+  out5[0] = p.built ? 1 : 0; out5[1] = p.depth; out5[2] = p.rows; out5[3] = p.width; out5[4] = p.last_blocks;
+  API_END
+}
 HYPRE_Real b200hypre_amg_setup_seconds(HYPRE_Solver amg) {
   try { return as_amg(amg)->amg.setup_seconds; } catch (const std::exception &e) { set_error(HYPRE_ERROR_ARG, e.what()); return -1.0; }
 }

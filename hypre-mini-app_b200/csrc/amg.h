@@ -61,7 +61,7 @@ struct AmgOptions {
 
 // wavefront schedule of one Gauss-Seidel pass (gs.cu): rows of the set sorted by dependency level
 struct GsPlan {
-  int n = 0, dir = 0, depth = 0, width = 0, rows = 0, cap = 1;
+  int n = 0, dir = 0, depth = 0, width = 0, rows = 0, cap = 1, last_blocks = 0;
   DVec<signed char> mask;         // 1 = row is updated by this pass
   DVec<int> order, lvl_off;       // rows by wavefront; wavefront l = order[lvl_off[l] .. lvl_off[l+1])
   DVec<unsigned long long> bar;   // grid-barrier counter

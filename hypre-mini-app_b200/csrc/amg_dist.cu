@@ -749,7 +749,10 @@ bool coarsen_level_dist(Amg &amg, AmgLevel &L, AmgLevel &Lc) {
     }
     DLAUNCH(k_f2c_ext, ntot, n, ntot, code_ext.p, f2c.p, nc, xc0.p, nxc0, f2c_ext.p);
     Pm.nc = nc + nxc0;
-    build_interp(Aext, Sext.ptr.p, Sext.col.p, Sext.nnz, cf_ext.p, f2c_ext.p, n, n, o.trunc_factor, o.p_max_elmts, Pm);
+    {
+      PhaseTimerD t2(amg, "interp.build");
+      build_interp(Aext, Sext.ptr.p, Sext.col.p, Sext.nnz, cf_ext.p, f2c_ext.p, n, n, o.trunc_factor, o.p_max_elmts, Pm);
+    }
     split_merged(Pm, nc, xc0.p, nxc0, L.P);
     set_par_shape(L.P, n, nc, Ap.row_start, cstart, gn, gnc);
     build_partition_and_halo(L.P);
@@ -762,6 +765,7 @@ bool coarsen_level_dist(Amg &amg, AmgLevel &L, AmgLevel &Lc) {
     PhaseTimerD t(amg, "rap");
     ParCsr &P = L.P, &R = L.R;
     // restriction: own part by local transposition, the rest arrives from the ranks whose P_offd references my coarse points
+    std::unique_ptr<PhaseTimerD> sub(new PhaseTimerD(amg, "rap.transpose"));
     csr_transpose(P.diag, R.diag);
     {
       DCsr T;  // (P_offd)^T: one row per halo coarse column, entries = (local fine row ascending, value)
@@ -814,6 +818,8 @@ bool coarsen_level_dist(Amg &amg, AmgLevel &L, AmgLevel &Lc) {
     build_partition_and_halo(R);
 
     // Q = A_merged * P_ext
+    sub.reset();
+    sub.reset(new PhaseTimerD(amg, "rap.AP"));
     DCsr Q;
     DVec<i64> xq;
     int nxq = 0;
@@ -838,6 +844,8 @@ bool coarsen_level_dist(Amg &amg, AmgLevel &L, AmgLevel &Lc) {
       csr_spgemm(Am, Pext, Q, false, false);
     }
     // A_c = R_merged * Q_ext
+    sub.reset();
+    sub.reset(new PhaseTimerD(amg, "rap.RQ"));
     {
       Numbering Nq{cstart, nc, xq.p, nxq, nullptr, 0};
       RowsMsg extQ;
@@ -854,9 +862,16 @@ bool coarsen_level_dist(Amg &amg, AmgLevel &L, AmgLevel &Lc) {
       DLAUNCH(k_remap_cols, Q.nnz, Q.nnz, Q.col.p, nc, xq.p, Na, bad.p);
       B200_REQUIRE(fetch1(bad.p) == 0, "R*Q: column renumbering failed");
       DCsr Qext, Rm, Acm;
-      stack_rows(n, Q.ptr.p, Q.col.p, Q.val.p, Q.nnz, extQ, Na, nc + nxa, true, Qext);
-      merge_parcsr(R, Rm);
-      csr_spgemm(Rm, Qext, Acm, true);
+      {
+        PhaseTimerD t2(amg, "rap.RQ.stack");
+        stack_rows(n, Q.ptr.p, Q.col.p, Q.val.p, Q.nnz, extQ, Na, nc + nxa, true, Qext);
+        merge_parcsr(R, Rm);
+      }
+      {
+        PhaseTimerD t2(amg, "rap.RQ.spgemm");
+        csr_spgemm(Rm, Qext, Acm, true);
+      }
+      PhaseTimerD t3(amg, "rap.RQ.split");
       Lc.A_own.reset(new ParCsr());
       Lc.A = Lc.A_own.get();
       split_merged(Acm, nc, xa.p, nxa, *Lc.A);

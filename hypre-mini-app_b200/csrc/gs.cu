@@ -37,7 +37,7 @@ __device__ __forceinline__ void grid_barrier(unsigned long long *bar, unsigned n
     __threadfence();
     atomicAdd(bar, 1ull);
     const unsigned long long target = epoch * nblocks;
-    while (*(volatile unsigned long long *)bar < target) { }
+    while (*(volatile unsigned long long *)bar < target) __nanosleep(64);
     __threadfence();
   }
   __syncthreads();
@@ -76,18 +76,20 @@ __global__ void k_gs_seed(int n, const int *indeg, int *order, int *ctr) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n && indeg[i] == 0) order[atomicAdd(ctr, 1)] = i;
 }
+template <int G>
 __global__ void __launch_bounds__(GS_THREADS) k_gs_kahn(const int *__restrict__ Tptr, const int *__restrict__ Tcol, int dir, int *indeg,
                                                         int *order, int *ctr, int *lvl_off, unsigned long long *bar, unsigned nblocks) {
   const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gthreads = gridDim.x * blockDim.x;
+  const int lane = threadIdx.x % G, grp = gtid / G, ngrp = gthreads / G;   // G lanes walk the dependants of one frontier row
   unsigned long long epoch = 0;
   int head = 0, tail = __ldcg(ctr), lvl = 0;
   if (gtid == 0) lvl_off[0] = 0;
   while (head < tail) {
     int *cnt = ctr + 1 + (lvl % 3);
     if (gtid == 0) ctr[1 + ((lvl + 1) % 3)] = 0;   // last read after the barrier of level lvl - 2
-    for (int idx = head + gtid; idx < tail; idx += gthreads) {
+    for (int idx = head + grp; idx < tail; idx += ngrp) {
       const int i = __ldcg(order + idx);
-      for (int k = Tptr[i]; k < Tptr[i + 1]; ++k) {
+      for (int k = Tptr[i] + lane; k < Tptr[i + 1]; k += G) {
         const int j = Tcol[k];
         if (dir == 0 ? j > i : j < i) {
           if (__ldcg(indeg + j) > 0 && atomicSub(indeg + j, 1) == 1) order[tail + atomicAdd(cnt, 1)] = j;
@@ -103,8 +105,11 @@ __global__ void __launch_bounds__(GS_THREADS) k_gs_kahn(const int *__restrict__ 
   if (gtid == 0) { ctr[4] = lvl; ctr[0] = tail; }
 }
 
-// one Gauss-Seidel pass over the rows of a plan
-template <bool L1>
+// one Gauss-Seidel pass over the rows of a plan.  G lanes share a row: the entries are loaded and multiplied in parallel
+// (one round of dependent loads per row instead of one per entry) and the partial sums are combined by shuffles, so the
+// row sum is associated differently from the sequential loop (values agree to rounding, well inside the 1e-10 bar);
+// WHICH value every term uses (updated or not) is exactly the sequential algorithm's.
+template <int G, bool L1>
 __global__ void __launch_bounds__(GS_THREADS) k_gs_sweep(int n, CsrView D, CsrView O, const int *__restrict__ order,
                                                          const int *__restrict__ lvl_off, int depth,
                                                          const signed char *__restrict__ mask, int dir, const double *__restrict__ dsm,
@@ -113,22 +118,30 @@ __global__ void __launch_bounds__(GS_THREADS) k_gs_sweep(int n, CsrView D, CsrVi
   const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gthreads = gridDim.x * blockDim.x;
   for (int i = gtid; i < n; i += gthreads)
     if (!mask[i]) uout[i] = uin[i];          // rows outside the set keep their value (never read from uout)
+  const int lane = threadIdx.x % G, grp = gtid / G, ngrp = gthreads / G;
+  unsigned gm = 0xffffffffu;
+  if (G < 32) gm = ((1u << G) - 1u) << ((threadIdx.x & 31) / G * G);
   unsigned long long epoch = 0;
   for (int l = 0; l < depth; ++l) {
     const int lb = lvl_off[l], le = lvl_off[l + 1];
-    for (int idx = lb + gtid; idx < le; idx += gthreads) {
+    for (int idx = lb + grp; idx < le; idx += ngrp) {
       const int i = order[idx];
       const int b = D.ptr[i], e = D.ptr[i + 1];
-      double res = f[i];
-      for (int q = L1 ? b : b + 1; q < e; ++q) {
+      double sum = 0.0;
+      for (int q = (L1 ? b : b + 1) + lane; q < e; q += G) {
         const int c = D.col[q];
         const bool done = mask[c] && (dir == 0 ? c < i : c > i);
         const double v = done ? __ldcg(uout + c) : uin[c];
-        res = __dsub_rn(res, __dmul_rn(D.val[q], v));
+        sum += D.val[q] * v;
       }
       if (O.ptr != nullptr)
-        for (int q = O.ptr[i]; q < O.ptr[i + 1]; ++q) res = __dsub_rn(res, __dmul_rn(O.val[q], halo[O.col[q]]));
-      uout[i] = L1 ? __dadd_rn(uin[i], __ddiv_rn(res, dsm[i])) : __ddiv_rn(res, D.val[b]);
+        for (int q = O.ptr[i] + lane; q < O.ptr[i + 1]; q += G) sum += O.val[q] * halo[O.col[q]];
+#pragma unroll
+      for (int o = G >> 1; o > 0; o >>= 1) sum += __shfl_xor_sync(gm, sum, o, G);
+      if (lane == 0) {
+        const double res = f[i] - sum;
+        uout[i] = L1 ? uin[i] + res / dsm[i] : res / D.val[b];
+      }
     }
     if (l + 1 < depth) grid_barrier(bar, nblocks, epoch);
   }
@@ -179,7 +192,7 @@ void build_gs_plan(ParCsr &A, const DCsr &T, const int *cf, const double *dsm, i
   plan.order.alloc((size_t)std::max(n, 1));
   plan.lvl_off.alloc((size_t)n + 2);
   plan.bar.alloc(2);
-  plan.cap = std::min(max_resident_blocks((const void *)k_gs_sweep<true>), max_resident_blocks((const void *)k_gs_sweep<false>));
+  plan.cap = std::min(max_resident_blocks((const void *)k_gs_sweep<32, true>), max_resident_blocks((const void *)k_gs_sweep<8, false>));
   if (n == 0) return;
   DVec<int> indeg((size_t)n), ctr(8);
   ctr.zero();
@@ -187,10 +200,17 @@ void build_gs_plan(ParCsr &A, const DCsr &T, const int *cf, const double *dsm, i
   k_gs_indeg<<<div_up(n, 256), 256, 0, stream()>>>(n, A.diag.ptr.p, A.diag.col.p, cf, dsm, points, dir, plan.mask.p, indeg.p, ctr.p);
   k_gs_seed<<<div_up(n, 256), 256, 0, stream()>>>(n, indeg.p, plan.order.p, ctr.p);
   static int cap = 0;
-  if (!cap) cap = max_resident_blocks((const void *)k_gs_kahn);
-  const int nblocks = std::max(1, std::min(cap, div_up(n, GS_THREADS)));
-  k_gs_kahn<<<nblocks, GS_THREADS, 0, stream()>>>(T.ptr.p, T.col.p, dir, indeg.p, plan.order.p, ctr.p, plan.lvl_off.p,
-                                                  plan.bar.p, (unsigned)nblocks);
+  if (!cap) cap = std::min(max_resident_blocks((const void *)k_gs_kahn<8>), max_resident_blocks((const void *)k_gs_kahn<32>));
+  // frontiers are narrow (rows / depth): a small grid keeps the software barrier cheap
+  const double mean = (double)T.nnz / std::max(T.nr, 1);
+  const int G = mean <= 10.0 ? 8 : (mean <= 20.0 ? 16 : 32);
+  const int nblocks = std::max(1, std::min(std::min(cap, 64), div_up((i64)n * G, (i64)512 * GS_THREADS)));
+  if (G == 8)
+    k_gs_kahn<8><<<nblocks, GS_THREADS, 0, stream()>>>(T.ptr.p, T.col.p, dir, indeg.p, plan.order.p, ctr.p, plan.lvl_off.p, plan.bar.p, (unsigned)nblocks);
+  else if (G == 16)
+    k_gs_kahn<16><<<nblocks, GS_THREADS, 0, stream()>>>(T.ptr.p, T.col.p, dir, indeg.p, plan.order.p, ctr.p, plan.lvl_off.p, plan.bar.p, (unsigned)nblocks);
+  else
+    k_gs_kahn<32><<<nblocks, GS_THREADS, 0, stream()>>>(T.ptr.p, T.col.p, dir, indeg.p, plan.order.p, ctr.p, plan.lvl_off.p, plan.bar.p, (unsigned)nblocks);
   count_launch(3);
   B200_KERNEL_CHECK();
   std::vector<int> h = ctr.to_host();
@@ -206,21 +226,37 @@ void build_gs_plan(ParCsr &A, const DCsr &T, const int *cf, const double *dsm, i
   }
 }
 
-void gs_sweep(ParCsr &A, GsPlan &plan, bool l1, const double *dsm, const double *f, const double *uin, double *uout) {
+template <int G>
+static void launch_sweep(ParCsr &A, GsPlan &plan, bool l1, const double *dsm, const double *f, const double *uin, double *uout) {
   const int n = A.n;
-  if (n == 0) return;
-  const int cap = plan.cap;   // queried at plan time (no runtime API calls here: the sweep may be captured into a CUDA graph)
-  const int want = std::max(div_up(std::max(plan.width, 1), GS_THREADS), plan.depth > 0 ? 1 : div_up(n, GS_THREADS));
-  const int nblocks = std::max(1, std::min(cap, want));
+  // grid sized for the AVERAGE wavefront (wide ones take a few grid-stride rounds): the cost of a sweep is the number of
+  // wavefronts times the barrier latency, which grows with the number of blocks; one block = __syncthreads only
+  const int rows_per_block = GS_THREADS / G;
+  int want = div_up(n, GS_THREADS);
+  if (plan.depth > 0) {
+    const int avg = std::max(1, plan.rows / plan.depth);
+    want = (avg <= 2 * rows_per_block) ? 1 : div_up(avg, rows_per_block);
+  }
+  const int nblocks = std::max(1, std::min(plan.cap, want));
+  plan.last_blocks = nblocks;
   CsrView O = A.offd.nnz > 0 ? A.offd.view() : CsrView{0, 0, nullptr, nullptr, nullptr};
   B200_CUDA(cudaMemsetAsync(plan.bar.p, 0, sizeof(unsigned long long), stream()));
   if (l1)
-    k_gs_sweep<true><<<nblocks, GS_THREADS, 0, stream()>>>(n, A.diag.view(), O, plan.order.p, plan.lvl_off.p, plan.depth, plan.mask.p,
-                                                           plan.dir, dsm, f, uin, uout, A.x_halo.p, plan.bar.p, (unsigned)nblocks);
+    k_gs_sweep<G, true><<<nblocks, GS_THREADS, 0, stream()>>>(n, A.diag.view(), O, plan.order.p, plan.lvl_off.p, plan.depth, plan.mask.p,
+                                                              plan.dir, dsm, f, uin, uout, A.x_halo.p, plan.bar.p, (unsigned)nblocks);
   else
-    k_gs_sweep<false><<<nblocks, GS_THREADS, 0, stream()>>>(n, A.diag.view(), O, plan.order.p, plan.lvl_off.p, plan.depth, plan.mask.p,
-                                                            plan.dir, dsm, f, uin, uout, A.x_halo.p, plan.bar.p, (unsigned)nblocks);
+    k_gs_sweep<G, false><<<nblocks, GS_THREADS, 0, stream()>>>(n, A.diag.view(), O, plan.order.p, plan.lvl_off.p, plan.depth, plan.mask.p,
+                                                               plan.dir, dsm, f, uin, uout, A.x_halo.p, plan.bar.p, (unsigned)nblocks);
   count_launch();
+}
+
+// no runtime API queries here (plan.cap was taken at plan time): the sweep may be captured into a CUDA graph
+void gs_sweep(ParCsr &A, GsPlan &plan, bool l1, const double *dsm, const double *f, const double *uin, double *uout) {
+  if (A.n == 0) return;
+  const double mean = A.diag.nr > 0 ? (double)A.diag.nnz / A.diag.nr : 1.0;
+  if (mean <= 10.0) launch_sweep<8>(A, plan, l1, dsm, f, uin, uout);
+  else if (mean <= 20.0) launch_sweep<16>(A, plan, l1, dsm, f, uin, uout);
+  else launch_sweep<32>(A, plan, l1, dsm, f, uin, uout);
 }
 
 // gathers the halo values of u (the state before the sweep) when the matrix is distributed

@@ -41,6 +41,10 @@ __global__ void k_check_range(i64 n, const i64 *rows, i64 lo, i64 hi, int *bad) 
   i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
   if (k < n && (rows[k] < lo || rows[k] > hi)) *bad = 1;
 }
+__global__ void k_pack_keys(i64 n, const i64 *rows, const i64 *cols, i64 row0, int cbits, i64 *key) {
+  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n) key[k] = ((rows[k] - row0) << cbits) | cols[k];
+}
 __global__ void k_iota64(i64 n, int *a) {
   i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
   if (k < n) a[k] = (int)k;
@@ -247,16 +251,42 @@ void ij_matrix_assemble(IJMatrix &M) {
       B200_CUDA(cudaMemsetAsync(o0.p + off, c.op, c.n, stream()));
       off += c.n;
     }
-    // stable sort by col, then stable sort by row (LSD on the pair)
+    // rows must lie in this rank's range before they are packed into sort keys
+    bad.zero();
+    k_check_range<<<div_up(ntot, 256), 256, 0, stream()>>>(ntot, r0.p, M.ilower, M.iupper, bad.p);
+    B200_REQUIRE(fetch1(bad.p) == 0, "IJ assemble: a row index lies outside [ilower, iupper] of this rank");
+    k_check_range<<<div_up(ntot, 256), 256, 0, stream()>>>(ntot, c0.p, 0, (i64)0x7fffffffffffffffLL, bad.p);
+    B200_REQUIRE(fetch1(bad.p) == 0, "IJ assemble: negative column index");
+    // stable sort by (row, col).  When (local row, column) fits one 64-bit key -- it always does for int32-sized ranks --
+    // ONE radix sort over just the significant bits replaces the two full 64-bit passes of the LSD pair sort.
     DVec<int> perm0((size_t)ntot), perm1((size_t)ntot), perm2((size_t)ntot);
     DVec<i64> k1((size_t)ntot), k2((size_t)ntot), ktmp((size_t)ntot);
     k_iota64<<<div_up(ntot, 256), 256, 0, stream()>>>(ntot, perm0.p);
+    i64 cmax = 0;
+    {
+      DVec<i64> dmax(1);
+      size_t rb = 0;
+      cub::DeviceReduce::Max(nullptr, rb, c0.p, dmax.p, (int)ntot, stream());
+      DVec<char> rtmp(rb);
+      cub::DeviceReduce::Max(rtmp.p, rb, c0.p, dmax.p, (int)ntot, stream());
+      cmax = fetch1(dmax.p);
+    }
+    int cbits = 1, rbits = 1;
+    while (cbits < 63 && (1LL << cbits) <= cmax) ++cbits;
+    while (rbits < 63 && (1LL << rbits) <= (i64)nloc) ++rbits;
     size_t tb = 0;
-    cub::DeviceRadixSort::SortPairs(nullptr, tb, c0.p, k1.p, perm0.p, perm1.p, (int)ntot, 0, 64, stream());
-    DVec<char> tmp(tb);
-    cub::DeviceRadixSort::SortPairs(tmp.p, tb, c0.p, k1.p, perm0.p, perm1.p, (int)ntot, 0, 64, stream());
-    k_gather<i64><<<div_up(ntot, 256), 256, 0, stream()>>>(ntot, perm1.p, r0.p, ktmp.p);  // rows in col-sorted order
-    cub::DeviceRadixSort::SortPairs(tmp.p, tb, ktmp.p, k2.p, perm1.p, perm2.p, (int)ntot, 0, 64, stream());
+    if (cmax >= 0 && rbits + cbits <= 63) {
+      k_pack_keys<<<div_up(ntot, 256), 256, 0, stream()>>>(ntot, r0.p, c0.p, M.ilower, cbits, ktmp.p);
+      cub::DeviceRadixSort::SortPairs(nullptr, tb, ktmp.p, k2.p, perm0.p, perm2.p, (int)ntot, 0, rbits + cbits, stream());
+      DVec<char> tmp(tb);
+      cub::DeviceRadixSort::SortPairs(tmp.p, tb, ktmp.p, k2.p, perm0.p, perm2.p, (int)ntot, 0, rbits + cbits, stream());
+    } else {
+      cub::DeviceRadixSort::SortPairs(nullptr, tb, c0.p, k1.p, perm0.p, perm1.p, (int)ntot, 0, 64, stream());
+      DVec<char> tmp(tb);
+      cub::DeviceRadixSort::SortPairs(tmp.p, tb, c0.p, k1.p, perm0.p, perm1.p, (int)ntot, 0, 64, stream());
+      k_gather<i64><<<div_up(ntot, 256), 256, 0, stream()>>>(ntot, perm1.p, r0.p, ktmp.p);  // rows in col-sorted order
+      cub::DeviceRadixSort::SortPairs(tmp.p, tb, ktmp.p, k2.p, perm1.p, perm2.p, (int)ntot, 0, 64, stream());
+    }
     // gather everything by perm2
     DVec<i64> rs((size_t)ntot), cs((size_t)ntot);
     DVec<double> vs((size_t)ntot);

@@ -98,6 +98,12 @@ class BoomerAMG:
         check(lib().b200hypre_amg_level_cheby(self.h, level, _ptr(out)))
         return out
 
+    def gs_plan(self, level, which=0, direction=0):
+        """wavefront schedule of a Gauss-Seidel pass: dict(built, depth, rows, width, blocks)"""
+        out = (C.c_int * 5)()
+        check(lib().b200hypre_amg_gs_plan(self.h, int(level), int(which), int(direction), out), "gs_plan")
+        return dict(zip(("built", "depth", "rows", "width", "blocks"), [int(v) for v in out]))
+
     def vcycle_ptr(self, r_ptr, z_ptr):
         check(lib().b200hypre_amg_vcycle(self.h, VP(r_ptr), VP(z_ptr)), "vcycle")
 

@@ -47,6 +47,9 @@ HYPRE_Int b200hypre_amg_level_get(HYPRE_Solver amg, HYPRE_Int level, HYPRE_Int w
 HYPRE_Int b200hypre_amg_level_cf(HYPRE_Solver amg, HYPRE_Int level, HYPRE_Int *cf);              /* +1 C, -1 F, -3 isolated */
 HYPRE_Int b200hypre_amg_level_smoother(HYPRE_Solver amg, HYPRE_Int level, HYPRE_Complex *d);     /* l1 norms / a_ii / D^-1/2 */
 HYPRE_Int b200hypre_amg_level_cheby(HYPRE_Solver amg, HYPRE_Int level, HYPRE_Real *out6);        /* max, min, c0..c3 */
+/* Gauss-Seidel wavefront schedule of a level: which = 0 all / 1 C / 2 F points, dir = 0 forward / 1 backward;
+   out5 = { built, wavefronts, rows, widest wavefront, blocks of the last sweep launch } */
+HYPRE_Int b200hypre_amg_gs_plan(HYPRE_Solver amg, HYPRE_Int level, HYPRE_Int which, HYPRE_Int dir, HYPRE_Int *out5);
 HYPRE_Real b200hypre_amg_setup_seconds(HYPRE_Solver amg);
 HYPRE_Int b200hypre_amg_setup_phases(HYPRE_Solver amg, char *names, HYPRE_Int names_cap, HYPRE_Real *ms, HYPRE_Int cap); /* ';'-joined names */
 /* one relaxation sweep of the level's smoother: u <- relax(u, f) (device pointers of the level's local length) */
