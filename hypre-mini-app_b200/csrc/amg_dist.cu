@@ -155,13 +155,21 @@ __global__ void k_merge_count(int n, const int *dptr, const int *optr, int *cnt)
   if (i < n) cnt[i] = (dptr[i + 1] - dptr[i]) + (optr ? (optr[i + 1] - optr[i]) : 0);
   if (i == n) cnt[i] = 0;
 }
+// G lanes per row: coalesced copies (thread-per-row loops run at a fraction of the HBM rate on 30-60 entry rows)
+template <int G>
 __global__ void k_merge_fill(int n, CsrView D, CsrView O, int shift, const int *mptr, int *mcol, double *mval) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) / G, lane = threadIdx.x % G;
   if (i >= n) return;
-  int w = mptr[i];
-  for (int k = D.ptr[i]; k < D.ptr[i + 1]; ++k, ++w) { mcol[w] = D.col[k]; mval[w] = D.val[k]; }
-  if (O.ptr)
-    for (int k = O.ptr[i]; k < O.ptr[i + 1]; ++k, ++w) { mcol[w] = O.col[k] + shift; mval[w] = O.val[k]; }
+  const int w = mptr[i], db = D.ptr[i], dn = D.ptr[i + 1] - db;
+  for (int k = lane; k < dn; k += G) { mcol[w + k] = D.col[db + k]; mval[w + k] = D.val[db + k]; }
+  if (O.ptr) {
+    const int ob = O.ptr[i], on = O.ptr[i + 1] - ob;
+    for (int k = lane; k < on; k += G) { mcol[w + dn + k] = O.col[ob + k] + shift; mval[w + dn + k] = O.val[ob + k]; }
+  }
+}
+inline int lanes_for(i64 nnz, int n) {
+  double mean = n > 0 ? (double)nnz / n : 1.0;
+  return mean <= 10.0 ? 8 : 32;
 }
 void merge_parcsr(const ParCsr &A, DCsr &M) {
   int n = A.n;
@@ -176,34 +184,58 @@ void merge_parcsr(const ParCsr &A, DCsr &M) {
   M.col.alloc((size_t)std::max<i64>(M.nnz, 1));
   M.val.alloc((size_t)std::max<i64>(M.nnz, 1));
   CsrView O = has_offd ? A.offd.view() : CsrView{0, 0, nullptr, nullptr, nullptr};
-  DLAUNCH(k_merge_fill, n, n, A.diag.view(), O, A.n_cols_local, M.ptr.p, M.col.p, M.val.p);
+  if (lanes_for(M.nnz, n) == 8) DLAUNCH(k_merge_fill<8>, (i64)n * 8, n, A.diag.view(), O, A.n_cols_local, M.ptr.p, M.col.p, M.val.p);
+  else DLAUNCH(k_merge_fill<32>, (i64)n * 32, n, A.diag.view(), O, A.n_cols_local, M.ptr.p, M.col.p, M.val.p);
   B200_KERNEL_CHECK();
 }
 
 // ---- split a merged matrix (columns own | external list) into the diag / offd blocks of a ParCsr; the offd column map is
 // compressed to the external columns that are actually referenced ------------------------------------------------------------
+template <int G>
+__device__ __forceinline__ unsigned grp_mask() {
+  if (G >= 32) return 0xffffffffu;
+  return ((1u << (G & 31)) - 1u) << (((threadIdx.x & 31) / G) * G);
+}
+template <int G>
 __global__ void k_split_count(int n, const int *mptr, const int *mcol, int n_own, int *dcnt, int *ocnt, int *used) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i == n) { dcnt[i] = 0; ocnt[i] = 0; }
-  if (i >= n) return;
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) / G, lane = threadIdx.x % G;
+  if (i > n) return;
+  if (i == n) { if (lane == 0) { dcnt[i] = 0; ocnt[i] = 0; } return; }
+  const unsigned gm = grp_mask<G>();
   int d = 0, o = 0;
-  for (int k = mptr[i]; k < mptr[i + 1]; ++k) {
+  for (int k = mptr[i] + lane; k < mptr[i + 1]; k += G) {
     int c = mcol[k];
     if (c < n_own) ++d;
     else { ++o; used[c - n_own] = 1; }
   }
-  dcnt[i] = d;
-  ocnt[i] = o;
+#pragma unroll
+  for (int off = G >> 1; off > 0; off >>= 1) { d += __shfl_xor_sync(gm, d, off, G); o += __shfl_xor_sync(gm, o, off, G); }
+  if (lane == 0) { dcnt[i] = d; ocnt[i] = o; }
 }
+// order-preserving split: positions inside the two output rows come from ballot prefixes over each chunk of G entries
+template <int G>
 __global__ void k_split_fill2(int n, const int *mptr, const int *mcol, const double *mval, int n_own, const int *newidx,
                               const int *dptr, int *dcol, double *dval, const int *optr, int *ocol, double *oval) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) / G, lane = threadIdx.x % G;
   if (i >= n) return;
+  const unsigned gm = grp_mask<G>();
+  const int first = (threadIdx.x & 31) - lane;
+  const unsigned lt = (1u << lane) - 1u;
   int wd = dptr[i], wo = optr[i];
-  for (int k = mptr[i]; k < mptr[i + 1]; ++k) {
-    int c = mcol[k];
-    if (c < n_own) { dcol[wd] = c; dval[wd] = mval[k]; ++wd; }
-    else { ocol[wo] = newidx[c - n_own]; oval[wo] = mval[k]; ++wo; }
+  const int b = mptr[i], e = mptr[i + 1];
+  for (int base = b; base < e; base += G) {
+    const int k = base + lane;
+    int c = 0;
+    bool valid = k < e, isd = false;
+    if (valid) { c = mcol[k]; isd = c < n_own; }
+    const unsigned bd = (__ballot_sync(gm, valid && isd) & gm) >> first;
+    const unsigned bo = (__ballot_sync(gm, valid && !isd) & gm) >> first;
+    if (valid) {
+      if (isd) { int w = wd + __popc(bd & lt); dcol[w] = c; dval[w] = mval[k]; }
+      else { int w = wo + __popc(bo & lt); ocol[w] = newidx[c - n_own]; oval[w] = mval[k]; }
+    }
+    wd += __popc(bd);
+    wo += __popc(bo);
   }
 }
 __global__ void k_gather_used(int n, const int *used, const int *pos, const i64 *ext, i64 *out) {
@@ -237,7 +269,9 @@ void split_merged(const DCsr &M, int n_own, const i64 *ext, int n_ext, ParCsr &o
   out.n_cols_local = n_own;
   DVec<int> dcnt((size_t)n + 1), ocnt((size_t)n + 1), used((size_t)n_ext + 1), pos((size_t)n_ext + 1);
   used.zero();
-  DLAUNCH(k_split_count, (i64)n + 1, n, M.ptr.p, M.col.p, n_own, dcnt.p, ocnt.p, used.p);
+  const int G = lanes_for(M.nnz, n);
+  if (G == 8) DLAUNCH(k_split_count<8>, ((i64)n + 1) * 8, n, M.ptr.p, M.col.p, n_own, dcnt.p, ocnt.p, used.p);
+  else DLAUNCH(k_split_count<32>, ((i64)n + 1) * 32, n, M.ptr.p, M.col.p, n_own, dcnt.p, ocnt.p, used.p);
   out.diag.nr = out.offd.nr = n;
   out.diag.nc = n_own;
   out.diag.ptr.alloc((size_t)n + 1);
@@ -261,8 +295,12 @@ void split_merged(const DCsr &M, int n_own, const i64 *ext, int n_ext, ParCsr &o
   out.diag.val.alloc((size_t)std::max<i64>(out.diag.nnz, 1));
   out.offd.col.alloc((size_t)std::max<i64>(out.offd.nnz, 1));
   out.offd.val.alloc((size_t)std::max<i64>(out.offd.nnz, 1));
-  DLAUNCH(k_split_fill2, n, n, M.ptr.p, M.col.p, M.val.p, n_own, pos.p, out.diag.ptr.p, out.diag.col.p, out.diag.val.p,
-          out.offd.ptr.p, out.offd.col.p, out.offd.val.p);
+  if (G == 8)
+    DLAUNCH(k_split_fill2<8>, (i64)n * 8, n, M.ptr.p, M.col.p, M.val.p, n_own, pos.p, out.diag.ptr.p, out.diag.col.p, out.diag.val.p,
+            out.offd.ptr.p, out.offd.col.p, out.offd.val.p);
+  else
+    DLAUNCH(k_split_fill2<32>, (i64)n * 32, n, M.ptr.p, M.col.p, M.val.p, n_own, pos.p, out.diag.ptr.p, out.diag.col.p, out.diag.val.p,
+            out.offd.ptr.p, out.offd.col.p, out.offd.val.p);
   build_offd_rows(out);
   B200_KERNEL_CHECK();
 }

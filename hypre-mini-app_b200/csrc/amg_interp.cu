@@ -79,7 +79,8 @@ template <int G, int H, int CAP, int MODE>
 __global__ void __launch_bounds__(256) k_interp_grp(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__ Scol,
                                                     const signed char *__restrict__ Scf, const int *__restrict__ cf,
                                                     const int *__restrict__ f2c, int n_own, int n_rows, double tf, int pmax, int lo,
-                                                    int *lraw, int *len, const int *__restrict__ Pptr, int *Pcol, double *Pval) {
+                                                    int *lraw, int *len, const int *__restrict__ Pptr, int *Pcol, double *Pval,
+                                                    const int *__restrict__ row_list) {
   constexpr int GROUPS = 256 / G;
   constexpr bool COUNT = (MODE == 0);
   __shared__ int s_keys[GROUPS][H];
@@ -87,8 +88,9 @@ __global__ void __launch_bounds__(256) k_interp_grp(rows::Csr A, const int *__re
   __shared__ int s_lc[GROUPS][CAP];
   __shared__ double s_lv[GROUPS][CAP];
   const int g = threadIdx.x / G, lane = threadIdx.x % G;
-  const int i = blockIdx.x * GROUPS + g;
-  if (i >= n_rows) return;
+  const int slot = blockIdx.x * GROUPS + g;
+  if (slot >= n_rows) return;
+  const int i = row_list ? row_list[slot] : slot;   // n_rows = length of the list when one is given
   const unsigned gm = group_mask<G>();
   const unsigned lane_lt = gm & ((1u << (threadIdx.x & 31)) - 1u);
   const int first_lane = (threadIdx.x & 31) - lane;
@@ -447,12 +449,29 @@ void launch_tiers(bool small_tier, const rows::Csr &A, const int *Sptr, const in
   int lo = -1;
   if (small_tier) {
     k_interp_grp<8, 64, 32, MODE><<<div_up(n_rows, 32), 256, 0, stream()>>>(A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo,
-                                                                          lraw, len, Pptr, Pcol, Pval);
+                                                                          lraw, len, Pptr, Pcol, Pval, nullptr);
     count_launch();
     lo = 32;
+    if (MODE != 1) {
+      // the rows the small tier could not hold are few (often none): run the large tier on their list only
+      constexpr int CAP = 1 << 20;
+      DVec<int> cnt(1), list((size_t)CAP);
+      cnt.zero();
+      k_collect_todo<<<div_up(n_rows, 256), 256, 0, stream()>>>(n_rows, lraw, cnt.p, list.p, CAP);
+      count_launch();
+      const int left = fetch1(cnt.p);
+      if (left == 0) return;
+      if (left <= CAP) {
+        k_interp_grp<32, 256, 128, MODE><<<div_up(left, 8), 256, 0, stream()>>>(A, Sptr, Scol, Scf, cf, f2c, n_own, left, tf, pmax, lo, lraw,
+                                                                               len, Pptr, Pcol, Pval, list.p);
+        count_launch();
+        B200_KERNEL_CHECK();
+        return;
+      }
+    }
   }
   k_interp_grp<32, 256, 128, MODE><<<div_up(n_rows, 8), 256, 0, stream()>>>(A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo,
-                                                                           lraw, len, Pptr, Pcol, Pval);
+                                                                           lraw, len, Pptr, Pcol, Pval, nullptr);
   count_launch();
   B200_KERNEL_CHECK();
 }
@@ -481,12 +500,17 @@ void build_interp(const DCsr &Aext, const int *Sptr, const int *Scol, i64 S_nnz,
   B200_CUDA(cudaMemsetAsync(len.p + n_rows, 0, sizeof(int), stream()));
   DVec<int> tcol;
   DVec<double> tval;
+  // algorithmic bytes of the row kernels: A and S read once, markers, and the (at most pmax wide) rows of P written once
+  {
+  ProfScope prof("interp_rows", 12.0 * (double)Aext.nnz + 4.0 * (double)S_nnz + 5.0 * (double)S_nnz / 4.0 + 16.0 * (double)Aext.nr +
+                                    12.0 * (double)n_rows * (pmax > 0 ? pmax : 4) * 0.75);
   if (single) {
     tcol.alloc((size_t)n_rows * pmax);
     tval.alloc((size_t)n_rows * pmax);
     launch_tiers<2>(small_tier, A, Sptr, Scol, Scf.p, cf, f2c, n_own, n_rows, tf, pmax, lraw.p, len.p, nullptr, tcol.p, tval.p);
   } else {
     launch_tiers<0>(small_tier, A, Sptr, Scol, Scf.p, cf, f2c, n_own, n_rows, tf, pmax, lraw.p, len.p, nullptr, nullptr, nullptr);
+  }
   }
   // rows beyond the last tier
   DVec<int> todo_count(1), todo((size_t)65536), err(1);
