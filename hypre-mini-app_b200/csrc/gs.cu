@@ -12,10 +12,11 @@
 //   setup  (build_gs_plan): in-degrees from the rows, then Kahn's peeling in ONE persistent kernel (frontier queue in
 //          global memory, the transposed pattern gives the dependants, software grid barrier between wavefronts).
 //          The queue is the row permutation "sorted by wavefront", the frontier boundaries are the level offsets.
-//   sweep  (gs_sweep): ONE persistent kernel per direction; wavefront l = rows order[off[l] .. off[l+1]), one thread per
+//   sweep  (gs_sweep): ONE persistent kernel per direction; wavefront l = rows order[off[l] .. off[l+1]), G lanes per
 //          row, grid barrier between wavefronts.  Values are read from `uout` for rows already updated in this sweep
-//          and from `uin` otherwise (out of place: a nonsymmetric pattern cannot create a write-after-read hazard), the
-//          row sum runs in storage order (diag block, then offd block) with unfused multiply / subtract like the oracle.
+//          and from `uin` otherwise (out of place: a nonsymmetric pattern cannot create a write-after-read hazard); the
+//          row sum (diag block, then offd block) is combined by a shuffle tree, so values agree with the sequential loop
+//          to rounding while the choice "updated or not" of every term is exactly the sequential algorithm's.
 // The grid never exceeds the number of co-resident blocks, so the software barrier cannot deadlock.
 #include "amg.h"
 #include <algorithm>
