@@ -7,7 +7,7 @@
 //     preconditioner handle, HypreSystem.cpp:99-110);
 //   * build_27pt_stencil / build_7pt_stencil call the device generator of libb200hypre with true-neighbour halo columns
 //     (the reference glue at HypreSystem.cpp:1555 maps halo indices to fictitious global columns);
-//   * methods / preconditioners outside the built path (cg, bicg, fgmres, cogmres, ilu) throw instead of running.
+//   * the ILU solver / preconditioner (outside the built path) throws instead of running.
 #include "HypreSystem.h"
 
 #include <algorithm>
@@ -66,8 +66,12 @@ void HypreSystem::setup_precon_and_solver() {
 
   if (method == "gmres") setup_gmres();
   else if (method == "boomeramg") setup_boomeramg_solver();
-  else if (method == "cg" || method == "bicg" || method == "fgmres" || method == "cogmres" || method == "ilu")
-    throw std::runtime_error("solver method '" + method + "' is outside the built path (gmres | boomeramg; SURVEY.md §8f.2)");
+  else if (method == "cg") setup_cg();
+  else if (method == "bicg") setup_bicg();
+  else if (method == "fgmres") setup_fgmres();
+  else if (method == "cogmres") setup_cogmres();
+  else if (method == "ilu")
+    throw std::runtime_error("solver method 'ilu' is outside the built path (SURVEY.md §8f.4)");
   else throw std::runtime_error("Invalid option for solver method provided: " + method);
   MPI_Barrier(comm_);
   fflush(stdout);
@@ -93,6 +97,8 @@ void HypreSystem::setup_boomeramg_solver() {
   solverSetupPtr_ = &HYPRE_BoomerAMGSetup;
   solverPrecondPtr_ = nullptr;
   solverSolvePtr_ = &HYPRE_BoomerAMGSolve;
+  solverItersPtr_ = &HYPRE_BoomerAMGGetNumIterations;
+  solverRelresPtr_ = &HYPRE_BoomerAMGGetFinalRelativeResidualNorm;
   usePrecond_ = false;
 }
 
@@ -203,8 +209,33 @@ void HypreSystem::setup_gmres() {
   solverSetupPtr_ = &HYPRE_ParCSRGMRESSetup;
   solverPrecondPtr_ = &HYPRE_ParCSRGMRESSetPrecond;
   solverSolvePtr_ = &HYPRE_ParCSRGMRESSolve;
-  gmresSolver_ = true;
+  solverItersPtr_ = &HYPRE_ParCSRGMRESGetNumIterations;
+  solverRelresPtr_ = &HYPRE_ParCSRGMRESGetFinalRelativeResidualNorm;
 }
+
+// ---- HypreSystem.cpp:372-388, 406-421, 423-438, 440-455: the sibling Krylov methods -----------------------------------------
+#define B200_KRYLOV_SETUP(FN, NAME, KDIM_LINE, EXTRA)                                         \
+  void HypreSystem::FN() {                                                                    \
+    YAML::Node node = inpfile_["solver_settings"];                                            \
+    HYPRE_ParCSR##NAME##Create(comm_, &solver_);                                              \
+    HYPRE_ParCSR##NAME##SetTol(solver_, get_optional(node, "tolerance", 1.0e-5));             \
+    HYPRE_ParCSR##NAME##SetMaxIter(solver_, get_optional(node, "max_iterations", 1000));      \
+    KDIM_LINE;                                                                                \
+    HYPRE_ParCSR##NAME##SetPrintLevel(solver_, get_optional(node, "print_level", 4));         \
+    EXTRA;                                                                                    \
+    solverDestroyPtr_ = &HYPRE_ParCSR##NAME##Destroy;                                         \
+    solverSetupPtr_ = &HYPRE_ParCSR##NAME##Setup;                                             \
+    solverPrecondPtr_ = &HYPRE_ParCSR##NAME##SetPrecond;                                      \
+    solverSolvePtr_ = &HYPRE_ParCSR##NAME##Solve;                                             \
+    solverItersPtr_ = &HYPRE_ParCSR##NAME##GetNumIterations;                                  \
+    solverRelresPtr_ = &HYPRE_ParCSR##NAME##GetFinalRelativeResidualNorm;                     \
+  }
+B200_KRYLOV_SETUP(setup_cogmres, COGMRES, HYPRE_ParCSRCOGMRESSetKDim(solver_, get_optional(node, "kspace", 10)),
+                  HYPRE_ParCSRCOGMRESSetCGS(solver_, get_optional(node, "cgs", 0)))
+B200_KRYLOV_SETUP(setup_fgmres, FlexGMRES, HYPRE_ParCSRFlexGMRESSetKDim(solver_, get_optional(node, "kspace", 10)), (void)0)
+B200_KRYLOV_SETUP(setup_bicg, BiCGSTAB, (void)0 /* kspace is commented out at :431 */, (void)0)
+B200_KRYLOV_SETUP(setup_cg, PCG, (void)0 /* kspace is commented out at :448 */, (void)0)
+#undef B200_KRYLOV_SETUP
 
 // ---- HypreSystem.cpp:499-523: the caller owns and destroys IJ objects, solver and preconditioner separately -------------------
 void HypreSystem::destroy_system() {
@@ -357,13 +388,8 @@ void HypreSystem::solve() {
     solve += std::chrono::duration<double>(clk::now() - stop2).count();
     MPI_Barrier(comm_);
     fflush(stdout);
-    if (gmresSolver_) {
-      HYPRE_ParCSRGMRESGetNumIterations(solver_, &iterations_);
-      HYPRE_ParCSRGMRESGetFinalRelativeResidualNorm(solver_, &relres_);
-    } else {
-      HYPRE_BoomerAMGGetNumIterations(solver_, &iterations_);
-      HYPRE_BoomerAMGGetFinalRelativeResidualNorm(solver_, &relres_);
-    }
+    solverItersPtr_(solver_, &iterations_);
+    solverRelresPtr_(solver_, &relres_);
     if (iproc_ == 0) printf("Solve %d: iterations = %d, final relative residual norm = %e\n", i, iterations_, relres_);
   }
   timers_.emplace_back("Preconditioner setup", setup);

@@ -5,8 +5,8 @@
 // destroy_system, driven by /root/reference/src/main.cpp:172-192), same YAML keys and defaults, same
 // timer names, the seven solver / preconditioner function pointers (HypreSystem.h:265-277) and the COO staging
 // vectors rows_/cols_/vals_ (HypreSystem.h:174-227).  Written from scratch against the behaviour documented in
-// SURVEY.md; only GMRES (+ BoomerAMG-as-solver) with BoomerAMG / no preconditioner is wired, the other methods of
-// HypreSystem.cpp:69-86 raise "outside the built path" (SURVEY.md §8f).
+// SURVEY.md; methods gmres | cogmres | fgmres | bicg | cg | boomeramg with BoomerAMG / no preconditioner are wired, the
+// ILU solver / preconditioner of HypreSystem.cpp:61,82 raises "outside the built path" (SURVEY.md §8f.4).
 #pragma once
 #include <string>
 #include <utility>
@@ -68,6 +68,10 @@ class HypreSystem {
   void setup_boomeramg_precond();  // :119-326
   void setup_boomeramg_solver();   // :91-117
   void setup_gmres();              // :390-404
+  void setup_cogmres();            // :372-388
+  void setup_fgmres();             // :406-421
+  void setup_bicg();               // :423-438
+  void setup_cg();                 // :440-455
 
   MPI_Comm comm_;
   YAML::Node &inpfile_;
@@ -104,7 +108,10 @@ class HypreSystem {
   bool segregatedSolve_ = true;
   double rtol_ = 1.0e-6, atol_ = 1.0e-8;
   bool solveComplete_ = false, checkSolution_ = false, outputSystem_ = false, outputSolution_ = false, usePrecond_ = true;
-  bool writeAmgMatrices_ = false, complexNumbers_ = false, gmresSolver_ = false;
+  bool writeAmgMatrices_ = false, complexNumbers_ = false;
+  // result accessors of the selected solver (reported after every solve; not in the reference, which prints nothing)
+  HYPRE_Int (*solverItersPtr_)(HYPRE_Solver, HYPRE_Int *) = nullptr;
+  HYPRE_Int (*solverRelresPtr_)(HYPRE_Solver, HYPRE_Real *) = nullptr;
   int iterations_ = 0;
   double relres_ = 0.0;
   bool allClose_ = true;

@@ -22,6 +22,16 @@ GmresHandle *as_gmres(HYPRE_Solver s) {
   B200_REQUIRE(b && b->kind == SolverBase::GMRES, "handle is not a ParCSR GMRES solver");
   return static_cast<GmresHandle *>(b);
 }
+KrylovHandle *as_krylov(HYPRE_Solver s, int method) {
+  SolverBase *b = as_solver(s);
+  B200_REQUIRE(b && b->kind == SolverBase::KRYLOV && static_cast<KrylovHandle *>(b)->k.method == method,
+               method == Krylov::PCG ? "handle is not a ParCSR PCG solver" : "handle is not a ParCSR BiCGSTAB solver");
+  return static_cast<KrylovHandle *>(b);
+}
+int accumulate_error(int code) {
+  g_error_flag |= code;
+  return g_error_flag;
+}
 AmgHandle *as_amg(HYPRE_Solver s) {
   SolverBase *b = as_solver(s);
   B200_REQUIRE(b && b->kind == SolverBase::AMG, "handle is not a BoomerAMG solver");

@@ -267,18 +267,32 @@ HYPRE_Int b200hypre_amg_vcycle(HYPRE_Solver amg, const HYPRE_Complex *r, HYPRE_C
 
 // ---- GMRES extras / instrumentation -------------------------------------------------------------------------------------
 HYPRE_Int b200hypre_gmres_set_orthogonalization(HYPRE_Solver gmres, HYPRE_Int kind) {
-  API_ARG(gmres && (kind == 0 || kind == 1), "b200hypre_gmres_set_orthogonalization: kind must be 0 (MGS) or 1 (CGS2)");
+  API_ARG(gmres && kind >= 0 && kind <= 2, "b200hypre_gmres_set_orthogonalization: kind must be 0 (MGS), 1 (CGS2) or 2 (CGS)");
   API_BEGIN as_gmres(gmres)->g.orth = kind; API_END
 }
-HYPRE_Int b200hypre_gmres_get_history(HYPRE_Solver gmres, HYPRE_Real *out, HYPRE_Int cap) {
+HYPRE_Int b200hypre_gmres_get_history(HYPRE_Solver solver, HYPRE_Real *out, HYPRE_Int cap) {  // any Krylov handle
   try {
-    const std::vector<double> &h = as_gmres(gmres)->g.history;
-    for (int k = 0; k < cap && k < (int)h.size(); ++k) out[k] = h[k];
-    return (HYPRE_Int)h.size();
-  } catch (const std::exception &e) { set_error(HYPRE_ERROR_ARG, e.what()); return 0; }
+    SolverBase *b = as_solver(solver);
+    B200_REQUIRE(b && (b->kind == SolverBase::GMRES || b->kind == SolverBase::KRYLOV), "handle is not a Krylov solver");
+    const std::vector<double> &h = b->kind == SolverBase::GMRES ? static_cast<GmresHandle *>(b)->g.history : static_cast<KrylovHandle *>(b)->k.history;
+    int n = (int)h.size();
+    for (int i = 0; i < n && i < cap; ++i) out[i] = h[i];
+    return n;
+  } catch (const std::exception &e) { set_error(HYPRE_ERROR_ARG, e.what()); return -1; }
 }
-HYPRE_Real b200hypre_gmres_solve_seconds(HYPRE_Solver gmres) {
-  try { return as_gmres(gmres)->g.solve_seconds; } catch (const std::exception &e) { set_error(HYPRE_ERROR_ARG, e.what()); return -1.0; }
+HYPRE_Real b200hypre_gmres_solve_seconds(HYPRE_Solver solver) {  // any Krylov handle
+  try {
+    SolverBase *b = as_solver(solver);
+    B200_REQUIRE(b && (b->kind == SolverBase::GMRES || b->kind == SolverBase::KRYLOV), "handle is not a Krylov solver");
+    return b->kind == SolverBase::GMRES ? static_cast<GmresHandle *>(b)->g.solve_seconds : static_cast<KrylovHandle *>(b)->k.solve_seconds;
+  } catch (const std::exception &e) { set_error(HYPRE_ERROR_ARG, e.what()); return -1.0; }
+}
+HYPRE_Int b200hypre_solver_converged(HYPRE_Solver solver) {  // any Krylov handle: 1 if the last Solve met its stopping test
+  try {
+    SolverBase *b = as_solver(solver);
+    B200_REQUIRE(b && (b->kind == SolverBase::GMRES || b->kind == SolverBase::KRYLOV), "handle is not a Krylov solver");
+    return b->kind == SolverBase::GMRES ? static_cast<GmresHandle *>(b)->g.converged : static_cast<KrylovHandle *>(b)->k.converged;
+  } catch (const std::exception &e) { set_error(HYPRE_ERROR_ARG, e.what()); return -1; }
 }
 unsigned long long b200hypre_launch_count(void) { return ctx().launches; }
 // out[0..3] = bytes the library's stream-ordered pool holds from the driver (now / high-water) and bytes in use (now / high)

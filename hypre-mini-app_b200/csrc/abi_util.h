@@ -10,13 +10,17 @@ namespace b200 {
 int set_error(int code, const char *what);
 
 struct SolverBase {
-  enum Kind { GMRES = 1, AMG = 2 } kind;
+  enum Kind { GMRES = 1, AMG = 2, KRYLOV = 3 } kind;
   explicit SolverBase(Kind k) : kind(k) {}
   virtual ~SolverBase() {}
 };
 struct GmresHandle : SolverBase {
   Gmres g;
   GmresHandle() : SolverBase(GMRES) {}
+};
+struct KrylovHandle : SolverBase {   // PCG / BiCGSTAB
+  Krylov k;
+  KrylovHandle() : SolverBase(KRYLOV) {}
 };
 struct AmgHandle : SolverBase {
   Amg amg;
@@ -35,6 +39,8 @@ inline IJVector *as_ijv(HYPRE_IJVector v) { return reinterpret_cast<IJVector *>(
 inline SolverBase *as_solver(HYPRE_Solver s) { return reinterpret_cast<SolverBase *>(s); }
 GmresHandle *as_gmres(HYPRE_Solver s);
 AmgHandle *as_amg(HYPRE_Solver s);
+KrylovHandle *as_krylov(HYPRE_Solver s, int method);
+int accumulate_error(int code);  // OR a solver return code (e.g. HYPRE_ERROR_CONV) into the global flag, return the flag
 
 bool precond_zero_guess_hint();
 void comm_get_unique_id(void *out128);

@@ -115,11 +115,14 @@ typedef int (*PrecondFn)(void *solver, void *A, void *b, void *x);  // HYPRE_Ptr
 struct Gmres {
   double tol = 1e-6, atol = 0.0;
   int max_iter = 1000, min_iter = 0, k_dim = 5, print_level = 0, logging = 0;
-  int orth = 1;                   // 0 = modified Gram-Schmidt (hypre's), 1 = fused CGS2 (default)
+  int orth = 1;                   // 0 = modified Gram-Schmidt (hypre's), 1 = fused CGS2 (default), 2 = fused one-pass CGS
+  int variant = 0;                // 0 = GMRES, 1 = FlexGMRES (keeps z_j = M^{-1} v_j), 2 = COGMRES (orth from `cgs`)
+  int cgs = 1, unroll = 0;        // COGMRES knobs (HYPRE_ParCSRCOGMRESSetCGS / SetUnroll)
   PrecondFn precond = nullptr, precond_setup = nullptr;
   void *precond_data = nullptr;
   // workspace
   DVec<double> V;                 // (k_dim + 1) basis vectors, leading dimension ld
+  DVec<double> Z;                 // FlexGMRES only: k_dim preconditioned vectors
   i64 ld = 0;
   DVec<double> r, w, hdev;
   DotWork dw;
@@ -132,6 +135,27 @@ struct Gmres {
 };
 void gmres_setup(Gmres &g, ParCsr &A, ParVec &b, ParVec &x);
 int gmres_solve(Gmres &g, ParCsr &A, ParVec &b, ParVec &x);
+
+// ---- PCG / BiCGSTAB (krylov.cu) ---------------------------------------------------------------------------------------
+struct Krylov {
+  enum Method { PCG = 0, BICGSTAB = 1 } method = PCG;
+  double tol = 1e-6, atol = 0.0;
+  int max_iter = 1000, min_iter = 0, print_level = 0, logging = 0, two_norm = 0;
+  PrecondFn precond = nullptr, precond_setup = nullptr;
+  void *precond_data = nullptr;
+  DVec<double> W;                 // work vectors, leading dimension ld
+  i64 ld = 0;
+  DVec<double> hdev;
+  DotWork dw;
+  int n = 0;
+  int num_iterations = 0, converged = 0;
+  double rel_residual_norm = 0.0;
+  std::vector<double> history;
+  double solve_seconds = 0;
+};
+void set_precond_zero_guess_hint(bool v);  // the next preconditioner call may treat its output vector as zero (gmres.cu)
+void krylov_setup(Krylov &k, ParCsr &A, ParVec &b, ParVec &x);
+int krylov_solve(Krylov &k, ParCsr &A, ParVec &b, ParVec &x);
 
 // ---- IJ interface (ij.cu) --------------------------------------------------------------------------------------------
 struct IJMatrix {

@@ -271,24 +271,27 @@ void amg_vcycle(Amg &amg, const double *rhs, double *z) {
 }
 
 void amg_solve(Amg &amg, ParCsr &A, const double *b, double *x, int *iters, double *relres) {
+  // hypre_BoomerAMGSolve as a solver (method: boomeramg, HypreSystem.cpp:91-117): cycle while ||b - A x|| / ||b|| >= tol
+  // and cycles < max_iter; each cycle is x += M^{-1} (b - A x) with the zero-guess V-cycle (the cycle is affine in x).
   int n = A.n;
   i64 ld = ((i64)n + 1) & ~1LL;
   DVec<double> r(ld), z(ld);
   double bnorm = std::sqrt(dot_host(amg.dw, b, b, n));
-  double den = bnorm > 0 ? bnorm : 1.0;
   int it = 0;
-  double rn = 0;
+  double rel = 0;
   while (true) {
     SpmvArgs a; a.x = x; a.y = r.p; a.b = b;
     par_spmv(A, SPMV_RES, a);
-    rn = std::sqrt(dot_host(amg.dw, r.p, r.p, n));
-    if (it >= amg.opt.max_iter || rn / den <= amg.opt.tol) break;
+    double rn = std::sqrt(dot_host(amg.dw, r.p, r.p, n));
+    rel = bnorm ? rn / bnorm : rn;
+    if (amg.opt.print_level > 1 && ctx().rank == 0) printf("    Cycle %2d   %e    %e\n", it, rn, rel);
+    if (!(rel >= amg.opt.tol) || it >= amg.opt.max_iter) break;
     amg_vcycle(amg, r.p, z.p);
     vec_axpy(1.0, z.p, x, n);
     ++it;
   }
   if (iters) *iters = it;
-  if (relres) *relres = rn / den;
+  if (relres) *relres = rel;
 }
 
 }  // namespace b200

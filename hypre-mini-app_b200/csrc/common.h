@@ -174,6 +174,8 @@ struct DotWork {
 };
 void multi_dot(DotWork &w, const double *V, i64 ld, int k, const double *x, i64 n, double *out);  // out[j] = <V_j, x>, j<k
 void multi_axpy_norm(DotWork &w, const double *V, i64 ld, int k, const double *h, double *x, i64 n, double *norm2_out);  // x -= sum h_j V_j ; norm2 = <x,x>
+// x += a p ; r -= a s ; out[0] = <r,r>, out[1] = <t,r> of the updated r (t null: only out[0]; out null: no reduction)
+void fused_update2(DotWork &w, double a, const double *p, const double *s, double *x, double *r, const double *t, i64 n, double *out);
 void lin_comb(double *out, const double *V, i64 ld, int k, const double *coef_dev, i64 n);  // out = sum coef_j V_j
 double dot_host(DotWork &w, const double *a, const double *b, i64 n);  // local + allreduce, returned on host
 

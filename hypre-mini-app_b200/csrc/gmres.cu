@@ -1,4 +1,5 @@
-// gmres.cu -- restarted right-preconditioned GMRES on the device (hypre_GMRESSolve semantics).
+// gmres.cu -- restarted right-preconditioned GMRES on the device (hypre_GMRESSolve semantics), and its
+// siblings FlexGMRES (HypreSystem.cpp:406-421) and COGMRES (:372-388), which share the restart / Givens skeleton.
 // Replaces HYPRE_ParCSRGMRESSetup / HYPRE_ParCSRGMRESSolve (/root/reference/src/HypreSystem.cpp:401,403 called at
 // :692 and :723).  Control flow, convergence tests ("false convergence" re-checks with the true residual), Givens
 // rotations, back substitution and the restart update follow A.1 line by line; the Hessenberg scalars live on the
@@ -18,6 +19,7 @@ namespace {
 thread_local bool g_zero_guess_hint = false;
 }
 bool precond_zero_guess_hint() { return g_zero_guess_hint; }
+void set_precond_zero_guess_hint(bool v) { g_zero_guess_hint = v; }
 
 void gmres_setup(Gmres &g, ParCsr &A, ParVec &b, ParVec &x) {
   ensure_init();
@@ -26,6 +28,8 @@ void gmres_setup(Gmres &g, ParCsr &A, ParVec &b, ParVec &x) {
   if (g.ld == 0) g.ld = 2;
   g.V.alloc((size_t)g.ld * (g.k_dim + 1));
   g.V.zero();
+  if (g.variant == 1) { g.Z.alloc((size_t)g.ld * g.k_dim); g.Z.zero(); }
+  if (g.variant == 2) g.orth = (g.cgs >= 2) ? 1 : 2;  // COGMRES: classical Gram-Schmidt, one pass or two (SetCGS)
   g.r.alloc(g.ld); g.r.zero();
   g.w.alloc(g.ld); g.w.zero();
   g.hdev.alloc(4 * (size_t)(g.k_dim + 8));
@@ -44,6 +48,9 @@ int gmres_solve(Gmres &g, ParCsr &A, ParVec &bvec, ParVec &xvec) {
   const double *b = bvec.p;
   double *x = xvec.p;
   auto P = [&](int j) { return g.V.p + (i64)j * ld; };
+  const bool flex = g.variant == 1;
+  B200_REQUIRE(!flex || g.Z.n >= (size_t)ld * k_dim, "FlexGMRES: Solve called before Setup");
+  auto Zv = [&](int j) { return g.Z.p + (i64)j * ld; };
   double *r = g.r.p, *w = g.w.p;
   std::vector<double> rs(k_dim + 1), c(k_dim), s(k_dim);
   std::vector<std::vector<double>> hh(k_dim + 1, std::vector<double>(k_dim, 0.0));
@@ -100,8 +107,9 @@ int gmres_solve(Gmres &g, ParCsr &A, ParVec &bvec, ParVec &xvec) {
     while (i < k_dim && iter < max_iter) {
       ++i;
       ++iter;
-      precond(P(i - 1), r);
-      { SpmvArgs a; a.x = r; a.y = P(i); par_spmv(A, SPMV_AX, a); }
+      double *zi = flex ? Zv(i - 1) : r;
+      precond(P(i - 1), zi);
+      { SpmvArgs a; a.x = zi; a.y = P(i); par_spmv(A, SPMV_AX, a); }
       double t;
       if (g.orth == 0) {  // modified Gram-Schmidt
         for (int j = 0; j < i; ++j) {
@@ -109,6 +117,16 @@ int gmres_solve(Gmres &g, ParCsr &A, ParVec &bvec, ParVec &xvec) {
           vec_axpy(-hh[j][i - 1], P(j), P(i), n);
         }
         t = norm(P(i));
+      } else if (g.orth == 2) {  // fused one-pass classical Gram-Schmidt (COGMRES mass inner product + mass axpy)
+        double *h1 = g.hdev.p, *nn = g.hdev.p + 2 * (k_dim + 8);
+        multi_dot(g.dw, P(0), ld, i, P(i), n, h1);
+        allreduce_sum_dev(h1, i);
+        multi_axpy_norm(g.dw, P(0), ld, i, h1, P(i), n, nn);
+        allreduce_sum_dev(nn, 1);
+        B200_CUDA(cudaMemcpyAsync(hpin, g.hdev.p, sizeof(double) * (2 * (k_dim + 8) + 1), cudaMemcpyDeviceToHost, stream()));
+        B200_CUDA(cudaStreamSynchronize(stream()));
+        for (int j = 0; j < i; ++j) hh[j][i - 1] = hpin[j];
+        t = std::sqrt(hpin[2 * (k_dim + 8)]);
       } else {  // fused CGS2
         double *h1 = g.hdev.p, *h2 = g.hdev.p + (k_dim + 8), *nn = g.hdev.p + 2 * (k_dim + 8);
         multi_dot(g.dw, P(0), ld, i, P(i), n, h1);
@@ -153,12 +171,18 @@ int gmres_solve(Gmres &g, ParCsr &A, ParVec &bvec, ParVec &xvec) {
       t += rs[k];
       rs[k] = t / hh[k][k];
     }
-    // w = sum_j rs[j] p[j] ; x += M^{-1} w
-    B200_CUDA(cudaMemcpyAsync(g.hdev.p, rs.data(), sizeof(double) * i, cudaMemcpyHostToDevice, stream()));
-    lin_comb(w, P(0), ld, i, g.hdev.p, n);
-    B200_CUDA(cudaStreamSynchronize(stream()));  // rs (pageable) must stay untouched until the copy is done
-    precond(w, r);
-    vec_axpy(1.0, r, x, n);
+    if (flex) {  // x += sum_j rs[j] z[j] : one pass over the stored preconditioned vectors
+      for (int j = 0; j < i; ++j) hpin[j] = -rs[j];
+      B200_CUDA(cudaMemcpyAsync(g.hdev.p, hpin, sizeof(double) * i, cudaMemcpyHostToDevice, stream()));
+      multi_axpy_norm(g.dw, Zv(0), ld, i, g.hdev.p, x, n, g.hdev.p + 2 * (k_dim + 8));
+      B200_CUDA(cudaStreamSynchronize(stream()));
+    } else {     // w = sum_j rs[j] p[j] ; x += M^{-1} w
+      B200_CUDA(cudaMemcpyAsync(g.hdev.p, rs.data(), sizeof(double) * i, cudaMemcpyHostToDevice, stream()));
+      lin_comb(w, P(0), ld, i, g.hdev.p, n);
+      B200_CUDA(cudaStreamSynchronize(stream()));  // rs (pageable) must stay untouched until the copy is done
+      precond(w, r);
+      vec_axpy(1.0, r, x, n);
+    }
     if (r_norm <= epsilon && iter >= min_iter) {
       residual(r);
       real_r_norm_new = r_norm = norm(r);
@@ -166,8 +190,10 @@ int gmres_solve(Gmres &g, ParCsr &A, ParVec &bvec, ParVec &xvec) {
       if (g.print_level > 0 && ctx().rank == 0) printf("false convergence 2, L2 norm of residual: %e\n", r_norm);
       vec_copy(P(0), r, n);
       i = 0;
-      if (real_r_norm_new >= real_r_norm_old) { break; }
-      real_r_norm_old = real_r_norm_new;
+      if (!flex) {  // FlexGMRES restarts from the true residual without the stagnation test
+        if (real_r_norm_new >= real_r_norm_old) { break; }
+        real_r_norm_old = real_r_norm_new;
+      }
       continue;
     }
     // restart: residual vector from the Arnoldi data

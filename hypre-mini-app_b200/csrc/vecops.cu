@@ -159,6 +159,38 @@ __global__ void __launch_bounds__(VB) k_multi_axpy_norm(const double *__restrict
   block_finish<1>(acc, partial, out, ticket, 1);
 }
 
+// Short-recurrence update of PCG / BiCGSTAB in one pass: x += a p ; r -= a s ; then, with the updated r,
+// out[0] = <r,r> and out[1] = <t,r> (NDOT = 0: no reduction, 1: <r,r>, 2: both).
+template <int NDOT>
+__global__ void __launch_bounds__(VB) k_update2(double a, const double *__restrict__ p, const double *__restrict__ s, double *__restrict__ x,
+                                                double *__restrict__ r, const double *__restrict__ t, i64 n, double *partial, double *out,
+                                                unsigned int *ticket) {
+  double acc[2] = {0.0, 0.0};
+  i64 n2 = n >> 1;
+  i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x, st = (i64)gridDim.x * blockDim.x;
+  for (; i < n2; i += st) {
+    double2 pv = reinterpret_cast<const double2 *>(p)[i], sv = reinterpret_cast<const double2 *>(s)[i];
+    double2 xv = reinterpret_cast<double2 *>(x)[i], rv = reinterpret_cast<double2 *>(r)[i];
+    xv.x += a * pv.x; xv.y += a * pv.y;
+    rv.x -= a * sv.x; rv.y -= a * sv.y;
+    reinterpret_cast<double2 *>(x)[i] = xv;
+    reinterpret_cast<double2 *>(r)[i] = rv;
+    if (NDOT >= 1) acc[0] += rv.x * rv.x + rv.y * rv.y;
+    if (NDOT >= 2) {
+      double2 tv = reinterpret_cast<const double2 *>(t)[i];
+      acc[1] += tv.x * rv.x + tv.y * rv.y;
+    }
+  }
+  if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+    double xv = x[n - 1] + a * p[n - 1], rv = r[n - 1] - a * s[n - 1];
+    x[n - 1] = xv;
+    r[n - 1] = rv;
+    if (NDOT >= 1) acc[0] += rv * rv;
+    if (NDOT >= 2) acc[1] += t[n - 1] * rv;
+  }
+  if (NDOT >= 1) block_finish<2>(acc, partial, out, ticket, NDOT);
+}
+
 // out = sum_j coef_j V_j
 __global__ void __launch_bounds__(VB) k_lin_comb(double *__restrict__ out, const double *__restrict__ V, i64 ld, int k,
                                                  const double *__restrict__ coef, i64 n) {
@@ -252,6 +284,20 @@ void multi_axpy_norm(DotWork &w, const double *V, i64 ld, int k, const double *h
   ensure_work(w, grid, 8);
   ProfScope prof("multi_axpy_norm", 8.0 * (double)n * (k + 2));
   k_multi_axpy_norm<<<grid, VB, 0, stream()>>>(V, ld, k, h, x, n, w.partial.p, norm2_out, ticket_ptr());
+  count_launch();
+  B200_KERNEL_CHECK();
+}
+
+void fused_update2(DotWork &w, double a, const double *p, const double *s, double *x, double *r, const double *t, i64 n, double *out) {
+  auto al = [](const void *q) { return ((uintptr_t)q & 15) == 0; };
+  B200_REQUIRE(al(p) && al(s) && al(x) && al(r) && al(t), "fused_update2: unaligned vectors");
+  int ndot = out ? (t ? 2 : 1) : 0;
+  int grid = stream_grid(n > 0 ? n : 1, 8);
+  ensure_work(w, grid, 8);
+  ProfScope prof("krylov_update2", 8.0 * (double)n * (6 + (ndot == 2)));
+  if (ndot == 0) k_update2<0><<<grid, VB, 0, stream()>>>(a, p, s, x, r, t, n, w.partial.p, out, ticket_ptr());
+  else if (ndot == 1) k_update2<1><<<grid, VB, 0, stream()>>>(a, p, s, x, r, t, n, w.partial.p, out, ticket_ptr());
+  else k_update2<2><<<grid, VB, 0, stream()>>>(a, p, s, x, r, t, n, w.partial.p, out, ticket_ptr());
   count_launch();
   B200_KERNEL_CHECK();
 }

@@ -116,57 +116,69 @@ class BoomerAMG:
             self.h = None
 
 
-class GMRES:
-    def __init__(self, tolerance=1e-5, max_iterations=1000, kspace=10, print_level=0, absolute_tolerance=0.0, orthogonalization=None):
+class ParKrylov:
+    """One of hypre's ParCSR Krylov solvers over the C ABI.  `family` is the hypre name part (GMRES, FlexGMRES, COGMRES,
+    PCG, BiCGSTAB) selected by the YAML `method` (gmres | fgmres | cogmres | cg | bicg, HypreSystem.cpp:69-85)."""
+    FAMILY = {"gmres": "GMRES", "fgmres": "FlexGMRES", "cogmres": "COGMRES", "cg": "PCG", "bicg": "BiCGSTAB"}
+
+    def __init__(self, family="GMRES", tolerance=1e-5, max_iterations=1000, kspace=10, print_level=0, absolute_tolerance=0.0,
+                 orthogonalization=None, cgs=None):
         L = lib()
+        self.family = family
         self.h = VP()
-        check(L.HYPRE_ParCSRGMRESCreate(0, C.byref(self.h)), "GMRESCreate")
-        check(L.HYPRE_ParCSRGMRESSetTol(self.h, float(tolerance)))
-        check(L.HYPRE_ParCSRGMRESSetMaxIter(self.h, int(max_iterations)))
-        check(L.HYPRE_ParCSRGMRESSetKDim(self.h, int(kspace)))
-        check(L.HYPRE_ParCSRGMRESSetPrintLevel(self.h, int(print_level)))
+        for name in ("SetTol", "SetAbsoluteTol"):
+            self._fn(name).argtypes = [VP, F64]
+        check(self._fn("Create")(0, C.byref(self.h)), family + "Create")
+        check(self._fn("SetTol")(self.h, float(tolerance)))
+        check(self._fn("SetMaxIter")(self.h, int(max_iterations)))
+        if family in ("GMRES", "FlexGMRES", "COGMRES"):  # kspace is commented out for cg / bicg (HypreSystem.cpp:431,448)
+            check(self._fn("SetKDim")(self.h, int(kspace)))
+        check(self._fn("SetPrintLevel")(self.h, int(print_level)))
+        if family == "COGMRES" and cgs is not None:      # HypreSystem.cpp:384
+            check(L.HYPRE_ParCSRCOGMRESSetCGS(self.h, int(cgs)))
         if absolute_tolerance:
-            check(L.HYPRE_ParCSRGMRESSetAbsoluteTol(self.h, float(absolute_tolerance)))
-        if orthogonalization is not None:
-            check(L.b200hypre_gmres_set_orthogonalization(self.h, {"mgs": 0, "cgs2": 1}[orthogonalization]))
+            check(self._fn("SetAbsoluteTol")(self.h, float(absolute_tolerance)))
+        if orthogonalization is not None and family in ("GMRES", "FlexGMRES"):
+            check(L.b200hypre_gmres_set_orthogonalization(self.h, {"mgs": 0, "cgs2": 1, "cgs": 2}[orthogonalization]))
+
+    def _fn(self, name):
+        return getattr(lib(), f"HYPRE_ParCSR{self.family}{name}")
 
     def set_precond(self, amg):
         L = lib()
         if amg is None:
-            check(L.HYPRE_ParCSRGMRESSetPrecond(self.h, None, None, None))
+            check(self._fn("SetPrecond")(self.h, None, None, None))
         else:  # HypreSystem.cpp:402 with the pointers stored at :323-324
             solve = C.cast(L.HYPRE_BoomerAMGSolve, VP)
             setup = C.cast(L.HYPRE_BoomerAMGSetup, VP)
-            check(L.HYPRE_ParCSRGMRESSetPrecond(self.h, solve, setup, amg.h))
+            check(self._fn("SetPrecond")(self.h, solve, setup, amg.h))
 
     def setup(self, A, b, x):
-        check(lib().HYPRE_ParCSRGMRESSetup(self.h, A.object(), b.object(), x.object()), "GMRESSetup")
+        check(self._fn("Setup")(self.h, A.object(), b.object(), x.object()), self.family + "Setup")
 
     def solve(self, A, b, x):
-        rc = lib().HYPRE_ParCSRGMRESSolve(self.h, A.object(), b.object(), x.object())
+        rc = self._fn("Solve")(self.h, A.object(), b.object(), x.object())
         if rc == 256:  # HYPRE_ERROR_CONV: reported, not fatal (the mini-app ignores return codes, HypreSystem.cpp:723)
             lib().HYPRE_ClearAllErrors()
             return rc
-        check(rc, "GMRESSolve")
+        check(rc, self.family + "Solve")
         return 0
 
     @property
     def iterations(self):
         v = I32()
-        check(lib().HYPRE_ParCSRGMRESGetNumIterations(self.h, C.byref(v)))
+        check(self._fn("GetNumIterations")(self.h, C.byref(v)))
         return v.value
 
     @property
     def relres(self):
         v = F64()
-        check(lib().HYPRE_ParCSRGMRESGetFinalRelativeResidualNorm(self.h, C.byref(v)))
+        check(self._fn("GetFinalRelativeResidualNorm")(self.h, C.byref(v)))
         return v.value
 
     @property
     def converged(self):
-        v = I32()
-        check(lib().HYPRE_ParCSRGMRESGetConverged(self.h, C.byref(v)))
-        return v.value
+        return lib().b200hypre_solver_converged(self.h)
 
     @property
     def solve_seconds(self):
@@ -175,9 +187,52 @@ class GMRES:
     def history(self):
         out = np.zeros(4096)
         n = lib().b200hypre_gmres_get_history(self.h, _ptr(out), 4096)
-        return out[:n].copy()
+        return out[:min(n, 4096)].copy()
 
     def destroy(self):
         if self.h:
-            lib().HYPRE_ParCSRGMRESDestroy(self.h)
+            self._fn("Destroy")(self.h)
             self.h = None
+
+
+class GMRES(ParKrylov):
+    def __init__(self, **kw):
+        super().__init__("GMRES", **kw)
+
+
+class AMGSolver:
+    """BoomerAMG used as the solver (`method: boomeramg`, HypreSystem.cpp:91-117): same duck type as ParKrylov."""
+
+    def __init__(self, amg, tolerance=1e-5, max_iterations=1000, print_level=0):
+        self.amg = amg
+        self.tol = tolerance
+        amg.set(tolerance=tolerance, max_iterations=max_iterations, print_level=print_level)
+
+    def set_precond(self, amg):
+        pass
+
+    def setup(self, A, b, x):
+        self.amg.setup(A, b, x)
+
+    def solve(self, A, b, x):
+        self.amg.solve(A, b, x)
+        return 0
+
+    @property
+    def iterations(self):
+        v = I32()
+        check(lib().HYPRE_BoomerAMGGetNumIterations(self.amg.h, C.byref(v)))
+        return v.value
+
+    @property
+    def relres(self):
+        v = F64()
+        check(lib().HYPRE_BoomerAMGGetFinalRelativeResidualNorm(self.amg.h, C.byref(v)))
+        return v.value
+
+    @property
+    def converged(self):
+        return int(self.relres < self.tol)
+
+    def destroy(self):
+        pass

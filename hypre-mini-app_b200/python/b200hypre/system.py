@@ -12,7 +12,7 @@ import time
 import numpy as np
 
 from . import (HYPRE_MEMORY_DEVICE, I32, I64, VP, IJMatrix, IJVector, check, lib, process_grid, synchronize)
-from .solvers import GMRES, BoomerAMG
+from .solvers import AMGSolver, BoomerAMG, ParKrylov
 
 
 class DeviceCOO:
@@ -51,7 +51,7 @@ class HypreSystem:
         self.rank, self.nranks = rank, nranks
         self.timers = []
         self.A = self.b = self.x = None
-        self.solver = self.precond = None
+        self.solver = self.precond = self.amg_solver = None
         self.n_local = self.i_lower = self.i_upper = self.global_rows = 0
 
     def _timer(self, name, t0):
@@ -61,8 +61,8 @@ class HypreSystem:
     def setup_precon_and_solver(self):
         ss = self.cfg.get("solver_settings", {})
         method = ss.get("method", "gmres")
-        if method != "gmres":
-            raise ValueError(f"solver method '{method}' is outside the built path (gmres only; SURVEY.md §8f.2)")
+        if method not in ParKrylov.FAMILY and method != "boomeramg":
+            raise ValueError(f"solver method '{method}' is outside the built path (gmres | fgmres | cogmres | cg | bicg | boomeramg)")
         precond = ss.get("preconditioner", "boomeramg")
         if precond == "boomeramg":
             amg = dict(DEFAULT_AMG)
@@ -72,9 +72,28 @@ class HypreSystem:
             self.precond = None
         else:
             raise ValueError(f"preconditioner '{precond}' is outside the built path (boomeramg | none)")
-        self.solver = GMRES(tolerance=ss.get("tolerance", 1e-5), max_iterations=ss.get("max_iterations", 1000),
-                            kspace=ss.get("kspace", 10), print_level=ss.get("print_level", 0),
-                            orthogonalization=ss.get("orthogonalization"))
+        if method == "boomeramg":
+            # setup_boomeramg_solver (HypreSystem.cpp:91-117): BoomerAMG is the solver, no preconditioner.  The reference
+            # applies the coarsening / relaxation keys of solver_settings to precond_ (:100-110), leaving solver_ on hypre's
+            # defaults; here they configure the solver itself, which is what those lines evidently intend.
+            amg = dict(DEFAULT_AMG)
+            amg.update(coarsen_type=ss.get("coarsen_type", 8), cycle_type=ss.get("cycle_type", 1), relax_type=ss.get("relax_type", 6),
+                       num_sweeps=ss.get("num_sweeps", 1), smooth_num_sweeps=ss.get("smooth_num_sweeps", 1),
+                       relax_order=ss.get("relax_order", 1), max_levels=ss.get("max_levels", 20),
+                       strong_threshold=ss.get("strong_threshold", 0.57))
+            for k in ("interp_type", "p_max_elmts", "trunc_factor"):
+                if k in ss:
+                    amg[k] = ss[k]
+            if self.precond is not None:
+                self.precond.destroy()
+            self.precond = None
+            self.amg_solver = BoomerAMG(**amg)
+            self.solver = AMGSolver(self.amg_solver, tolerance=ss.get("tolerance", 1e-5), max_iterations=ss.get("max_iterations", 1000),
+                                    print_level=ss.get("print_level", 0))
+            return
+        self.solver = ParKrylov(ParKrylov.FAMILY[method], tolerance=ss.get("tolerance", 1e-5), max_iterations=ss.get("max_iterations", 1000),
+                                kspace=ss.get("kspace", 10), print_level=ss.get("print_level", 0),
+                                orthogonalization=ss.get("orthogonalization"), cgs=ss.get("cgs", 0))
 
     # -- HypreSystem.cpp:16-47 --------------------------------------------------------------------------------------------
     def load(self):
@@ -180,7 +199,7 @@ class HypreSystem:
         return self.x.get_values()
 
     def destroy_system(self):
-        for o in (self.solver, self.precond, self.A, self.b, self.x):
+        for o in (self.solver, self.precond, getattr(self, "amg_solver", None), self.A, self.b, self.x):
             if o is not None:
                 o.destroy()
-        self.solver = self.precond = self.A = self.b = self.x = None
+        self.solver = self.precond = self.amg_solver = self.A = self.b = self.x = None

@@ -59,7 +59,8 @@ HYPRE_Int b200hypre_amg_vcycle(HYPRE_Solver amg, const HYPRE_Complex *r, HYPRE_C
 /* ---- GMRES extras ---------------------------------------------------------------------------------------------------------- */
 HYPRE_Int b200hypre_gmres_set_orthogonalization(HYPRE_Solver gmres, HYPRE_Int kind);   /* 0 = MGS (hypre), 1 = fused CGS2 (default) */
 HYPRE_Int b200hypre_gmres_get_history(HYPRE_Solver gmres, HYPRE_Real *out, HYPRE_Int cap);   /* returns the history length */
-HYPRE_Real b200hypre_gmres_solve_seconds(HYPRE_Solver gmres);
+HYPRE_Real b200hypre_gmres_solve_seconds(HYPRE_Solver gmres);                                 /* history / seconds accept any Krylov handle */
+HYPRE_Int b200hypre_solver_converged(HYPRE_Solver krylov);
 
 /* device name / compute capability / memory of the device this rank runs on (the checkMemory() print, HypreSystem.cpp:638-671) */
 HYPRE_Int b200hypre_device_info(char *name, HYPRE_Int name_cap, int *device, int *count, int *cc_major, int *cc_minor, double *free_gb,

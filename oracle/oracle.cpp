@@ -231,6 +231,7 @@ struct Options {
   // gmres
   double tol = 1e-8, atol = 0.0;
   int max_iter = 1000, kdim = 50, precond = 1;  // precond: 1 = boomeramg, 0 = none
+  int cgs = 0;                                  // COGMRES: 0/1 = one classical Gram-Schmidt pass, 2 = two passes
   // amg
   int coarsen_type = 8, interp_type = 6, relax_type = 18, relax_order = 0, max_levels = 20;
   int num_sweeps = 1, p_max_elmts = 4, max_coarse_size = 9, min_coarse_size = 0, cheby_order = 2, cheby_eig_est = 10;
@@ -1099,6 +1100,7 @@ static void gmres(Sys &s, double *x) {
   s.solve_s = now_s() - t0;
 }
 
+#include "krylov.inc"
 }  // namespace
 
 // =========================================================================================================
@@ -1125,7 +1127,7 @@ int ora_set_opt(void *h, const char *name, double v) {
 #define OPT_I(key, field) if (k == key) { o.field = (int)v; return 0; }
 #define OPT_D(key, field) if (k == key) { o.field = v; return 0; }
   OPT_D("tolerance", tol) OPT_D("absolute_tolerance", atol) OPT_I("max_iterations", max_iter) OPT_I("kspace", kdim)
-  OPT_I("preconditioner", precond) OPT_I("coarsen_type", coarsen_type) OPT_I("interp_type", interp_type)
+  OPT_I("preconditioner", precond) OPT_I("cgs", cgs) OPT_I("coarsen_type", coarsen_type) OPT_I("interp_type", interp_type)
   OPT_I("relax_type", relax_type) OPT_I("relax_order", relax_order) OPT_I("max_levels", max_levels)
   OPT_I("num_sweeps", num_sweeps) OPT_I("p_max_elmts", p_max_elmts) OPT_I("max_coarse_size", max_coarse_size)
   OPT_I("min_coarse_size", min_coarse_size) OPT_I("cheby_order", cheby_order) OPT_I("cheby_eig_est", cheby_eig_est)
@@ -1169,6 +1171,24 @@ int ora_gmres_solve(void *h, double *x) {
     s.opt.precond = 0;
   }
   gmres(s, x);
+  return 0;
+}
+// method: 0 gmres, 1 fgmres, 2 cogmres, 3 cg, 4 bicg, 5 boomeramg (the YAML `method` names of HypreSystem.cpp:69-85)
+int ora_krylov_solve(void *h, int method, double *x) {
+  Sys &s = *(Sys *)h;
+  if (s.lev.empty()) return 1;
+  if (s.lev[0].vtemp.empty()) {
+    if (method == 5) return 2;  // BoomerAMG as solver needs the hierarchy
+    s.opt.precond = 0;
+  }
+  switch (method) {
+    case 0: gmres(s, x); break;
+    case 1: case 2: gmres_family(s, x, method); break;
+    case 3: pcg(s, x); break;
+    case 4: bicgstab(s, x); break;
+    case 5: amg_solver(s, x); break;
+    default: return 3;
+  }
   return 0;
 }
 int ora_vcycle(void *h, const double *r, double *z) {

@@ -16,7 +16,8 @@ def lib():
     global _LIB
     if _LIB is None:
         path = os.path.join(ROOT, "oracle", "_build", "liboracle.so")
-        if not os.path.exists(path) or os.path.getmtime(path) < os.path.getmtime(os.path.join(ROOT, "oracle", "oracle.cpp")):
+        if not os.path.exists(path) or os.path.getmtime(path) < max(
+                os.path.getmtime(os.path.join(ROOT, "oracle", f)) for f in ("oracle.cpp", "krylov.inc")):
             build()
         L = C.CDLL(path)
         L.ora_create.restype = C.c_void_p
@@ -28,6 +29,7 @@ def lib():
             getattr(L, f).argtypes = [C.c_void_p]
         L.ora_set_opt.argtypes = [C.c_void_p, C.c_char_p, C.c_double]
         L.ora_gen_laplace.argtypes = [C.c_void_p] + [C.c_int] * 7
+        L.ora_krylov_solve.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double)]
         _LIB = L
     return _LIB
 
@@ -80,9 +82,15 @@ class Oracle:
     def setup(self):
         self.L.ora_amg_setup(self.h)
 
-    def solve(self, x0=None):
+    METHODS = {"gmres": 0, "fgmres": 1, "cogmres": 2, "cg": 3, "bicg": 4, "boomeramg": 5}
+
+    def solve(self, x0=None, method="gmres"):
         x = np.zeros(self.n) if x0 is None else np.array(x0, dtype=np.float64)
-        self.L.ora_gmres_solve(self.h, _p(x, C.c_double))
+        if method == "gmres":
+            self.L.ora_gmres_solve(self.h, _p(x, C.c_double))
+        else:
+            rc = self.L.ora_krylov_solve(self.h, C.c_int(self.METHODS[method]), _p(x, C.c_double))
+            assert rc == 0, f"oracle krylov solve failed ({rc})"
         return x
 
     def vcycle(self, r):

@@ -56,7 +56,7 @@ def write_mm_vector(path, v, complex_vals=False):
 YAML_TMPL = """linear_system:
 {linsys}
 solver_settings:
-  method: gmres
+  method: {method}
   preconditioner: {precond}
   tolerance: 1.0e-10
   max_iterations: 200
@@ -73,10 +73,10 @@ boomeramg_settings:
 """
 
 
-def run_app(app, workdir, linsys, precond="boomeramg", solver_extra="", nranks=1):
+def run_app(app, workdir, linsys, precond="boomeramg", solver_extra="", nranks=1, method="gmres"):
     y = os.path.join(workdir, "in.yaml")
     with open(y, "w") as f:
-        f.write(YAML_TMPL.format(linsys="\n".join("  " + l for l in linsys), precond=precond, solver_extra=solver_extra))
+        f.write(YAML_TMPL.format(linsys="\n".join("  " + l for l in linsys), precond=precond, solver_extra=solver_extra, method=method))
     if nranks == 1:
         r = subprocess.run([app, y], cwd=workdir, capture_output=True, text=True, timeout=600)
         return r.returncode, r.stdout + r.stderr
@@ -218,3 +218,22 @@ def test_two_ranks_matrix_market(app, tmp_path):
     s1 = np.loadtxt(tmp_path / "IJV0.sln.00001", skiprows=1)
     sol = np.concatenate([s0[:, 1], s1[:, 1]])
     assert np.abs(sol - x).max() < 1e-6
+
+
+@pytest.mark.parametrize("method,nranks", [("cg", 1), ("bicg", 1), ("fgmres", 1), ("cogmres", 1), ("boomeramg", 1), ("cg", 2), ("bicg", 2),
+                                           ("fgmres", 2)])
+def test_sibling_methods_through_the_app(app, tmp_path, method, nranks):
+    """solver_settings.method selects the sibling Krylov methods (HypreSystem.cpp:69-85); generator input => x == 1"""
+    extra = "  cgs: 2" if method == "cogmres" else ""
+    if method == "boomeramg":
+        extra = "  relax_type: 18\n  relax_order: 0\n  strong_threshold: 0.25"
+    rc, out = run_app(app, str(tmp_path), ["type: build_7pt_stencil", "nx: 16", "ny: 16", "nz: 16", "write_solution: true"],
+                      solver_extra=extra, nranks=nranks, method=method)
+    assert rc == 0, out
+    assert f"Using {method} solver" in out
+    assert 0 < iterations(out) < (80 if method == "boomeramg" else 30), out
+    m = re.search(r"final relative residual norm = ([0-9.eE+-]+)", out)
+    assert float(m.group(1)) < 1e-10
+    for k in range(nranks):
+        sol = np.loadtxt(tmp_path / f"IJV0.sln.{k:05d}", skiprows=1)
+        assert np.abs(sol[:, 1] - 1.0).max() < 1e-7
