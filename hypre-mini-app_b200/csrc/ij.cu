@@ -37,6 +37,32 @@ __global__ void k_check_sorted(i64 n, const i64 *rows, const i64 *cols, int *bad
   i64 r0 = rows[k - 1], r1 = rows[k];
   if (r1 < r0 || (r1 == r0 && cols[k] <= cols[k - 1])) *bad = 1;
 }
+// Row-sorted input whose columns are in arbitrary order inside a row (the generator's stencil order on a multi-rank
+// grid, many MatrixMarket files): bad[0] = 1 if the rows are not nondecreasing.
+__global__ void k_check_rows_sorted(i64 n, const i64 *rows, int *bad) {
+  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k == 0 || k >= n) return;
+  if (rows[k] < rows[k - 1]) *bad = 1;
+}
+// The thread that sees the head of a row run sorts that run by column, in place (stable insertion sort; runs are a few
+// dozen entries at most).  Runs longer than `maxlen` are left alone and reported through toolong.
+__global__ void k_sort_short_rows(i64 n, const i64 *__restrict__ rows, i64 *cols, double *vals, int maxlen, int *toolong) {
+  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const i64 r = rows[k];
+  if (k > 0 && rows[k - 1] == r) return;
+  i64 e = k + 1;
+  while (e < n && e - k <= maxlen && rows[e] == r) ++e;
+  if (e - k > maxlen) { *toolong = 1; return; }
+  for (i64 a = k + 1; a < e; ++a) {
+    i64 c = cols[a];
+    double v = vals[a];
+    i64 b = a - 1;
+    while (b >= k && cols[b] > c) { cols[b + 1] = cols[b]; vals[b + 1] = vals[b]; --b; }
+    cols[b + 1] = c;
+    vals[b + 1] = v;
+  }
+}
 __global__ void k_check_range(i64 n, const i64 *rows, i64 lo, i64 hi, int *bad) {
   i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
   if (k < n && (rows[k] < lo || rows[k] > hi)) *bad = 1;
@@ -232,6 +258,20 @@ void ij_matrix_assemble(IJMatrix &M) {
     if (c.n) k_check_sorted<<<div_up(c.n, 256), 256, 0, stream()>>>(c.n, c.rows.p, c.cols.p, bad.p);
     count_launch();
     fast = (fetch1(bad.p) == 0);
+    if (!fast && c.n) {  // rows in order, columns not: sort every (short) row in place instead of radix-sorting all keys
+      DVec<int> flags(2);
+      flags.zero();
+      k_check_rows_sorted<<<div_up(c.n, 256), 256, 0, stream()>>>(c.n, c.rows.p, flags.p);
+      count_launch();
+      if (fetch1(flags.p) == 0) {
+        k_sort_short_rows<<<div_up(c.n, 256), 256, 0, stream()>>>(c.n, c.rows.p, c.cols.p, c.vals.p, 64, flags.p + 1);
+        bad.zero();
+        k_check_sorted<<<div_up(c.n, 256), 256, 0, stream()>>>(c.n, c.rows.p, c.cols.p, bad.p);
+        count_launch(2);
+        // duplicates or a long row fall through to the general path (the in-place sort was stable, so Set/Add order holds)
+        fast = (fetch1(flags.p + 1) == 0) && (fetch1(bad.p) == 0);
+      }
+    }
   }
   if (fast) {
     rows = std::move(M.staged[0].rows);

@@ -138,6 +138,43 @@ def test_spmv_matches_oracle_and_scipy(b200):
         s.destroy_system()
 
 
+@pytest.mark.parametrize("duplicates", [False, True])
+def test_ij_assembly_row_sorted_columns_shuffled(b200, duplicates):
+    """rows in order, columns in arbitrary order inside each row (multi-rank generator output, typical MatrixMarket files):
+    the per-row sort path; with duplicates it must fall through to the general path and keep Set semantics (last wins)"""
+    import scipy.sparse as sp
+    rng = np.random.default_rng(23)
+    n = 3000
+    M = (sp.random(n, n, density=0.004, random_state=9, format="csr") + sp.eye(n) * 3).tocsr()
+    M.sort_indices()
+    rows = np.repeat(np.arange(n), np.diff(M.indptr))
+    cols, vals = M.indices.copy(), M.data.copy()
+    for i in range(n):
+        a, b = M.indptr[i], M.indptr[i + 1]
+        p = rng.permutation(b - a)
+        cols[a:b], vals[a:b] = cols[a:b][p], vals[a:b][p]
+    ref = M.copy()
+    if duplicates:   # repeat the first entry of every 7th row with another value right after it: Set => the later value wins
+        ins = M.indptr[:-1][::7]
+        rows = np.insert(rows, ins + 1, rows[ins])
+        cols = np.insert(cols, ins + 1, cols[ins])
+        vals = np.insert(vals, ins + 1, 99.0)
+        ref = ref.tolil()
+        for r, c in zip(rows[ins + np.arange(len(ins)) + 1], cols[ins + np.arange(len(ins)) + 1]):
+            ref[r, c] = 99.0
+        ref = ref.tocsr()
+    A = b200.IJMatrix(0, n - 1)
+    A.set_values(rows, cols, vals)
+    A.assemble()
+    ptr, col, val, _ = A.to_csr()
+    got = sp.csr_matrix((val, col, ptr), shape=(n, n))
+    assert abs(got - ref).max() == 0.0
+    for i in range(0, n, 17):   # diagonal first, remaining columns ascending
+        c = col[ptr[i]:ptr[i + 1]]
+        assert c[0] == i and np.all(np.diff(c[1:]) > 0)
+    A.destroy()
+
+
 def test_ij_assembly_unsorted_duplicates(b200):
     """Set overwrites, AddTo accumulates, any entry order; result is ParCSR order (diagonal first, then ascending)"""
     import scipy.sparse as sp
