@@ -19,6 +19,23 @@ struct HaloPlan {                 // receive lists grouped by owner (contiguous)
   DVec<int> send_idx;                     // local indices to pack, concatenated per destination
   DVec<double> send_buf;
   int n_send = 0;
+  // peer-memory exchange (comm_peer.cu): region of this rank's arena = [flags | halo buffer 0 | halo buffer 1]
+  bool p2p = false;
+  i64 region = -1;                        // arena offset, -1: none
+  DVec<unsigned long long> state;         // device: [0] exchanges completed on this plan (exchange s uses buffer s & 1),
+                                          //         [1] address of the halo buffer of the exchange in flight (read by consumers)
+  unsigned long long *flags = nullptr;    // one per sending neighbour (recv_rank order), written by the peers
+  double *buf[2] = {nullptr, nullptr};
+  DVec<int> send_off_dev;                 // send_off on the device
+  DVec<unsigned long long> push_dst;      // per destination: address of my segment in its buffer 0, buffer 1, and of my flag
+  DVec<unsigned int> ticket;
+  HaloPlan() {}
+  HaloPlan(const HaloPlan &) = delete;
+  HaloPlan &operator=(const HaloPlan &) = delete;
+  HaloPlan(HaloPlan &&o) noexcept { *this = std::move(o); }
+  HaloPlan &operator=(HaloPlan &&o) noexcept;
+  ~HaloPlan() { release(); }
+  void release();
 };
 
 struct ParCsr {
@@ -29,7 +46,10 @@ struct ParCsr {
   std::vector<i64> col_map_offd;  // sorted global ids of the halo columns
   std::vector<i64> row_starts, col_starts;  // partition over ranks (nranks + 1)
   HaloPlan halo;
-  DVec<double> x_halo;
+  DVec<double> x_halo;            // NCCL / shm transport: receive buffer
+  // device location holding the address of the halo values of the exchange in flight: x_halo.p, or the peer-memory buffer
+  // the last wait selected.  Kept on the device so that exchanges can be replayed inside a CUDA graph.
+  const double *const *xhp() const { return reinterpret_cast<const double *const *>(halo.state.p + 1); }
   DSell sell;
   SpmvPlan plan;
   void finalize_spmv();           // pick kernels / build SELL after diag is final
@@ -97,6 +117,7 @@ struct Amg {
   // levels >= 1 of the V-cycle captured as a CUDA graph (all their buffers are internal, hence pointer-stable)
   cudaGraphExec_t graph_exec = nullptr;
   int graph_launches = 0;
+  bool graph_failed = false;
   ~Amg();
 };
 

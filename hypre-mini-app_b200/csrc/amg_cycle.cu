@@ -233,35 +233,58 @@ void amg_vcycle(Amg &amg, const double *rhs, double *z) {
   init_bufs(amg, rhs, z, bufs);
   level_down(amg, 0, bufs);
   if (nl > 2) {
-    if (!use_graph || ctx().nranks > 1) {
+    // multi-rank: replayable only when every halo exchange of levels >= 1 runs over peer memory (device-side sequence
+    // numbers, parcsr.cu); the coarsest-level all-reduce is an NCCL call, which is capturable
+    bool graph_ok = use_graph && !amg.graph_failed;
+    if (graph_ok && ctx().nranks > 1) {
+      const char *e = getenv("B200_CUDA_GRAPH_DIST");
+      if (e && atoi(e) == 0) graph_ok = false;
+      for (int l = 1; l < nl && graph_ok; ++l) {
+        AmgLevel &L = *amg.lev[l];
+        graph_ok = L.A->halo.p2p && (l == nl - 1 || (L.P.halo.p2p && L.R.halo.p2p));
+      }
+    }
+    if (!graph_ok) {
       coarse_part(amg, bufs);
     } else {
+      bool replayed = true;
       if (!amg.graph_exec) {
         cudaGraph_t graph = nullptr;
         unsigned long long before = ctx().launches;
+        const std::vector<LevelBufs> saved = bufs;
         B200_CUDA(cudaStreamBeginCapture(stream(), cudaStreamCaptureModeThreadLocal));
+        bool captured = true;
         try {
           coarse_part(amg, bufs);
         } catch (...) {
-          cudaStreamEndCapture(stream(), &graph);
-          if (graph) cudaGraphDestroy(graph);
-          throw;
+          captured = false;
         }
-        B200_CUDA(cudaStreamEndCapture(stream(), &graph));
-        amg.graph_launches = (int)(ctx().launches - before);
-        ctx().launches = before;
-        B200_CUDA(cudaGraphInstantiate(&amg.graph_exec, graph, 0));
-        cudaGraphDestroy(graph);
-        B200_CUDA(cudaGraphLaunch(amg.graph_exec, stream()));
-        count_launch(amg.graph_launches);
+        cudaError_t ce = cudaStreamEndCapture(stream(), &graph);
+        if (captured && ce == cudaSuccess && graph) ce = cudaGraphInstantiate(&amg.graph_exec, graph, 0);
+        if (graph) cudaGraphDestroy(graph);
+        if (!captured || ce != cudaSuccess || !amg.graph_exec) {  // not capturable here: run the levels directly from now on
+          cudaGetLastError();
+          amg.graph_exec = nullptr;
+          amg.graph_failed = true;
+          ctx().launches = before;
+          bufs = saved;
+          coarse_part(amg, bufs);
+          replayed = false;
+        } else {
+          amg.graph_launches = (int)(ctx().launches - before);
+          ctx().launches = before;
+          B200_CUDA(cudaGraphLaunch(amg.graph_exec, stream()));
+          count_launch(amg.graph_launches);
+        }
       }
       else {
         B200_CUDA(cudaGraphLaunch(amg.graph_exec, stream()));
         count_launch(amg.graph_launches);
       }
       // the replayed levels leave their result in u (init_bufs parity); mirror the flips the host did not execute
-      for (int l = 1; l < nl; ++l)
-        if (bufs[l].cur != amg.lev[l]->u.p) std::swap(bufs[l].cur, bufs[l].other);
+      if (replayed)
+        for (int l = 1; l < nl; ++l)
+          if (bufs[l].cur != amg.lev[l]->u.p) std::swap(bufs[l].cur, bufs[l].other);
     }
   } else if (nl == 2) {
     level_down(amg, 1, bufs);

@@ -115,7 +115,8 @@ __global__ void __launch_bounds__(GS_THREADS) k_gs_sweep(int n, CsrView D, CsrVi
                                                          const int *__restrict__ lvl_off, int depth,
                                                          const signed char *__restrict__ mask, int dir, const double *__restrict__ dsm,
                                                          const double *__restrict__ f, const double *__restrict__ uin, double *uout,
-                                                         const double *__restrict__ halo, unsigned long long *bar, unsigned nblocks) {
+                                                         const double *const *halo_p, unsigned long long *bar, unsigned nblocks) {
+  const double *halo = (O.ptr != nullptr) ? *halo_p : nullptr;   // halo values of the exchange that preceded the sweep
   const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gthreads = gridDim.x * blockDim.x;
   for (int i = gtid; i < n; i += gthreads)
     if (!mask[i]) uout[i] = uin[i];          // rows outside the set keep their value (never read from uout)
@@ -136,7 +137,7 @@ __global__ void __launch_bounds__(GS_THREADS) k_gs_sweep(int n, CsrView D, CsrVi
         sum += D.val[q] * v;
       }
       if (O.ptr != nullptr)
-        for (int q = O.ptr[i] + lane; q < O.ptr[i + 1]; q += G) sum += O.val[q] * halo[O.col[q]];
+        for (int q = O.ptr[i] + lane; q < O.ptr[i + 1]; q += G) sum += O.val[q] * __ldcg(halo + O.col[q]);
 #pragma unroll
       for (int o = G >> 1; o > 0; o >>= 1) sum += __shfl_xor_sync(gm, sum, o, G);
       if (lane == 0) {
@@ -244,10 +245,10 @@ static void launch_sweep(ParCsr &A, GsPlan &plan, bool l1, const double *dsm, co
   B200_CUDA(cudaMemsetAsync(plan.bar.p, 0, sizeof(unsigned long long), stream()));
   if (l1)
     k_gs_sweep<G, true><<<nblocks, GS_THREADS, 0, stream()>>>(n, A.diag.view(), O, plan.order.p, plan.lvl_off.p, plan.depth, plan.mask.p,
-                                                              plan.dir, dsm, f, uin, uout, A.x_halo.p, plan.bar.p, (unsigned)nblocks);
+                                                              plan.dir, dsm, f, uin, uout, A.xhp(), plan.bar.p, (unsigned)nblocks);
   else
     k_gs_sweep<G, false><<<nblocks, GS_THREADS, 0, stream()>>>(n, A.diag.view(), O, plan.order.p, plan.lvl_off.p, plan.depth, plan.mask.p,
-                                                               plan.dir, dsm, f, uin, uout, A.x_halo.p, plan.bar.p, (unsigned)nblocks);
+                                                               plan.dir, dsm, f, uin, uout, A.xhp(), plan.bar.p, (unsigned)nblocks);
   count_launch();
 }
 

@@ -184,6 +184,9 @@ void shm_allgather_dev(const void *in, void *out, size_t bytes, cudaStream_t s);
 void shm_exchange_dev(int nsend, const int *send_rank, const void *const *send_ptr, const size_t *send_bytes, int nrecv,
                       const int *recv_rank, void *const *recv_ptr, const size_t *recv_bytes, cudaStream_t s);
 
+void peer_init();       // comm_peer.cu
+void peer_finalize();
+
 void comm_init_shm(int rank, int nranks, const char *name, size_t slot_bytes) {
   ensure_init();
   Context &c = ctx();
@@ -214,10 +217,12 @@ void comm_init(int rank, int nranks, const void *id128) {
   void *comm = nullptr;
   B200_NCCL(g_nccl.CommInitRank(&comm, nranks, id, rank));
   c.nccl = comm;
+  peer_init();  // NVLink peer-memory arena for the halo exchange (falls back to NCCL send/recv when unavailable)
 }
 
 void comm_finalize() {
   Context &c = ctx();
+  peer_finalize();
   if (c.nccl) { g_nccl.CommDestroy(c.nccl); c.nccl = nullptr; }
   shm_finalize();
   c.rank = 0;

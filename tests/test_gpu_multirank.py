@@ -110,7 +110,8 @@ def test_multirank_hierarchy_and_solve(b200, n, grid, stencil, theta):
     compare_with_oracle(res, n, grid, stencil, theta)
 
 
-@pytest.mark.parametrize("n,grid,stencil,theta", [((16, 16, 16), (2, 1, 1), 7, 0.25), ((10, 10, 10), (2, 2, 2), 27, 0.25)])
+@pytest.mark.parametrize("n,grid,stencil,theta", [((16, 16, 16), (2, 1, 1), 7, 0.25), ((32, 32, 32), (2, 1, 1), 7, 0.25),
+                                                 ((16, 16, 16), (2, 1, 1), 27, 0.57), ((10, 10, 10), (2, 2, 2), 27, 0.25)])
 def test_multigpu_nccl_hierarchy_and_solve(b200, n, grid, stencil, theta):
     """the same comparison with one rank per GPU over NCCL; skipped on boxes with fewer GPUs than ranks"""
     nranks = grid[0] * grid[1] * grid[2]
@@ -118,6 +119,33 @@ def test_multigpu_nccl_hierarchy_and_solve(b200, n, grid, stencil, theta):
         pytest.skip(f"needs {nranks} GPUs")
     res = run_ranks_nccl(nranks, settings(n, grid, stencil, strong_threshold=theta))
     compare_with_oracle(res, n, grid, stencil, theta)
+
+
+@pytest.mark.parametrize("method", ["cg", "bicg", "fgmres", "cogmres"])
+@pytest.mark.parametrize("transport", ["shm", "nccl"])
+def test_multirank_sibling_krylov_methods(b200, method, transport):
+    """PCG / BiCGSTAB / FlexGMRES / COGMRES on 2 ranks (all-reduced inner products, distributed preconditioner) against the
+    oracle with 2 virtual ranks; the NCCL variant (one GPU per rank, peer-memory halo exchange, graph-replayed coarse
+    levels) needs 2 GPUs"""
+    n, grid = ((20, 20, 20) if transport == "nccl" else (10, 10, 10)), (2, 1, 1)
+    if transport == "nccl" and n_gpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    cfg = settings(n, grid, 7)
+    cfg["solver_settings"].update(method=method, kspace=20)
+    res = (run_ranks_nccl if transport == "nccl" else run_ranks)(2, cfg)
+    o = Oracle(tolerance=1e-8, kspace=20, max_iterations=200)
+    o.threads(8)
+    o.gen_laplace(n, p=grid, stencil=7)
+    o.setup()
+    xo = o.solve(method=method)
+    x = np.concatenate([d["x"] for d in res])
+    its = int(res[0]["iterations"])
+    assert all(int(d["iterations"]) == its for d in res)
+    assert abs(its - o.iterations) <= 1, (its, o.iterations)
+    assert float(res[0]["relres"]) <= max(o.relres * (1 + 1e-6), 1e-8)
+    assert np.abs(x - 1.0).max() < 1e-5
+    if its == o.iterations:
+        assert np.abs(x - xo).max() / np.abs(xo).max() <= 1e-8
 
 
 def compare_with_oracle(res, n, grid, stencil, theta):
