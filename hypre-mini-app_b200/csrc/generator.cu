@@ -7,7 +7,7 @@
 // or 6 (7-point, BASELINE.json configs), off-diagonals -1, rhs = diag - (nnz_row - 1) so that x == 1.
 // Off-rank neighbours carry the TRUE neighbour's global row id (the reference glue's surrogate
 // numbering at HypreSystem.cpp:1555 is not reproduced).
-// Output: COO triplets in row order, stencil order (z, y, x offsets ascending) inside a row, plus the rhs.
+// Output: COO triplets in row order, ascending global column inside a row (= stencil order z, y, x on one rank), plus the rhs.
 #include "amg.h"
 #include <cub/cub.cuh>
 
@@ -77,6 +77,7 @@ __global__ void k_gen_fill(Box b, const int *ptr, i64 *rows, i64 *cols, double *
   const double dval = (b.stencil == 27) ? 26.0 : 6.0;
   i64 grow = b.row_start + l;
   int p = ptr[l], c = 0;
+  i64 gc[27];
   for (int dz = -1; dz <= 1; ++dz)
     for (int dy = -1; dy <= 1; ++dy)
       for (int dx = -1; dx <= 1; ++dx) {
@@ -86,12 +87,17 @@ __global__ void k_gen_fill(Box b, const int *ptr, i64 *rows, i64 *cols, double *
         int rx = x / b.nx, ry = y / b.ny, rz = z / b.nz;
         i64 r = rx + (i64)b.px * (ry + (i64)b.py * rz);
         i64 gcol = r * b.nloc + (x - rx * b.nx) + (i64)b.nx * ((y - ry * b.ny) + (i64)b.ny * (z - rz * b.nz));
-        rows[p] = grow;
-        cols[p] = gcol;
-        vals[p] = (gcol == grow) ? dval : -1.0;
-        ++p;
-        ++c;
+        // ascending global column inside the row (stencil order already is, except across rank boundaries), so that the
+        // IJ assembly takes its pre-sorted path on every rank
+        int q = c++;
+        for (; q > 0 && gc[q - 1] > gcol; --q) gc[q] = gc[q - 1];
+        gc[q] = gcol;
       }
+  for (int q = 0; q < c; ++q) {
+    rows[p + q] = grow;
+    cols[p + q] = gc[q];
+    vals[p + q] = (gc[q] == grow) ? dval : -1.0;
+  }
   rhs[l] = dval - (double)(c - 1);
 }
 

@@ -81,10 +81,22 @@ __device__ __forceinline__ void block_finish(double (&acc)[K], double *partial, 
   }
   __syncthreads();
   if (is_last) {
+    // all threads of the last block add the per-block partials (thread t takes blocks t, t + VB, ... in that order), then
+    // the same fixed-order block reduction as above: deterministic for a given grid, and no serial chain of L2 loads
     __threadfence();
+#pragma unroll
+    for (int j = 0; j < K; ++j) {
+      double s = 0.0;
+      if (j < kvalid)
+        for (unsigned int b = threadIdx.x; b < gridDim.x; b += VB) s += __ldcg(partial + (size_t)b * K + j);
+      s = warp_sum(s);
+      if (lane == 0) sm[j][wid] = s;
+    }
+    __syncthreads();
     if (threadIdx.x < kvalid) {
       double s = 0.0;
-      for (unsigned int b = 0; b < gridDim.x; ++b) s += ((volatile double *)partial)[(size_t)b * K + threadIdx.x];
+#pragma unroll
+      for (int w = 0; w < VB / 32; ++w) s += sm[threadIdx.x][w];
       out[threadIdx.x] = s;
     }
     if (threadIdx.x == 0) *ticket = 0;

@@ -1,0 +1,93 @@
+"""Timings of the other BASELINE.json configurations and of the sibling Krylov methods on one B200 (run under gpurun):
+    python profiles/run_workloads.py [--quick] > gpurun_out/workloads_<tag>.jsonl
+One JSON line per case: setup / solve seconds (the reference's "Preconditioner setup" and "Solve" timers,
+HypreSystem.cpp:685-696,723-734, measured with CUDA events on the library stream), iterations, final relative residual,
+max |x - 1| (every system has rhs = A 1) and the SpMV-class kernel bandwidths of the kernel-class profiler.
+  lap27_256      : configs[1] with the reference generator's 27-point stencil (theta 0.57), device generator, full size
+  poisson27_<n>  : configs[3] perturbed-hex 27-point Poisson + Chebyshev, built on the host (tests/workloads.py) -- reduced
+                   size (the 50 M row system needs ~32 GB of host COO and minutes of numpy time; say so next to the numbers)
+  momentum3_<n>  : configs[4] 3-DOF nonsymmetric momentum, smoother-only preconditioner (max_levels 1), Jacobi and SGS
+  <method>_256   : lap7_256 with cg | bicg | fgmres | cogmres | boomeramg instead of gmres
+"""
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "hypre-mini-app_b200", "python"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def run(bh, name, linear_system, solver, amg, repeat=2):
+    import numpy as np
+    import torch
+    stream = torch.cuda.ExternalStream(bh.stream_ptr())
+    best = None
+    for k in range(repeat):
+        s = bh.HypreSystem({"linear_system": linear_system, "solver_settings": solver, "boomeramg_settings": amg})
+        s.setup_precon_and_solver()
+        s.load()
+        s.assemble_system()
+        bh.profile_enable(True, 8e6)
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        ev[0].record(stream)
+        s.solver.set_precond(s.precond)
+        s.solver.setup(s.A, s.b, s.x)
+        ev[1].record(stream)
+        s.solver.solve(s.A, s.b, s.x)
+        ev[2].record(stream)
+        bh.synchronize()
+        torch.cuda.synchronize()
+        prof = bh.profile_summary()
+        bh.profile_enable(False)
+        x = s.solution()
+        amg_h = s.precond if s.precond is not None else getattr(s, "amg_solver", None)
+        rec = {"case": name, "rows": int(s.global_rows), "setup_s": ev[0].elapsed_time(ev[1]) * 1e-3, "solve_s": ev[1].elapsed_time(ev[2]) * 1e-3,
+               "iterations": s.solver.iterations, "final_relres": s.solver.relres, "converged": int(s.solver.converged),
+               "max_err_vs_1": float(np.abs(x - 1.0).max()), "levels": amg_h.num_levels if amg_h is not None else 0,
+               "method": solver["method"], "amg": amg,
+               "kernel_gbs": {c: round(v[2] / 1e9 / (v[0] / 1e3)) for c, v in prof.items() if v[0] > 0 and c.startswith(("spmv", "multi", "krylov"))}}
+        rec["per_iteration_ms"] = 1e3 * rec["solve_s"] / max(1, rec["iterations"])
+        s.destroy_system()
+        if best is None or rec["setup_s"] + rec["solve_s"] < best["setup_s"] + best["solve_s"]:
+            best = rec
+    print(json.dumps(best), flush=True)
+
+
+def main():
+    quick = "--quick" in sys.argv
+    import b200hypre as bh
+    bh.comm_init(0, 1)
+    bh.pool_reserve(int((8 if quick else 60) * 2 ** 30))
+    from workloads import momentum3, poisson27_hex
+    gm = {"method": "gmres", "preconditioner": "boomeramg", "tolerance": 1e-8, "kspace": 50, "max_iterations": 400}
+    n7 = 64 if quick else 256
+    # lap27 at full size
+    run(bh, f"lap27_{n7}", {"type": "build_27pt_stencil", "nx": n7, "ny": n7, "nz": n7}, gm, {"strong_threshold": 0.57})
+    # sibling Krylov methods on lap7
+    for method in ("gmres", "fgmres", "cogmres", "cg", "bicg", "boomeramg"):
+        sv = dict(gm, method=method)
+        if method == "boomeramg":
+            sv.update(relax_type=18, relax_order=0, strong_threshold=0.25, max_iterations=100)
+        run(bh, f"{method}_{n7}", {"type": "build_7pt_stencil", "nx": n7, "ny": n7, "nz": n7}, sv, {})
+    # perturbed-hex Poisson + Chebyshev (relax 16)
+    n = 32 if quick else 144
+    t0 = time.time()
+    A, b = poisson27_hex(n)
+    sys.stderr.write(f"poisson27_hex({n}) built in {time.time() - t0:.1f} s\n")
+    run(bh, f"poisson27_{n}", {"type": "csr", "ptr": A.indptr, "col": A.indices, "val": A.data, "rhs": b}, gm, {"relax_type": 16, "strong_threshold": 0.5})
+    del A, b
+    # momentum: smoother-only preconditioner
+    n = 24 if quick else 128
+    t0 = time.time()
+    A, b = momentum3(n)
+    sys.stderr.write(f"momentum3({n}) built in {time.time() - t0:.1f} s\n")
+    ls = {"type": "csr", "ptr": A.indptr, "col": A.indices, "val": A.data, "rhs": b}
+    run(bh, f"momentum3_{n}_jacobi", ls, gm, {"max_levels": 1, "relax_type": 18})
+    run(bh, f"momentum3_{n}_sgs", ls, gm, {"max_levels": 1, "relax_type": 6, "relax_order": 0})
+    run(bh, f"momentum3_{n}_bicg_jacobi", ls, dict(gm, method="bicg"), {"max_levels": 1, "relax_type": 18})
+
+
+if __name__ == "__main__":
+    main()
