@@ -7,7 +7,8 @@
 //     preconditioner handle, HypreSystem.cpp:99-110);
 //   * build_27pt_stencil / build_7pt_stencil call the device generator of libb200hypre with true-neighbour halo columns
 //     (the reference glue at HypreSystem.cpp:1555 maps halo indices to fictitious global columns);
-//   * the ILU solver / preconditioner (outside the built path) throws instead of running.
+//   * ILU: only the default combination (ilu_type 0, fill 0, local_reordering 0, trisolve 1 = block-Jacobi ILU(0)) is built;
+//     other values are passed on and rejected by HYPRE_ILUSetup.
 #include "HypreSystem.h"
 
 #include <algorithm>
@@ -61,7 +62,7 @@ void HypreSystem::setup_precon_and_solver() {
 
   if (preconditioner == "boomeramg") setup_boomeramg_precond();
   else if (preconditioner == "none") usePrecond_ = false;
-  else if (preconditioner == "ilu") throw std::runtime_error("preconditioner 'ilu' is outside the built path (SURVEY.md §8f.4)");
+  else if (preconditioner == "ilu") setup_ilu_precond();
   else throw std::runtime_error("Invalid option for preconditioner provided" + preconditioner);
 
   if (method == "gmres") setup_gmres();
@@ -70,8 +71,7 @@ void HypreSystem::setup_precon_and_solver() {
   else if (method == "bicg") setup_bicg();
   else if (method == "fgmres") setup_fgmres();
   else if (method == "cogmres") setup_cogmres();
-  else if (method == "ilu")
-    throw std::runtime_error("solver method 'ilu' is outside the built path (SURVEY.md §8f.4)");
+  else if (method == "ilu") setup_ilu();
   else throw std::runtime_error("Invalid option for solver method provided: " + method);
   MPI_Barrier(comm_);
   fflush(stdout);
@@ -211,6 +211,43 @@ void HypreSystem::setup_gmres() {
   solverSolvePtr_ = &HYPRE_ParCSRGMRESSolve;
   solverItersPtr_ = &HYPRE_ParCSRGMRESGetNumIterations;
   solverRelresPtr_ = &HYPRE_ParCSRGMRESGetFinalRelativeResidualNorm;
+}
+
+// ---- HypreSystem.cpp:328-370 (preconditioner) and :457-497 (solver): one option surface, two YAML nodes and defaults ---------
+static void ilu_options(HYPRE_Solver h, YAML::Node node, int max_iter_default, int print_level_default) {
+  HYPRE_ILUSetType(h, get_optional(node, "ilu_type", 0));
+  HYPRE_ILUSetMaxIter(h, get_optional(node, "max_iterations", max_iter_default));
+  HYPRE_ILUSetTol(h, get_optional(node, "tolerance", 0.0));
+  HYPRE_ILUSetLocalReordering(h, get_optional(node, "local_reordering", 0));
+  HYPRE_ILUSetPrintLevel(h, get_optional(node, "print_level", print_level_default));
+  HYPRE_ILUSetLevelOfFill(h, get_optional(node, "fill", 0));
+  HYPRE_ILUSetMaxNnzPerRow(h, get_optional(node, "max_nnz_per_row", 1000));
+  HYPRE_ILUSetDropThreshold(h, get_optional(node, "drop_threshold", 1.0e-2));
+  HYPRE_ILUSetIterativeSetupType(h, get_optional(node, "iterative_algorithm_type", 0));
+  HYPRE_ILUSetIterativeSetupOption(h, get_optional(node, "iterative_setup_option", 2));
+  HYPRE_ILUSetIterativeSetupMaxIter(h, get_optional(node, "iterative_ilu_max_iterations", 1));
+  HYPRE_ILUSetIterativeSetupTolerance(h, get_optional(node, "iterative_ilu_tolerance", 1e-5));
+  HYPRE_ILUSetTriSolve(h, get_optional(node, "trisolve", 1));
+  HYPRE_ILUSetLowerJacobiIters(h, get_optional(node, "lower_jacobi_iters", 5));
+  HYPRE_ILUSetUpperJacobiIters(h, get_optional(node, "upper_jacobi_iters", 5));
+}
+void HypreSystem::setup_ilu_precond() {
+  HYPRE_ILUCreate(&precond_);
+  ilu_options(precond_, inpfile_["ilu_preconditioner_settings"], 1, 1);
+  precondSetupPtr_ = &HYPRE_ILUSetup;
+  precondSolvePtr_ = &HYPRE_ILUSolve;
+  precondDestroyPtr_ = &HYPRE_ILUDestroy;
+}
+void HypreSystem::setup_ilu() {
+  HYPRE_ILUCreate(&solver_);
+  ilu_options(solver_, inpfile_["solver_settings"], 20, 4);
+  solverDestroyPtr_ = &HYPRE_ILUDestroy;
+  solverSetupPtr_ = &HYPRE_ILUSetup;
+  solverPrecondPtr_ = nullptr;
+  solverSolvePtr_ = &HYPRE_ILUSolve;
+  solverItersPtr_ = &HYPRE_ILUGetNumIterations;
+  solverRelresPtr_ = &HYPRE_ILUGetFinalRelativeResidualNorm;
+  usePrecond_ = false;
 }
 
 // ---- HypreSystem.cpp:372-388, 406-421, 423-438, 440-455: the sibling Krylov methods -----------------------------------------

@@ -5,8 +5,8 @@
 // destroy_system, driven by /root/reference/src/main.cpp:172-192), same YAML keys and defaults, same
 // timer names, the seven solver / preconditioner function pointers (HypreSystem.h:265-277) and the COO staging
 // vectors rows_/cols_/vals_ (HypreSystem.h:174-227).  Written from scratch against the behaviour documented in
-// SURVEY.md; methods gmres | cogmres | fgmres | bicg | cg | boomeramg with BoomerAMG / no preconditioner are wired, the
-// ILU solver / preconditioner of HypreSystem.cpp:61,82 raises "outside the built path" (SURVEY.md §8f.4).
+// SURVEY.md; methods gmres | cogmres | fgmres | bicg | cg | boomeramg with BoomerAMG / no preconditioner are wired, and
+// the ILU preconditioner / solver of HypreSystem.cpp:61,82 in its default form (block-Jacobi ILU(0)).
 #pragma once
 #include <string>
 #include <utility>
@@ -72,6 +72,8 @@ class HypreSystem {
   void setup_fgmres();             // :406-421
   void setup_bicg();               // :423-438
   void setup_cg();                 // :440-455
+  void setup_ilu_precond();        // :328-370
+  void setup_ilu();                // :457-497
 
   MPI_Comm comm_;
   YAML::Node &inpfile_;

@@ -28,6 +28,11 @@ KrylovHandle *as_krylov(HYPRE_Solver s, int method) {
                method == Krylov::PCG ? "handle is not a ParCSR PCG solver" : "handle is not a ParCSR BiCGSTAB solver");
   return static_cast<KrylovHandle *>(b);
 }
+IluHandle *as_ilu(HYPRE_Solver s) {
+  SolverBase *b = as_solver(s);
+  B200_REQUIRE(b && b->kind == SolverBase::ILU, "handle is not an ILU solver");
+  return static_cast<IluHandle *>(b);
+}
 int accumulate_error(int code) {
   g_error_flag |= code;
   return g_error_flag;

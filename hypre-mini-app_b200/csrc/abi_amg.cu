@@ -124,10 +124,12 @@ AMG_SETTER(HYPRE_BoomerAMGSetILUIterSetupOption, HYPRE_Int, true, (void)v)
 AMG_SETTER(HYPRE_BoomerAMGSetILUIterSetupMaxIter, HYPRE_Int, true, (void)v)
 AMG_SETTER(HYPRE_BoomerAMGSetILUIterSetupTolerance, HYPRE_Real, true, (void)v)
 
-HYPRE_Int HYPRE_ILUSetTriSolve(HYPRE_Solver solver, HYPRE_Int) {
-  // the mini-app calls this on the BoomerAMG handle (HypreSystem.cpp:306); harmless no-op
+HYPRE_Int HYPRE_ILUSetTriSolve(HYPRE_Solver solver, HYPRE_Int v) {
+  // the mini-app also calls this on the BoomerAMG handle (HypreSystem.cpp:306): harmless no-op there
   API_ARG(solver, "HYPRE_ILUSetTriSolve: null solver");
-  return 0;
+  API_BEGIN
+  if (as_solver(solver)->kind == SolverBase::ILU) as_ilu(solver)->ilu.tri_solve = v;
+  API_END
 }
 HYPRE_Int HYPRE_BoomerAMGSetCycleRelaxType(HYPRE_Solver solver, HYPRE_Int relax_type, HYPRE_Int k) {
   API_ARG(solver && k >= 1 && k <= 3 && relax_type >= 0, "HYPRE_BoomerAMGSetCycleRelaxType: bad argument");

@@ -191,4 +191,63 @@ HYPRE_Int HYPRE_ParCSRBiCGSTABSetStopCrit(HYPRE_Solver solver, HYPRE_Int stop_cr
   API_BEGIN as_krylov(solver, Krylov::BICGSTAB); API_END
 }
 
+
+// ---- ILU (HypreSystem.cpp:328-370 as preconditioner, :457-497 as solver): block-Jacobi ILU(0), ilu.cu --------------------
+HYPRE_Int HYPRE_ILUCreate(HYPRE_Solver *solver) {
+  API_ARG(solver, "HYPRE_ILUCreate: null output");
+  API_BEGIN *solver = reinterpret_cast<HYPRE_Solver>(static_cast<SolverBase *>(new IluHandle())); API_END
+}
+HYPRE_Int HYPRE_ILUDestroy(HYPRE_Solver solver) { API_BEGIN if (solver) { as_ilu(solver); destroy_solver(solver); } API_END }
+HYPRE_Int HYPRE_ILUSetup(HYPRE_Solver solver, HYPRE_ParCSRMatrix A, HYPRE_ParVector, HYPRE_ParVector) {
+  API_ARG(solver && A, "HYPRE_ILUSetup: null argument");
+  API_BEGIN ilu_setup(as_ilu(solver)->ilu, *as_par(A)); API_END
+}
+HYPRE_Int HYPRE_ILUSolve(HYPRE_Solver solver, HYPRE_ParCSRMatrix A, HYPRE_ParVector b, HYPRE_ParVector x) {
+  API_ARG(solver && A && b && x, "HYPRE_ILUSolve: null argument");
+  API_BEGIN ilu_solve(as_ilu(solver)->ilu, *as_par(A), as_vec(b)->p, as_vec(x)->p, precond_zero_guess_hint()); API_END
+}
+#define ILU_SETTER(NAME, TYPE, COND, STMT)                                  \
+  HYPRE_Int NAME(HYPRE_Solver solver, TYPE v) {                             \
+    API_ARG(solver && (COND), #NAME ": bad argument");                      \
+    API_BEGIN Ilu &u = as_ilu(solver)->ilu; (void)u; STMT; API_END          \
+  }
+ILU_SETTER(HYPRE_ILUSetType, HYPRE_Int, v >= 0, u.type = v)                              /* only 0 is built: checked at Setup */
+ILU_SETTER(HYPRE_ILUSetMaxIter, HYPRE_Int, v >= 0, u.max_iter = v)
+ILU_SETTER(HYPRE_ILUSetTol, HYPRE_Real, v >= 0, u.tol = v)
+ILU_SETTER(HYPRE_ILUSetLocalReordering, HYPRE_Int, v >= 0, u.reordering = v)           /* only 0 is built */
+ILU_SETTER(HYPRE_ILUSetPrintLevel, HYPRE_Int, true, u.print_level = v)
+ILU_SETTER(HYPRE_ILUSetLogging, HYPRE_Int, true, u.logging = v)
+ILU_SETTER(HYPRE_ILUSetLevelOfFill, HYPRE_Int, v >= 0, u.fill = v)                      /* only 0 is built */
+ILU_SETTER(HYPRE_ILUSetMaxNnzPerRow, HYPRE_Int, true, (void)v)                          /* ILUT parameter: no effect on ILU(0) */
+ILU_SETTER(HYPRE_ILUSetDropThreshold, HYPRE_Real, true, (void)v)                        /* ILUT parameter: no effect on ILU(0) */
+ILU_SETTER(HYPRE_ILUSetIterativeSetupType, HYPRE_Int, v >= 0, u.iter_setup_type = v)    /* only 0 (non-iterative) is built */
+ILU_SETTER(HYPRE_ILUSetIterativeSetupOption, HYPRE_Int, true, (void)v)
+ILU_SETTER(HYPRE_ILUSetIterativeSetupMaxIter, HYPRE_Int, true, (void)v)
+ILU_SETTER(HYPRE_ILUSetIterativeSetupTolerance, HYPRE_Real, true, (void)v)
+ILU_SETTER(HYPRE_ILUSetLowerJacobiIters, HYPRE_Int, true, (void)v)                      /* used by trisolve 0 only */
+ILU_SETTER(HYPRE_ILUSetUpperJacobiIters, HYPRE_Int, true, (void)v)
+#undef ILU_SETTER
+HYPRE_Int HYPRE_ILUGetNumIterations(HYPRE_Solver solver, HYPRE_Int *out) {
+  API_ARG(solver && out, "HYPRE_ILUGetNumIterations: null argument");
+  API_BEGIN *out = as_ilu(solver)->ilu.num_iterations; API_END
+}
+HYPRE_Int HYPRE_ILUGetFinalRelativeResidualNorm(HYPRE_Solver solver, HYPRE_Real *out) {
+  API_ARG(solver && out, "HYPRE_ILUGetFinalRelativeResidualNorm: null argument");
+  API_BEGIN *out = as_ilu(solver)->ilu.rel_resid; API_END
+}
+// inspection (tests): factor values in the pattern / order of the diagonal block, and the inverted pivots
+HYPRE_Int b200hypre_ilu_get_factors(HYPRE_Solver solver, HYPRE_Real *val, HYPRE_Real *dinv) {
+  API_ARG(solver && val && dinv, "b200hypre_ilu_get_factors: null argument");
+  API_BEGIN
+  Ilu &u = as_ilu(solver)->ilu;
+  B200_REQUIRE(u.setup_done, "ILU: factors requested before Setup");
+  B200_CUDA(cudaMemcpyAsync(val, u.fval.p, sizeof(double) * (size_t)(u.Lm.diag.nnz + u.Um.diag.nnz - u.n), cudaMemcpyDeviceToHost, stream()));
+  B200_CUDA(cudaMemcpyAsync(dinv, u.dinv.p, sizeof(double) * (size_t)u.n, cudaMemcpyDeviceToHost, stream()));
+  B200_CUDA(cudaStreamSynchronize(stream()));
+  API_END
+}
+HYPRE_Real b200hypre_ilu_setup_seconds(HYPRE_Solver solver) {
+  try { return as_ilu(solver)->ilu.setup_seconds; } catch (const std::exception &e) { set_error(HYPRE_ERROR_ARG, e.what()); return -1.0; }
+}
+
 }  // extern "C"

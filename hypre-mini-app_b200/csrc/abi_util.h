@@ -10,7 +10,7 @@ namespace b200 {
 int set_error(int code, const char *what);
 
 struct SolverBase {
-  enum Kind { GMRES = 1, AMG = 2, KRYLOV = 3 } kind;
+  enum Kind { GMRES = 1, AMG = 2, KRYLOV = 3, ILU = 4 } kind;
   explicit SolverBase(Kind k) : kind(k) {}
   virtual ~SolverBase() {}
 };
@@ -21,6 +21,10 @@ struct GmresHandle : SolverBase {
 struct KrylovHandle : SolverBase {   // PCG / BiCGSTAB
   Krylov k;
   KrylovHandle() : SolverBase(KRYLOV) {}
+};
+struct IluHandle : SolverBase {
+  Ilu ilu;
+  IluHandle() : SolverBase(ILU) {}
 };
 struct AmgHandle : SolverBase {
   Amg amg;
@@ -40,6 +44,7 @@ inline SolverBase *as_solver(HYPRE_Solver s) { return reinterpret_cast<SolverBas
 GmresHandle *as_gmres(HYPRE_Solver s);
 AmgHandle *as_amg(HYPRE_Solver s);
 KrylovHandle *as_krylov(HYPRE_Solver s, int method);
+IluHandle *as_ilu(HYPRE_Solver s);
 int accumulate_error(int code);  // OR a solver return code (e.g. HYPRE_ERROR_CONV) into the global flag, return the flag
 
 bool precond_zero_guess_hint();

@@ -178,6 +178,25 @@ void set_precond_zero_guess_hint(bool v);  // the next preconditioner call may t
 void krylov_setup(Krylov &k, ParCsr &A, ParVec &b, ParVec &x);
 int krylov_solve(Krylov &k, ParCsr &A, ParVec &b, ParVec &x);
 
+// ---- ILU (ilu.cu): hypre ILU type 0 / fill 0 = block-Jacobi ILU(0) ------------------------------------------------------------
+struct Ilu {
+  int type = 0, fill = 0, reordering = 0, tri_solve = 1, iter_setup_type = 0;   // the only combination built (checked at Setup)
+  int max_iter = 20, print_level = 0, logging = 0;
+  double tol = 1e-7;
+  int n = 0;
+  ParCsr Lm, Um;                  // L with unit diagonal first / U with the pivot first, local block only
+  GsPlan plan_l, plan_u;          // forward / backward wavefront schedules (gs.cu)
+  DVec<double> fval, dinv;        // factor values in the pattern of A.diag (inspection) and inverted pivots
+  DVec<double> r, y, z;
+  DotWork dw;
+  bool setup_done = false;
+  int num_iterations = 0;
+  double rel_resid = 0.0, setup_seconds = 0.0;
+};
+void ilu_setup(Ilu &ilu, ParCsr &A);
+void ilu_apply(Ilu &ilu, const double *r, double *z);
+void ilu_solve(Ilu &ilu, ParCsr &A, const double *b, double *x, bool zero_guess);
+
 // ---- IJ interface (ij.cu) --------------------------------------------------------------------------------------------
 struct IJMatrix {
   i64 ilower = 0, iupper = -1, jlower = 0, jupper = -1;

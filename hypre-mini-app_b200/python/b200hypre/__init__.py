@@ -298,5 +298,5 @@ def matvec(A, x, y, alpha=1.0, beta=0.0):
     check(lib().HYPRE_ParCSRMatrixMatvec(alpha, A.object(), x.object(), beta, y.object()), "Matvec")
 
 
-from .solvers import AMGSolver, BoomerAMG, GMRES, ParKrylov  # noqa: E402
+from .solvers import ILU, AMGSolver, BoomerAMG, GMRES, ParKrylov  # noqa: E402
 from .system import HypreSystem, generate_laplace  # noqa: E402

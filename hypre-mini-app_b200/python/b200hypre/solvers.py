@@ -148,9 +148,10 @@ class ParKrylov:
         L = lib()
         if amg is None:
             check(self._fn("SetPrecond")(self.h, None, None, None))
-        else:  # HypreSystem.cpp:402 with the pointers stored at :323-324
-            solve = C.cast(L.HYPRE_BoomerAMGSolve, VP)
-            setup = C.cast(L.HYPRE_BoomerAMGSetup, VP)
+        else:  # HypreSystem.cpp:402 with the pointers stored at :323-324 (BoomerAMG) or :367-368 (ILU)
+            prefix = getattr(amg, "ABI_PREFIX", "HYPRE_BoomerAMG")
+            solve = C.cast(getattr(L, prefix + "Solve"), VP)
+            setup = C.cast(getattr(L, prefix + "Setup"), VP)
             check(self._fn("SetPrecond")(self.h, solve, setup, amg.h))
 
     def setup(self, A, b, x):
@@ -236,3 +237,83 @@ class AMGSolver:
 
     def destroy(self):
         pass
+
+
+class ILU:
+    """hypre's ILU handle (block-Jacobi ILU(0) is the built combination): preconditioner (`preconditioner: ilu`, keys of
+    ilu_preconditioner_settings, HypreSystem.cpp:328-370) or solver (`method: ilu`, keys of solver_settings, :457-497)."""
+    ABI_PREFIX = "HYPRE_ILU"
+    _INT = {"ilu_type": "SetType", "max_iterations": "SetMaxIter", "local_reordering": "SetLocalReordering", "print_level": "SetPrintLevel",
+            "fill": "SetLevelOfFill", "max_nnz_per_row": "SetMaxNnzPerRow", "iterative_algorithm_type": "SetIterativeSetupType",
+            "iterative_setup_option": "SetIterativeSetupOption", "iterative_ilu_max_iterations": "SetIterativeSetupMaxIter",
+            "trisolve": "SetTriSolve", "lower_jacobi_iters": "SetLowerJacobiIters", "upper_jacobi_iters": "SetUpperJacobiIters"}
+    _REAL = {"tolerance": "SetTol", "drop_threshold": "SetDropThreshold", "iterative_ilu_tolerance": "SetIterativeSetupTolerance"}
+
+    def __init__(self, **settings):
+        L = lib()
+        for name in self._REAL.values():
+            getattr(L, "HYPRE_ILU" + name).argtypes = [VP, F64]
+        L.b200hypre_ilu_setup_seconds.restype = F64
+        L.b200hypre_ilu_setup_seconds.argtypes = [VP]
+        self.h = VP()
+        check(L.HYPRE_ILUCreate(C.byref(self.h)), "ILUCreate")
+        self.tol = 0.0
+        self.set(**settings)
+
+    def set(self, **settings):
+        L = lib()
+        for k, v in settings.items():
+            if k in self._INT:
+                check(getattr(L, "HYPRE_ILU" + self._INT[k])(self.h, int(v)), k)
+            elif k in self._REAL:
+                check(getattr(L, "HYPRE_ILU" + self._REAL[k])(self.h, float(v)), k)
+                if k == "tolerance":
+                    self.tol = float(v)
+            else:
+                raise KeyError(f"unknown ilu setting {k}")
+
+    # duck type of ParKrylov so that `method: ilu` plugs into HypreSystem.solve
+    def set_precond(self, _):
+        pass
+
+    def setup(self, A, b=None, x=None):
+        check(lib().HYPRE_ILUSetup(self.h, A.object(), b.object() if b else None, x.object() if x else None), "ILUSetup")
+
+    def solve(self, A, b, x):
+        check(lib().HYPRE_ILUSolve(self.h, A.object(), b.object(), x.object()), "ILUSolve")
+        return 0
+
+    @property
+    def iterations(self):
+        v = I32()
+        check(lib().HYPRE_ILUGetNumIterations(self.h, C.byref(v)))
+        return v.value
+
+    @property
+    def relres(self):
+        v = F64()
+        check(lib().HYPRE_ILUGetFinalRelativeResidualNorm(self.h, C.byref(v)))
+        return v.value
+
+    @property
+    def converged(self):
+        return int(self.tol == 0.0 or self.relres < self.tol)
+
+    @property
+    def setup_seconds(self):
+        return lib().b200hypre_ilu_setup_seconds(self.h)
+
+    def factors(self, nnz, n):
+        val, dinv = np.zeros(nnz), np.zeros(n)
+        check(lib().b200hypre_ilu_get_factors(self.h, _ptr(val), _ptr(dinv)), "ilu_get_factors")
+        return val, dinv
+
+    def history(self):
+        return np.zeros(0)
+
+    num_levels = 0
+
+    def destroy(self):
+        if self.h:
+            lib().HYPRE_ILUDestroy(self.h)
+            self.h = None

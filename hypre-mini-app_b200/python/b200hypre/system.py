@@ -12,7 +12,7 @@ import time
 import numpy as np
 
 from . import (HYPRE_MEMORY_DEVICE, I32, I64, VP, IJMatrix, IJVector, check, lib, process_grid, synchronize)
-from .solvers import AMGSolver, BoomerAMG, ParKrylov
+from .solvers import ILU, AMGSolver, BoomerAMG, ParKrylov
 
 
 class DeviceCOO:
@@ -61,17 +61,30 @@ class HypreSystem:
     def setup_precon_and_solver(self):
         ss = self.cfg.get("solver_settings", {})
         method = ss.get("method", "gmres")
-        if method not in ParKrylov.FAMILY and method != "boomeramg":
-            raise ValueError(f"solver method '{method}' is outside the built path (gmres | fgmres | cogmres | cg | bicg | boomeramg)")
+        if method not in ParKrylov.FAMILY and method not in ("boomeramg", "ilu"):
+            raise ValueError(f"Invalid option for solver method provided: {method}")
         precond = ss.get("preconditioner", "boomeramg")
         if precond == "boomeramg":
             amg = dict(DEFAULT_AMG)
             amg.update(self.cfg.get("boomeramg_settings", {}))
             self.precond = BoomerAMG(**amg)
+        elif precond == "ilu":   # setup_ilu_precond, HypreSystem.cpp:328-370 (defaults of the reference)
+            ilu = dict(ilu_type=0, max_iterations=1, tolerance=0.0, local_reordering=0, print_level=0, fill=0, trisolve=1)
+            ilu.update(self.cfg.get("ilu_preconditioner_settings", {}))
+            self.precond = ILU(**ilu)
         elif precond == "none":
             self.precond = None
         else:
-            raise ValueError(f"preconditioner '{precond}' is outside the built path (boomeramg | none)")
+            raise ValueError(f"Invalid option for preconditioner provided {precond}")
+        if method == "ilu":       # setup_ilu, HypreSystem.cpp:457-497: ILU sweeps as the solver, no preconditioner
+            keys = set(ILU._INT) | set(ILU._REAL)
+            ilu = dict(ilu_type=0, max_iterations=20, tolerance=0.0, local_reordering=0, print_level=0, fill=0, trisolve=1)
+            ilu.update({k: v for k, v in ss.items() if k in keys})
+            if self.precond is not None:
+                self.precond.destroy()
+            self.precond = None
+            self.solver = ILU(**ilu)
+            return
         if method == "boomeramg":
             # setup_boomeramg_solver (HypreSystem.cpp:91-117): BoomerAMG is the solver, no preconditioner.  The reference
             # applies the coarsening / relaxation keys of solver_settings to precond_ (:100-110), leaving solver_ on hypre's

@@ -202,6 +202,31 @@ HYPRE_Int HYPRE_ParCSRBiCGSTABGetFinalRelativeResidualNorm(HYPRE_Solver solver, 
 HYPRE_Int HYPRE_ParCSRBiCGSTABSetMinIter(HYPRE_Solver solver, HYPRE_Int min_iter);
 HYPRE_Int HYPRE_ParCSRBiCGSTABSetStopCrit(HYPRE_Solver solver, HYPRE_Int stop_crit);
 
+/* ---- ILU solver / preconditioner: HypreSystem.cpp:328-370 (setup_ilu_precond), :457-497 (setup_ilu).  Built: ilu_type 0 with
+ * level of fill 0 (block-Jacobi ILU(0)), local_reordering 0, direct triangular solves; other values are accepted by the
+ * setters and rejected by HYPRE_ILUSetup with HYPRE_ERROR_GENERIC. ---------------------------------------------------------- */
+HYPRE_Int HYPRE_ILUCreate(HYPRE_Solver *solver);                                       /* :331,:459 */
+HYPRE_Int HYPRE_ILUDestroy(HYPRE_Solver solver);                                       /* :369,:493 */
+HYPRE_Int HYPRE_ILUSetup(HYPRE_Solver solver, HYPRE_ParCSRMatrix A, HYPRE_ParVector b, HYPRE_ParVector x);   /* :367,:494 */
+HYPRE_Int HYPRE_ILUSolve(HYPRE_Solver solver, HYPRE_ParCSRMatrix A, HYPRE_ParVector b, HYPRE_ParVector x);   /* :368,:496 */
+HYPRE_Int HYPRE_ILUSetType(HYPRE_Solver solver, HYPRE_Int ilu_type);                    /* :332 */
+HYPRE_Int HYPRE_ILUSetMaxIter(HYPRE_Solver solver, HYPRE_Int max_iter);                 /* :333 */
+HYPRE_Int HYPRE_ILUSetTol(HYPRE_Solver solver, HYPRE_Real tol);                         /* :334 */
+HYPRE_Int HYPRE_ILUSetLocalReordering(HYPRE_Solver solver, HYPRE_Int reordering_type);  /* :335 */
+HYPRE_Int HYPRE_ILUSetPrintLevel(HYPRE_Solver solver, HYPRE_Int print_level);           /* :336 */
+HYPRE_Int HYPRE_ILUSetLogging(HYPRE_Solver solver, HYPRE_Int logging);
+HYPRE_Int HYPRE_ILUSetLevelOfFill(HYPRE_Solver solver, HYPRE_Int lfil);                 /* :339 */
+HYPRE_Int HYPRE_ILUSetMaxNnzPerRow(HYPRE_Solver solver, HYPRE_Int nzmax);               /* :342 */
+HYPRE_Int HYPRE_ILUSetDropThreshold(HYPRE_Solver solver, HYPRE_Real threshold);         /* :343 */
+HYPRE_Int HYPRE_ILUSetIterativeSetupType(HYPRE_Solver solver, HYPRE_Int v);             /* :351 */
+HYPRE_Int HYPRE_ILUSetIterativeSetupOption(HYPRE_Solver solver, HYPRE_Int v);           /* :353 */
+HYPRE_Int HYPRE_ILUSetIterativeSetupMaxIter(HYPRE_Solver solver, HYPRE_Int v);          /* :354 */
+HYPRE_Int HYPRE_ILUSetIterativeSetupTolerance(HYPRE_Solver solver, HYPRE_Real v);       /* :356 */
+HYPRE_Int HYPRE_ILUSetLowerJacobiIters(HYPRE_Solver solver, HYPRE_Int v);               /* :364 */
+HYPRE_Int HYPRE_ILUSetUpperJacobiIters(HYPRE_Solver solver, HYPRE_Int v);               /* :365 */
+HYPRE_Int HYPRE_ILUGetNumIterations(HYPRE_Solver solver, HYPRE_Int *num_iterations);
+HYPRE_Int HYPRE_ILUGetFinalRelativeResidualNorm(HYPRE_Solver solver, HYPRE_Real *res_norm);
+
 /* ---- BoomerAMG: HypreSystem.cpp:119-326 ------------------------------------------------------------------------------------ */
 HYPRE_Int HYPRE_BoomerAMGCreate(HYPRE_Solver *solver);                                                  /* :122 */
 HYPRE_Int HYPRE_BoomerAMGDestroy(HYPRE_Solver solver);                                                  /* :325 */
@@ -258,7 +283,7 @@ HYPRE_Int HYPRE_BoomerAMGSetILUIterSetupType(HYPRE_Solver solver, HYPRE_Int v);
 HYPRE_Int HYPRE_BoomerAMGSetILUIterSetupOption(HYPRE_Solver solver, HYPRE_Int v);
 HYPRE_Int HYPRE_BoomerAMGSetILUIterSetupMaxIter(HYPRE_Solver solver, HYPRE_Int v);
 HYPRE_Int HYPRE_BoomerAMGSetILUIterSetupTolerance(HYPRE_Solver solver, HYPRE_Real v);
-HYPRE_Int HYPRE_ILUSetTriSolve(HYPRE_Solver solver, HYPRE_Int v);   /* HypreSystem.cpp:306 (called on the AMG handle) */
+HYPRE_Int HYPRE_ILUSetTriSolve(HYPRE_Solver solver, HYPRE_Int v);   /* HypreSystem.cpp:361 on an ILU handle; :306 on the AMG handle (no-op) */
 
 /* ---- internals the mini-app touches for the AMG level dump: HypreSystem.cpp:700-714 ------------------------------------------ */
 typedef struct hypre_Solver_struct hypre_ParAMGData;

@@ -61,6 +61,8 @@ HYPRE_Int b200hypre_gmres_set_orthogonalization(HYPRE_Solver gmres, HYPRE_Int ki
 HYPRE_Int b200hypre_gmres_get_history(HYPRE_Solver gmres, HYPRE_Real *out, HYPRE_Int cap);   /* returns the history length */
 HYPRE_Real b200hypre_gmres_solve_seconds(HYPRE_Solver gmres);                                 /* history / seconds accept any Krylov handle */
 HYPRE_Int b200hypre_solver_converged(HYPRE_Solver krylov);
+HYPRE_Int b200hypre_ilu_get_factors(HYPRE_Solver ilu, HYPRE_Real *val, HYPRE_Real *dinv);   /* host arrays: nnz(A_diag), n */
+HYPRE_Real b200hypre_ilu_setup_seconds(HYPRE_Solver ilu);
 
 /* device name / compute capability / memory of the device this rank runs on (the checkMemory() print, HypreSystem.cpp:638-671) */
 HYPRE_Int b200hypre_device_info(char *name, HYPRE_Int name_cap, int *device, int *count, int *cc_major, int *cc_minor, double *free_gb,

@@ -262,7 +262,11 @@ struct Sys {
   double relres = 0.0, setup_s = 0.0, solve_s = 0.0;
   std::vector<double> hist;
   int converged = 0;
+  // block-Jacobi ILU(0) of the level-0 matrix (krylov.inc): factor values in A's pattern (L strictly lower, U strictly
+  // upper, the diagonal slot holds u_ii) and the inverted pivots
+  std::vector<double> ilu_val, ilu_dinv;
 };
+static void ilu_apply(Sys &s, const double *r, double *z);
 
 // ---------------------------------------------------------------------------------------------------------
 // Generator: laplace_3d_weak_scaling semantics (laplace_3d_weak_scaling.hpp:98-169,216-233,321,558,600;
@@ -1006,7 +1010,8 @@ static void gmres(Sys &s, double *x) {
   std::vector<double> rs(k_dim + 1), c(k_dim), sn(k_dim);
   std::vector<std::vector<double>> hh(k_dim + 1, std::vector<double>(k_dim, 0.0));
   auto precond = [&](const double *in, double *out) {
-    if (o.precond) vcycle(s, in, out);
+    if (o.precond == 2) ilu_apply(s, in, out);
+    else if (o.precond) vcycle(s, in, out);
     else std::memcpy(out, in, sizeof(double) * n);
   };
   s.hist.clear();
@@ -1167,7 +1172,7 @@ int ora_amg_setup(void *h) { amg_setup(*(Sys *)h); return 0; }
 int ora_gmres_solve(void *h, double *x) {
   Sys &s = *(Sys *)h;
   if (s.lev.empty()) return 1;
-  if (s.lev[0].vtemp.empty()) {  // no AMG setup (preconditioner none)
+  if (s.lev[0].vtemp.empty() && s.opt.precond != 2) {  // no AMG setup (preconditioner none)
     s.opt.precond = 0;
   }
   gmres(s, x);
@@ -1177,7 +1182,7 @@ int ora_gmres_solve(void *h, double *x) {
 int ora_krylov_solve(void *h, int method, double *x) {
   Sys &s = *(Sys *)h;
   if (s.lev.empty()) return 1;
-  if (s.lev[0].vtemp.empty()) {
+  if (s.lev[0].vtemp.empty() && s.opt.precond != 2) {
     if (method == 5) return 2;  // BoomerAMG as solver needs the hierarchy
     s.opt.precond = 0;
   }
@@ -1187,9 +1192,24 @@ int ora_krylov_solve(void *h, int method, double *x) {
     case 3: pcg(s, x); break;
     case 4: bicgstab(s, x); break;
     case 5: amg_solver(s, x); break;
+    case 6: if (s.ilu_val.empty()) return 4; ilu_solver(s, x); break;
     default: return 3;
   }
   return 0;
+}
+int ora_ilu_setup(void *h) {
+  Sys &s = *(Sys *)h;
+  if (s.lev.empty()) return 1;
+  ilu0_setup(s);
+  s.opt.precond = 2;
+  return 0;
+}
+int ora_ilu_apply(void *h, const double *r, double *z) { ilu_apply(*(Sys *)h, r, z); return 0; }
+int ora_ilu_get(void *h, double *val, double *dinv) {
+  Sys &s = *(Sys *)h;
+  std::copy(s.ilu_val.begin(), s.ilu_val.end(), val);
+  std::copy(s.ilu_dinv.begin(), s.ilu_dinv.end(), dinv);
+  return (int)s.ilu_val.size();
 }
 int ora_vcycle(void *h, const double *r, double *z) {
   Sys &s = *(Sys *)h;

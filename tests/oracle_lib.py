@@ -82,7 +82,7 @@ class Oracle:
     def setup(self):
         self.L.ora_amg_setup(self.h)
 
-    METHODS = {"gmres": 0, "fgmres": 1, "cogmres": 2, "cg": 3, "bicg": 4, "boomeramg": 5}
+    METHODS = {"gmres": 0, "fgmres": 1, "cogmres": 2, "cg": 3, "bicg": 4, "boomeramg": 5, "ilu": 6}
 
     def solve(self, x0=None, method="gmres"):
         x = np.zeros(self.n) if x0 is None else np.array(x0, dtype=np.float64)
@@ -92,6 +92,23 @@ class Oracle:
             rc = self.L.ora_krylov_solve(self.h, C.c_int(self.METHODS[method]), _p(x, C.c_double))
             assert rc == 0, f"oracle krylov solve failed ({rc})"
         return x
+
+    def ilu_setup(self):
+        """block-Jacobi ILU(0) of the level-0 matrix; becomes the preconditioner of the following solves"""
+        assert self.L.ora_ilu_setup(self.h) == 0
+
+    def ilu_apply(self, r):
+        r = np.ascontiguousarray(r, dtype=np.float64)
+        z = np.zeros_like(r)
+        self.L.ora_ilu_apply(self.h, _p(r, C.c_double), _p(z, C.c_double))
+        return z
+
+    def ilu_factors(self):
+        """(values in the pattern / order of matrix(0, 'A') with u_ii in the diagonal slot, inverted pivots)"""
+        nnz = len(self.matrix(0, "A")[1])
+        val, dinv = np.zeros(nnz), np.zeros(self.n)
+        self.L.ora_ilu_get(self.h, _p(val, C.c_double), _p(dinv, C.c_double))
+        return val, dinv
 
     def vcycle(self, r):
         r = np.ascontiguousarray(r, dtype=np.float64)

@@ -148,6 +148,26 @@ def test_multirank_sibling_krylov_methods(b200, method, transport):
         assert np.abs(x - xo).max() / np.abs(xo).max() <= 1e-8
 
 
+@pytest.mark.parametrize("method", ["gmres", "cg"])
+def test_multirank_block_jacobi_ilu(b200, method):
+    """`preconditioner: ilu` on 2 ranks: every rank factors its own diagonal block (hypre ILU type 0), compared with the
+    oracle's 2-virtual-rank block-Jacobi ILU(0)"""
+    n, grid = (8, 8, 8), (2, 1, 1)
+    cfg = settings(n, grid, 7)
+    cfg["solver_settings"].update(method=method, preconditioner="ilu", kspace=40, orthogonalization="mgs")
+    res = run_ranks(2, cfg)
+    o = Oracle(tolerance=1e-8, kspace=40, max_iterations=200)
+    o.gen_laplace(n, p=grid, stencil=7)
+    o.ilu_setup()
+    xo = o.solve(method=method)
+    x = np.concatenate([d["x"] for d in res])
+    its = int(res[0]["iterations"])
+    assert abs(its - o.iterations) <= 1, (its, o.iterations)
+    assert np.abs(x - 1.0).max() < 1e-5
+    if its == o.iterations:
+        assert np.abs(x - xo).max() / np.abs(xo).max() <= 1e-8
+
+
 def compare_with_oracle(res, n, grid, stencil, theta):
     o = Oracle(strong_threshold=theta)
     o.threads(8)

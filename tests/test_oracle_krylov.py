@@ -147,3 +147,81 @@ def test_pcg_zero_rhs_and_max_iter():
     o.set(max_iterations=3)
     o.solve(method="cg")
     assert o.iterations == 3 and o.L.ora_converged(o.h) == 0
+
+
+# ---- ILU(0) (hypre ILU type 0, fill 0: block-Jacobi ILU(0); HypreSystem.cpp:328-370,457-497) ---------------------------------
+def ilu_lu(o, lo=0, hi=None):
+    """L (unit lower) and U of one diagonal block as scipy matrices, from the oracle's factor values"""
+    ptr, col, _, shape = o.matrix(0, "A")
+    val, dinv = o.ilu_factors()
+    hi = shape[0] if hi is None else hi
+    rows = np.repeat(np.arange(shape[0]), np.diff(ptr))
+    blk = (rows >= lo) & (rows < hi) & (col >= lo) & (col < hi)
+    F = sp.csr_matrix((val[blk], (rows[blk] - lo, col[blk] - lo)), shape=(hi - lo, hi - lo))
+    Lm = sp.tril(F, -1) + sp.identity(hi - lo)
+    Um = sp.triu(F, 0)
+    return Lm.tocsr(), Um.tocsr(), dinv[lo:hi]
+
+
+@pytest.mark.parametrize("which", ["lap7", "lap27", "advdiff"])
+def test_ilu0_defining_property(which):
+    """ILU(0): (L U)_ij = a_ij on the pattern of A; 1 / u_ii stored as the inverted pivot"""
+    if which == "advdiff":
+        A, b = advection_diffusion(7)
+        o = Oracle()
+        o.set_csr(A.indptr, A.indices, A.data, b)
+    else:
+        o = system(7, 7 if which == "lap7" else 27)
+        A = o.scipy(0, "A")
+    o.ilu_setup()
+    Lm, Um, dinv = ilu_lu(o)
+    np.testing.assert_allclose(dinv, 1.0 / Um.diagonal(), rtol=1e-15)
+    P = (Lm @ Um).tocsr()
+    Ac = A.tocoo()
+    got = np.asarray(P[Ac.row, Ac.col]).ravel()
+    np.testing.assert_allclose(got, Ac.data, rtol=1e-12, atol=1e-13)
+    # the application is the two triangular solves
+    rng = np.random.default_rng(4)
+    r = rng.standard_normal(A.shape[0])
+    z = o.ilu_apply(r)
+    zref = spla.spsolve_triangular(Um, spla.spsolve_triangular(Lm, r, lower=True), lower=False)
+    np.testing.assert_allclose(z, zref, rtol=1e-11, atol=1e-13)
+
+
+def test_ilu0_is_exact_lu_for_a_tridiagonal_matrix():
+    n = 50
+    A = sp.diags([-np.ones(n - 1), 2.5 * np.ones(n), -1.5 * np.ones(n - 1)], [-1, 0, 1]).tocsr()
+    b = A @ np.ones(n)
+    o = Oracle(tolerance=1e-12, max_iterations=5)
+    o.set_csr(A.indptr, A.indices, A.data, b)
+    o.ilu_setup()
+    x = o.solve(method="ilu")
+    assert o.iterations == 1 and np.abs(x - 1.0).max() < 1e-12
+
+
+def test_ilu0_block_jacobi_on_virtual_ranks():
+    """every rank factors its own diagonal block; couplings to other ranks are ignored"""
+    o = Oracle()
+    o.gen_laplace((5, 5, 5), p=(2, 1, 1), stencil=7)
+    o.ilu_setup()
+    A = o.scipy(0, "A")
+    for lo, hi in ((0, 125), (125, 250)):
+        Lm, Um, _ = ilu_lu(o, lo, hi)
+        B = A[lo:hi][:, lo:hi].tocoo()
+        got = np.asarray((Lm @ Um).tocsr()[B.row, B.col]).ravel()
+        np.testing.assert_allclose(got, B.data, rtol=1e-12, atol=1e-13)
+
+
+@pytest.mark.parametrize("method", ["gmres", "cg", "bicg", "fgmres", "ilu"])
+def test_ilu_preconditioned_methods_converge(method):
+    tol = 1e-8
+    o = system(10, 7, tolerance=tol, kspace=30, max_iterations=300)
+    A, b = o.scipy(0, "A"), o.rhs()
+    o.ilu_setup()
+    x = o.solve(method=method)
+    assert o.L.ora_converged(o.h) == 1
+    assert np.linalg.norm(b - A @ x) / np.linalg.norm(b) < (50 * tol if method == "cg" else 1.0001 * tol)
+    if method != "ilu":   # ILU(0) preconditioning beats no preconditioning
+        p = system(10, 7, tolerance=tol, kspace=30, max_iterations=300, preconditioner=0)
+        p.solve(method=method)
+        assert o.iterations < p.iterations
