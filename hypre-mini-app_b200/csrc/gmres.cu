@@ -33,7 +33,10 @@ void gmres_setup(Gmres &g, ParCsr &A, ParVec &b, ParVec &x) {
   g.r.alloc(g.ld); g.r.zero();
   g.w.alloc(g.ld); g.w.zero();
   g.hdev.alloc(4 * (size_t)(g.k_dim + 8));
-  if (g.precond_setup) g.precond_setup(g.precond_data, &A, &b, &x);
+  if (g.precond_setup) {
+    int rc = g.precond_setup(g.precond_data, &A, &b, &x);
+    B200_REQUIRE(rc == 0, "preconditioner setup failed (see the error reported above)");
+  }
 }
 
 int gmres_solve(Gmres &g, ParCsr &A, ParVec &bvec, ParVec &xvec) {

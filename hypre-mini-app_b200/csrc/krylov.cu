@@ -21,7 +21,10 @@ void krylov_setup(Krylov &k, ParCsr &A, ParVec &b, ParVec &x) {
   k.W.alloc((size_t)k.ld * nvec);
   k.W.zero();
   k.hdev.alloc(16);
-  if (k.precond_setup) k.precond_setup(k.precond_data, &A, &b, &x);
+  if (k.precond_setup) {
+    int rc = k.precond_setup(k.precond_data, &A, &b, &x);
+    B200_REQUIRE(rc == 0, "preconditioner setup failed (see the error reported above)");
+  }
 }
 
 namespace {
