@@ -57,12 +57,15 @@ def run(bh, name, linear_system, solver, amg, repeat=2):
 
 def main():
     quick = "--quick" in sys.argv
+    big = "--big" in sys.argv      # only the two host-built workloads, at the largest size that is practical to build with numpy
     import b200hypre as bh
     bh.comm_init(0, 1)
     bh.pool_reserve(int((8 if quick else 60) * 2 ** 30))
     from workloads import momentum3, poisson27_hex
     gm = {"method": "gmres", "preconditioner": "boomeramg", "tolerance": 1e-8, "kspace": 50, "max_iterations": 400}
     n7 = 64 if quick else 256
+    if big:
+        return run_host_built(bh, gm, 192, 200)
     # lap27 at full size
     run(bh, f"lap27_{n7}", {"type": "build_27pt_stencil", "nx": n7, "ny": n7, "nz": n7}, gm, {"strong_threshold": 0.57})
     # sibling Krylov methods on lap7
@@ -71,15 +74,20 @@ def main():
         if method == "boomeramg":
             sv.update(relax_type=18, relax_order=0, strong_threshold=0.25, max_iterations=100)
         run(bh, f"{method}_{n7}", {"type": "build_7pt_stencil", "nx": n7, "ny": n7, "nz": n7}, sv, {})
+    run_host_built(bh, gm, 32 if quick else 144, 24 if quick else 128)
+
+
+def run_host_built(bh, gm, n_poisson, n_momentum):
+    from workloads import momentum3, poisson27_hex
     # perturbed-hex Poisson + Chebyshev (relax 16)
-    n = 32 if quick else 144
+    n = n_poisson
     t0 = time.time()
     A, b = poisson27_hex(n)
     sys.stderr.write(f"poisson27_hex({n}) built in {time.time() - t0:.1f} s\n")
     run(bh, f"poisson27_{n}", {"type": "csr", "ptr": A.indptr, "col": A.indices, "val": A.data, "rhs": b}, gm, {"relax_type": 16, "strong_threshold": 0.5})
     del A, b
     # momentum: smoother-only preconditioner
-    n = 24 if quick else 128
+    n = n_momentum
     t0 = time.time()
     A, b = momentum3(n)
     sys.stderr.write(f"momentum3({n}) built in {time.time() - t0:.1f} s\n")
