@@ -231,7 +231,8 @@ SpmvPlan make_plan(const DCsr &A, const DSell *S) {
   SpmvPlan p;
   double mean = A.nr > 0 ? (double)A.nnz / A.nr : 0.0;
   int lanes = 1;
-  while (lanes < 32 && lanes * 4 <= mean) lanes *= 2;  // ~2-4 entries per lane: with 4 rows in flight per group, fewer lanes per row win
+  const int per_lane = mean <= 12.0 ? 4 : 8;  // entries per lane: with 4 rows in flight per group, few lanes per row win (measured, r01zc/zd)
+  while (lanes < 32 && lanes * per_lane <= mean) lanes *= 2;
   if (mean <= 3.0) lanes = 1;
   p.lanes = lanes;
   const char *force = getenv("B200_SPMV_KERNEL");  // "csr" | "sell" : benchmarking override
