@@ -45,12 +45,6 @@ AmgHandle *as_amg(HYPRE_Solver s) {
 
 namespace {
 
-bool is_dev(const void *p) {
-  if (!p) return false;
-  cudaPointerAttributes at;
-  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
-  return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
-}
 
 // hypre's IJ text grammar: one file per rank "<name>.%05d"; header then "row col value" lines
 void print_parcsr(const ParCsr &A, i64 base_i, i64 base_j, const char *filename, bool ij_header_with_cols) {

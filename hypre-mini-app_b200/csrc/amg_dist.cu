@@ -562,10 +562,6 @@ __global__ void k_codes(int n, const int *cf, const int *f2c, i64 coarse_start, 
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) code[i] = (cf[i] > 0) ? coarse_start + f2c[i] : (i64)cf[i];
 }
-__global__ void k_fill_int(i64 n, int *a, int v) {
-  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
-  if (k < n) a[k] = v;
-}
 __global__ void k_fill_i64(i64 n, i64 *a, i64 v) {
   i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
   if (k < n) a[k] = v;

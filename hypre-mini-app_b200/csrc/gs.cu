@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(GS_THREADS) k_gs_sweep(int n, CsrView D, CsrVi
     if (!mask[i]) uout[i] = uin[i];          // rows outside the set keep their value (never read from uout)
   const int lane = threadIdx.x % G, grp = gtid / G, ngrp = gthreads / G;
   unsigned gm = 0xffffffffu;
-  if (G < 32) gm = ((1u << G) - 1u) << ((threadIdx.x & 31) / G * G);
+  if (G < 32) gm = ((1u << (G & 31)) - 1u) << ((threadIdx.x & 31) / G * G);
   unsigned long long epoch = 0;
   for (int l = 0; l < depth; ++l) {
     const int lb = lvl_off[l], le = lvl_off[l + 1];

@@ -134,8 +134,8 @@ struct NcclApi {
   const char *(*GetErrorString)(int) = nullptr;
 };
 NcclApi g_nccl;
-// ncclDataType_t / ncclRedOp_t values (nccl.h): ncclInt8 0, ncclInt32 2, ncclInt64 4, ncclFloat64 8; ncclSum 0, ncclMax 2
-constexpr int NCCL_INT8 = 0, NCCL_INT32 = 2, NCCL_INT64 = 4, NCCL_F64 = 8, NCCL_SUM = 0, NCCL_MAX = 2;
+// ncclDataType_t / ncclRedOp_t values (nccl.h): ncclInt8 0, ncclInt64 4, ncclFloat64 8; ncclSum 0, ncclMax 2
+constexpr int NCCL_INT8 = 0, NCCL_INT64 = 4, NCCL_F64 = 8, NCCL_SUM = 0, NCCL_MAX = 2;
 
 void nccl_load() {
   if (g_nccl.h) return;
