@@ -158,3 +158,37 @@ def test_larger_size_properties(b200, method):
     assert rel <= (50 * TOL if method == "cg" else 1.01 * TOL)                # PCG stops on the energy norm
     r.destroy()
     s.destroy_system()
+
+
+@pytest.mark.parametrize("method", ["gmres", "fgmres", "cogmres", "cg", "bicg", "boomeramg"])
+def test_zero_rhs_and_exact_initial_guess(b200, method):
+    """edge cases of the stopping logic: b = 0 gives x = 0 without iterating; an exact initial guess is accepted as is"""
+    n = 10
+    s = gpu_system(b200, method, 1, laplace_system(n))
+    s.b.set_values(np.zeros(n ** 3))
+    s.solve()
+    assert s.solver.iterations == 0
+    assert np.all(s.solution() == 0.0)
+    s.destroy_system()
+    s = gpu_system(b200, method, 1, laplace_system(n))
+    s.x.set_values(np.ones(n ** 3))            # rhs = A 1 (generator): the initial guess is the solution
+    s.solve()
+    # hypre_PCGSolve has no test before its first step: it enters iteration 1, finds <A p, p> = 0 and stops there
+    assert s.solver.iterations == (1 if method == "cg" else 0)
+    np.testing.assert_allclose(s.solution(), 1.0, rtol=0, atol=1e-14)
+    s.destroy_system()
+
+
+@pytest.mark.parametrize("method", ["gmres", "fgmres", "cogmres", "bicg"])
+def test_iteration_limit_is_reported_not_fatal(b200, method):
+    """max_iterations reached: HYPRE_ERROR_CONV semantics (flag raised, iterate returned), the mini-app ignores the code"""
+    n = 12
+    s = gpu_system(b200, method, 0, laplace_system(n), kspace=4, max_it=6)
+    s.solve()
+    assert s.solver.iterations == 6 and s.solver.converged == 0
+    o = Oracle(tolerance=TOL, kspace=4, max_iterations=6, preconditioner=0)
+    o.gen_laplace(n, stencil=7)
+    xo = o.solve(method=method)
+    assert o.iterations == 6
+    np.testing.assert_allclose(s.solution(), xo, rtol=1e-8, atol=1e-10)
+    s.destroy_system()
