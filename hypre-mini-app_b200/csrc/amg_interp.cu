@@ -76,7 +76,7 @@ __device__ __forceinline__ unsigned gballot(unsigned gm, int first_lane, bool pr
 // the operation order then run over shuffled registers, and the first G entries of the NEXT neighbour row are requested
 // before the current one is processed.
 template <int G, int H, int CAP, int MODE>
-__global__ void __launch_bounds__(256) k_interp_grp(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__ Scol,
+__global__ void __launch_bounds__(256, 5) k_interp_grp(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__ Scol,
                                                     const signed char *__restrict__ Scf, const int *__restrict__ cf,
                                                     const int *__restrict__ f2c, int n_own, int n_rows, double tf, int pmax, int lo,
                                                     int *lraw, int *len, const int *__restrict__ Pptr, int *Pcol, double *Pval,
