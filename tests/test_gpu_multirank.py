@@ -100,6 +100,7 @@ CASES = [
     ((6, 6, 6), (2, 1, 1), 27, 0.25),
     ((5, 5, 5), (2, 2, 2), 27, 0.57),
     ((12, 12, 12), (3, 1, 1), 7, 0.25),
+    ((24, 24, 24), (2, 2, 1), 7, 0.25),
 ]
 
 

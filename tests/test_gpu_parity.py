@@ -43,7 +43,7 @@ def assert_same_csr(got, ref, what, values=True):
         assert err <= VAL_RTOL, f"{what}: values differ by {err:.3e} relative"
 
 
-@pytest.mark.parametrize("n,stencil,theta", [(16, 7, 0.25), (24, 7, 0.25), (12, 27, 0.25), (16, 27, 0.57)])
+@pytest.mark.parametrize("n,stencil,theta", [(16, 7, 0.25), (24, 7, 0.25), (12, 27, 0.25), (16, 27, 0.57), (96, 7, 0.25), (48, 27, 0.57)])
 def test_hierarchy_bit_exact(b200, n, stencil, theta):
     s = make_system(b200, n, stencil, strong_threshold=theta)
     s.solve()
