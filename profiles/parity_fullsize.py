@@ -1,7 +1,8 @@
 """Hierarchy parity at the headline size (run under gpurun): BoomerAMG setup of the 7-pt Laplacian with n^3 rows on the GPU
 (through the C ABI) and on the CPU oracle, compared level by level -- sizes, CF splitting, patterns of A / P bit-for-bit,
 values by maximum relative difference -- plus iteration counts and solutions of the GMRES solve.
-    python profiles/parity_fullsize.py 256 > gpurun_out/parity_256.jsonl
+    python profiles/parity_fullsize.py 256 > gpurun_out/parity_256.jsonl            # 7-pt, theta 0.25
+    python profiles/parity_fullsize.py 160 27 0.57 > gpurun_out/parity_27pt_160.jsonl
 The oracle is test infrastructure; this script is a checker like the tests, kept out of the -m gpu suite because of its size."""
 import json
 import os
@@ -17,26 +18,28 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 def main():
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 256
+    stencil = int(sys.argv[2]) if len(sys.argv) > 2 else 7
+    theta = float(sys.argv[3]) if len(sys.argv) > 3 else 0.25
     import b200hypre as bh
     from oracle_lib import Oracle
     bh.comm_init(0, 1)
-    s = bh.HypreSystem({"linear_system": {"type": "build_7pt_stencil", "nx": n, "ny": n, "nz": n},
+    s = bh.HypreSystem({"linear_system": {"type": f"build_{stencil}pt_stencil", "nx": n, "ny": n, "nz": n},
                         "solver_settings": {"method": "gmres", "preconditioner": "boomeramg", "tolerance": 1e-8, "kspace": 50,
                                             "max_iterations": 200, "orthogonalization": "mgs"},
-                        "boomeramg_settings": {}})
+                        "boomeramg_settings": {"strong_threshold": theta}})
     s.setup_precon_and_solver()
     s.load()
     s.solve()
     t0 = time.time()
-    o = Oracle(tolerance=1e-8, kspace=50, max_iterations=200)
+    o = Oracle(tolerance=1e-8, kspace=50, max_iterations=200, strong_threshold=theta)
     cores = o.threads(0)
-    o.gen_laplace(n, stencil=7)
+    o.gen_laplace(n, stencil=stencil)
     o.setup()
     xo = o.solve()
     t_oracle = time.time() - t0
     amg = s.precond
     ok = amg.num_levels == o.num_levels
-    print(json.dumps({"n": n, "rows": n ** 3, "levels_gpu": amg.num_levels, "levels_oracle": o.num_levels, "oracle_seconds": round(t_oracle, 1),
+    print(json.dumps({"n": n, "stencil": stencil, "strong_threshold": theta, "rows": n ** 3, "levels_gpu": amg.num_levels, "levels_oracle": o.num_levels, "oracle_seconds": round(t_oracle, 1),
                       "oracle_threads": cores}), flush=True)
     for l in range(min(amg.num_levels, o.num_levels)):
         rec = {"level": l}
