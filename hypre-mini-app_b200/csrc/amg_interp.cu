@@ -360,7 +360,7 @@ __global__ void __launch_bounds__(256, 5) k_interp_grp(rows::Csr A, const int *_
     if (pmax > 0 && n_out > pmax) {
       double row_sum = 0.0, scale = 0.0;
       for (int k = 0; k < n_out; ++k) row_sum = row_sum + lv[k];
-      rows::qsort2abs(lc, lv, n_out);
+      rows::qsort2abs(lc, lv, n_out, pmax);
       for (int k = 0; k < pmax; ++k) scale = scale + lv[k];
       n_out = pmax;
       if (scale != 0.0 && scale != row_sum) {

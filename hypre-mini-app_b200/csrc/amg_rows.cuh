@@ -95,7 +95,10 @@ B200_HD void swap2(int *v, double *w, int i, int j) {
   int t = v[i]; v[i] = v[j]; v[j] = t;
   double d = w[i]; w[i] = w[j]; w[j] = d;
 }
-B200_HD void qsort2abs(int *v, double *w, int n) {
+// Only positions [0, keep) of the result are used by the caller (P_max_elmts truncation): a sub-range that starts at or
+// beyond `keep` is left unsorted.  Sub-ranges are partitioned independently of each other, so the first `keep` entries are
+// exactly those of the full sort.
+B200_HD void qsort2abs(int *v, double *w, int n, int keep) {
   int stk[64];
   int sp = 0;
   stk[sp++] = 0;
@@ -103,20 +106,20 @@ B200_HD void qsort2abs(int *v, double *w, int n) {
   while (sp > 0) {
     int right = stk[--sp];
     int left = stk[--sp];
-    while (left < right) {
+    while (left < right && left < keep) {
       swap2(v, w, left, (left + right) / 2);
       int last = left;
       for (int i = left + 1; i <= right; ++i)
         if (fabs(w[i]) > fabs(w[left])) swap2(v, w, ++last, i);
       swap2(v, w, left, last);
-      int l1 = left, r1 = last - 1, l2 = last + 1, r2 = right;
-      if (r1 - l1 < r2 - l2) {
-        if (l2 < r2) { stk[sp++] = l2; stk[sp++] = r2; }
-        left = l1; right = r1;
-      } else {
-        if (l1 < r1) { stk[sp++] = l1; stk[sp++] = r1; }
-        left = l2; right = r2;
-      }
+      const int l1 = left, r1 = last - 1, l2 = last + 1, r2 = right;
+      const bool do1 = l1 < r1, do2 = l2 < r2 && l2 < keep;
+      if (do1 && do2) {  // continue with the shorter part, stack the longer one (bounds the stack by log2 n entries)
+        if (r1 - l1 < r2 - l2) { stk[sp++] = l2; stk[sp++] = r2; left = l1; right = r1; }
+        else { stk[sp++] = l1; stk[sp++] = r1; left = l2; right = r2; }
+      } else if (do1) { left = l1; right = r1; }
+      else if (do2) { left = l2; right = r2; }
+      else break;
     }
   }
 }
@@ -242,7 +245,7 @@ B200_HD int interp_row(const Csr &A, const int *Sptr, const int *Scol, const int
   if (p_max > 0 && len > p_max) {
     double row_sum = 0.0, scale = 0.0;
     for (int k = 0; k < len; ++k) row_sum = row_sum + lv[k];
-    qsort2abs(lc, lv, len);
+    qsort2abs(lc, lv, len, p_max);
     for (int k = 0; k < p_max; ++k) scale = scale + lv[k];
     len = p_max;
     if (scale != 0.0 && scale != row_sum) {

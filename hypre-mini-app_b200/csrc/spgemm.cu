@@ -65,6 +65,74 @@ __device__ __forceinline__ int hash_insert(int *keys, int H, int c, bool &isnew)
   }
 }
 
+// symbolic pass, optimistic tier: give up after a bounded number of probes (the table is smaller than the row's upper bound)
+__device__ __forceinline__ bool hash_insert_capped(int *keys, int H, int c, bool &isnew) {
+  unsigned h = (((unsigned)c * 2654435761u) >> 11) & (unsigned)(H - 1);
+  for (int probes = 0; probes < 48; ++probes) {
+    int old = atomicCAS(keys + h, -1, c);
+    if (old == -1) { isnew = true; return true; }
+    if (old == c) { isnew = false; return true; }
+    h = (h + 1) & (unsigned)(H - 1);
+  }
+  isnew = false;
+  return false;
+}
+
+// Rows whose product-count bound is far above their true length (R * Q on the coarser levels: bound ~ 2000, length ~ 70)
+// are first counted by one warp in a 1024-slot table; a row whose table fills up (an insertion gives up) is marked -1 and
+// counted again by the exact tier for its bound.  A count that completes is exact, whatever the load of the table.
+constexpr int H_TRY = 1024;
+__global__ void __launch_bounds__(256) k_spgemm_count_try(rows::Csr A, rows::Csr B, const int *row_list, int nrows, int *nnz_out) {
+  __shared__ int s_keys[8][H_TRY];
+  const int g = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int idx = blockIdx.x * 8 + g;
+  if (idx >= nrows) return;
+  const int row = row_list[idx];
+  int *keys = s_keys[g];
+  for (int s = lane; s < H_TRY; s += 32) keys[s] = -1;
+  __syncwarp();
+  const int ab = A.ptr[row], ae = A.ptr[row + 1];
+  int mine = 0;
+  bool fail = false;
+  for (int base = ab; base < ae && !fail; base += 32) {
+    const int ka = base + lane;
+    int bb_l = 0, be_l = 0;
+    if (ka < ae) { const int k = A.col[ka]; bb_l = B.ptr[k]; be_l = B.ptr[k + 1]; }
+    const int nstep = min(32, ae - base);
+    int bb = __shfl_sync(0xffffffffu, bb_l, 0), be = __shfl_sync(0xffffffffu, be_l, 0);
+    int c_cur = (bb + lane < be) ? B.col[bb + lane] : -1;
+    for (int t = 0; t < nstep; ++t) {
+      int bbn = 0, ben = 0, c_nxt = -1;
+      if (t + 1 < nstep) {
+        bbn = __shfl_sync(0xffffffffu, bb_l, t + 1);
+        ben = __shfl_sync(0xffffffffu, be_l, t + 1);
+        if (bbn + lane < ben) c_nxt = B.col[bbn + lane];
+      }
+      bool bad = false;
+      if (c_cur >= 0) {
+        bool isnew;
+        bad |= !hash_insert_capped(keys, H_TRY, c_cur, isnew);
+        mine += isnew ? 1 : 0;
+      }
+      for (int kb = bb + 32 + lane; kb < be; kb += 32) {
+        bool isnew;
+        bad |= !hash_insert_capped(keys, H_TRY, B.col[kb], isnew);
+        mine += isnew ? 1 : 0;
+      }
+      if (__any_sync(0xffffffffu, bad)) { fail = true; break; }
+      bb = bbn; be = ben; c_cur = c_nxt;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mine += __shfl_down_sync(0xffffffffu, mine, o);
+  if (lane == 0) nnz_out[row] = fail ? -1 : mine;
+}
+// size[i] = bound[i] for the rows the optimistic tier gave up on, 0 elsewhere
+__global__ void k_retry_size(int n, const int *nnz_row, const int *bound, int *size) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) size[i] = (nnz_row[i] == -1) ? bound[i] : 0;
+}
+
 // one output row handled by the G threads of a group.  keys/vals: hash table of H slots; lk/lv: compaction list.
 template <int G, bool NUMERIC>
 __device__ __forceinline__ void spgemm_row(const rows::Csr &A, const rows::Csr &B, int row, int lane, unsigned mask, int *keys,
@@ -438,7 +506,23 @@ void csr_spgemm(const DCsr &A, const DCsr &B, DCsr &C, bool diag_first, bool sor
     Bins bins;
     BinLimits L{{16, 32, 64, 128, 512, 2048, 16384}};
     make_bins(A.nr, bound.p, L, bins);
+    // bins 5, 6 and the global-memory bin (bound > 512): optimistic warp-per-row count first, exact tier for the failures
+    const int first_big = 5;
+    const int n_big = A.nr > 0 ? (bins.offset[NB] + bins.count[NB]) - bins.offset[first_big] : 0;
+    if (n_big > 0) {
+      k_spgemm_count_try<<<div_up(n_big, 8), 256, 0, stream()>>>(rv(A), rv(B), bins.list.p + bins.offset[first_big], n_big, nnz_row.p);
+      count_launch();
+      for (int k = first_big; k <= NB; ++k) bins.count[k] = 0;
+    }
     spgemm_pass<false>(A, B, bins, L, nullptr, nullptr, nullptr, nnz_row.p, diag_first, sorted);
+    if (n_big > 0) {
+      DVec<int> retry((size_t)A.nr);
+      k_retry_size<<<div_up(A.nr, 256), 256, 0, stream()>>>(A.nr, nnz_row.p, bound.p, retry.p);
+      count_launch();
+      Bins again;
+      make_bins(A.nr, retry.p, L, again);
+      spgemm_pass<false>(A, B, again, L, nullptr, nullptr, nullptr, nnz_row.p, diag_first, sorted);
+    }
   }
   exclusive_scan(nnz_row.p, C.ptr.p, (i64)C.nr + 1);
   int last = 0;
