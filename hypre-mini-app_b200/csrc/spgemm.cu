@@ -138,13 +138,13 @@ template <int G, bool NUMERIC>
 __device__ __forceinline__ void spgemm_row(const rows::Csr &A, const rows::Csr &B, int row, int lane, unsigned mask, int *keys,
                                            double *vals, int H, int *cnt, int *lk, double *lv, const int *Cptr, int *Ccol,
                                            double *Cval, int *nnz_out, int diag_col, bool sorted) {
+  const int ab = A.ptr[row], ae = A.ptr[row + 1];   // requested before the table is cleared
   for (int s = lane; s < H; s += G) {
     keys[s] = -1;
     if (NUMERIC) vals[s] = 0.0;
   }
   if (lane == 0) *cnt = 0;
   gsync<G>(mask);
-  const int ab = A.ptr[row], ae = A.ptr[row + 1];
   int mine = 0;
   if constexpr (G <= 32) {
     // Latency restructuring: the entries of the A row are loaded G at a time, one per lane, together with the extent of
@@ -152,21 +152,29 @@ __device__ __forceinline__ void spgemm_row(const rows::Csr &A, const rows::Csr &
     // sequential -- it fixes the floating-point order -- but gets its operands by shuffle, and the first G entries of the
     // NEXT B row are requested before the current row is accumulated, so the loop exposes about one memory latency per
     // chunk instead of three per k.
+    // Two chunks are in flight: while chunk c is accumulated, the B-row extents of chunk c+1 and the A entries of chunk
+    // c+2 are on their way, and the last step of a chunk requests the first B row of the next one.
+    int k_l = 0, bb_l = 0, be_l = 0;
+    double a_l = 0.0;
+    if (ab + lane < ae) {
+      k_l = A.col[ab + lane];
+      if (NUMERIC) a_l = A.val[ab + lane];
+      bb_l = B.ptr[k_l];
+      be_l = B.ptr[k_l + 1];
+    }
+    int k_n = 0;
+    double a_n = 0.0;
+    if (ab + G + lane < ae) { k_n = A.col[ab + G + lane]; if (NUMERIC) a_n = A.val[ab + G + lane]; }
+    int bb = __shfl_sync(mask, bb_l, 0, G), be = __shfl_sync(mask, be_l, 0, G);
+    int c_cur = -1;
+    double v_cur = 0.0;
+    if (bb + lane < be) { c_cur = B.col[bb + lane]; if (NUMERIC) v_cur = B.val[bb + lane]; }
     for (int base = ab; base < ae; base += G) {
-      const int ka = base + lane;
-      int k_l = 0, bb_l = 0, be_l = 0;
-      double a_l = 0.0;
-      if (ka < ae) {
-        k_l = A.col[ka];
-        if (NUMERIC) a_l = A.val[ka];
-        bb_l = B.ptr[k_l];
-        be_l = B.ptr[k_l + 1];
-      }
+      int bb_n = 0, be_n = 0, k_nn = 0;
+      double a_nn = 0.0;
+      if (base + G + lane < ae) { bb_n = B.ptr[k_n]; be_n = B.ptr[k_n + 1]; }
+      if (base + 2 * G + lane < ae) { k_nn = A.col[base + 2 * G + lane]; if (NUMERIC) a_nn = A.val[base + 2 * G + lane]; }
       const int nstep = min(G, ae - base);
-      int bb = __shfl_sync(mask, bb_l, 0, G), be = __shfl_sync(mask, be_l, 0, G);
-      int c_cur = -1;
-      double v_cur = 0.0;
-      if (bb + lane < be) { c_cur = B.col[bb + lane]; if (NUMERIC) v_cur = B.val[bb + lane]; }
       for (int t = 0; t < nstep; ++t) {
         const double a = NUMERIC ? __shfl_sync(mask, a_l, t, G) : 0.0;
         int bbn = 0, ben = 0, c_nxt = -1;
@@ -174,8 +182,11 @@ __device__ __forceinline__ void spgemm_row(const rows::Csr &A, const rows::Csr &
         if (t + 1 < nstep) {
           bbn = __shfl_sync(mask, bb_l, t + 1, G);
           ben = __shfl_sync(mask, be_l, t + 1, G);
-          if (bbn + lane < ben) { c_nxt = B.col[bbn + lane]; if (NUMERIC) v_nxt = B.val[bbn + lane]; }
+        } else if (base + G < ae) {
+          bbn = __shfl_sync(mask, bb_n, 0, G);
+          ben = __shfl_sync(mask, be_n, 0, G);
         }
+        if (bbn + lane < ben) { c_nxt = B.col[bbn + lane]; if (NUMERIC) v_nxt = B.val[bbn + lane]; }
         if (c_cur >= 0) {
           bool isnew;
           int slot = hash_insert(keys, H, c_cur, isnew);
@@ -191,6 +202,7 @@ __device__ __forceinline__ void spgemm_row(const rows::Csr &A, const rows::Csr &
         if (NUMERIC) __syncwarp(mask);
         bb = bbn; be = ben; c_cur = c_nxt; v_cur = v_nxt;
       }
+      a_l = a_n; bb_l = bb_n; be_l = be_n; k_n = k_nn; a_n = a_nn;
     }
   } else {
   for (int ka = ab; ka < ae; ++ka) {
@@ -275,13 +287,15 @@ __global__ void k_spgemm_smem(rows::Csr A, rows::Csr B, const int *row_list, int
   extern __shared__ __align__(16) unsigned char smem[];
   const int groups = blockDim.x / G;
   const int g = threadIdx.x / G, lane = threadIdx.x % G;
-  // per group: cnt (int, padded to 8 B) | [vals H doubles | lv H/2 doubles] | keys H ints | [lk H/2 ints]
-  size_t per = 8 + (NUMERIC ? ((size_t)H * 8 + (size_t)H * 4 + (size_t)H * 4 + (size_t)H * 2) : (size_t)H * 4);
+  // per group: cnt (int, padded to 8 B) | [vals H doubles | lv H/2 doubles] | keys H ints | [lk H/2 ints]; the compaction
+  // list lv / lk exists only for sorted output (an unsorted row is written straight from the table)
+  const bool list = NUMERIC && sorted != 0;
+  size_t per = 8 + (NUMERIC ? ((size_t)H * 12 + (list ? (size_t)H * 6 : 0)) : (size_t)H * 4);
   unsigned char *base = smem + per * g;
   int *cnt = (int *)base;
   double *vals = (double *)(base + 8);
   double *lv = vals + (NUMERIC ? H : 0);
-  int *keys = (int *)(base + 8 + (NUMERIC ? (size_t)H * 12 : 0));
+  int *keys = (int *)(base + 8 + (NUMERIC ? (size_t)H * (list ? 12 : 8) : 0));
   int *lk = keys + H;
   unsigned mask = 0xffffffffu;
   if constexpr (G < 32) mask = ((1u << G) - 1u) << ((threadIdx.x & 31) / G * G);
@@ -415,7 +429,7 @@ void spgemm_pass(const DCsr &A, const DCsr &B, const Bins &bins, const BinLimits
   for (int k = 0; k < NB; ++k) {
     if (!bins.count[k]) continue;
     const int H = 2 * next_pow2(L.lim[k]);
-    const size_t per = 8 + (NUMERIC ? (size_t)H * 18 : (size_t)H * 4);
+    const size_t per = 8 + (NUMERIC ? (size_t)H * (sorted ? 18 : 12) : (size_t)H * 4);
     const int *list = bins.list.p + bins.offset[k];
     int G = g_b;
     if (H >= 4096) G = 256;
