@@ -138,7 +138,10 @@ template <int G, bool NUMERIC>
 __device__ __forceinline__ void spgemm_row(const rows::Csr &A, const rows::Csr &B, int row, int lane, unsigned mask, int *keys,
                                            double *vals, int H, int *cnt, int *lk, double *lv, const int *Cptr, int *Ccol,
                                            double *Cval, int *nnz_out, int diag_col, bool sorted) {
-  const int ab = A.ptr[row], ae = A.ptr[row + 1];   // requested before the table is cleared
+  // row < 0: a group without a row (tail of the list).  It follows the warp's control flow with an empty row, because for
+  // G <= 32 every shuffle / warp barrier below names the FULL warp: a group-specific mask would make the compiler
+  // serialise each of them over the groups of the warp (match + per-group barrier), several times the cost of the loop.
+  const int ab = row >= 0 ? A.ptr[row] : 0, ae = row >= 0 ? A.ptr[row + 1] : 0;   // requested before the table is cleared
   for (int s = lane; s < H; s += G) {
     keys[s] = -1;
     if (NUMERIC) vals[s] = 0.0;
@@ -147,13 +150,12 @@ __device__ __forceinline__ void spgemm_row(const rows::Csr &A, const rows::Csr &
   gsync<G>(mask);
   int mine = 0;
   if constexpr (G <= 32) {
-    // Latency restructuring: the entries of the A row are loaded G at a time, one per lane, together with the extent of
-    // the B row each of them selects (independent loads, one round trip for the whole chunk).  The k loop itself stays
-    // sequential -- it fixes the floating-point order -- but gets its operands by shuffle, and the first G entries of the
-    // NEXT B row are requested before the current row is accumulated, so the loop exposes about one memory latency per
-    // chunk instead of three per k.
+    // The entries of the A row are loaded G at a time, one per lane, together with the extent of the B row each of them
+    // selects.  The k loop itself stays sequential -- it fixes the floating-point order -- but gets its operands by shuffle.
     // Two chunks are in flight: while chunk c is accumulated, the B-row extents of chunk c+1 and the A entries of chunk
-    // c+2 are on their way, and the last step of a chunk requests the first B row of the next one.
+    // c+2 are on their way; every step requests the first G entries of the next B row before it accumulates its own.
+    // Chunk and step counts are the maxima over the groups of the warp (groups that are done run predicated off).
+    constexpr unsigned FULL = 0xffffffffu;
     int k_l = 0, bb_l = 0, be_l = 0;
     double a_l = 0.0;
     if (ab + lane < ae) {
@@ -165,41 +167,45 @@ __device__ __forceinline__ void spgemm_row(const rows::Csr &A, const rows::Csr &
     int k_n = 0;
     double a_n = 0.0;
     if (ab + G + lane < ae) { k_n = A.col[ab + G + lane]; if (NUMERIC) a_n = A.val[ab + G + lane]; }
-    int bb = __shfl_sync(mask, bb_l, 0, G), be = __shfl_sync(mask, be_l, 0, G);
+    int bb = __shfl_sync(FULL, bb_l, 0, G), be = __shfl_sync(FULL, be_l, 0, G);
     int c_cur = -1;
     double v_cur = 0.0;
     if (bb + lane < be) { c_cur = B.col[bb + lane]; if (NUMERIC) v_cur = B.val[bb + lane]; }
-    for (int base = ab; base < ae; base += G) {
+    const int max_chunks = __reduce_max_sync(FULL, (ae - ab + G - 1) / G);
+    for (int c = 0; c < max_chunks; ++c) {
+      const int base = ab + c * G;   // >= ae once this group is done
       int bb_n = 0, be_n = 0, k_nn = 0;
       double a_nn = 0.0;
       if (base + G + lane < ae) { bb_n = B.ptr[k_n]; be_n = B.ptr[k_n + 1]; }
       if (base + 2 * G + lane < ae) { k_nn = A.col[base + 2 * G + lane]; if (NUMERIC) a_nn = A.val[base + 2 * G + lane]; }
-      const int nstep = min(G, ae - base);
-      for (int t = 0; t < nstep; ++t) {
-        const double a = NUMERIC ? __shfl_sync(mask, a_l, t, G) : 0.0;
-        int bbn = 0, ben = 0, c_nxt = -1;
+      const int nstep = max(0, min(G, ae - base));
+      const int tmax = __reduce_max_sync(FULL, nstep);
+      for (int t = 0; t < tmax; ++t) {
+        const double a = NUMERIC ? __shfl_sync(FULL, a_l, t, G) : 0.0;
+        int bbn = __shfl_sync(FULL, bb_l, (t + 1) & (G - 1), G), ben = __shfl_sync(FULL, be_l, (t + 1) & (G - 1), G);
+        if (t + 1 >= nstep) { bbn = 0; ben = 0; }
+        if (t == tmax - 1) {   // warp-uniform: the first B row of the next chunk
+          const int xb = __shfl_sync(FULL, bb_n, 0, G), xe = __shfl_sync(FULL, be_n, 0, G);
+          if (t + 1 >= nstep && base + G < ae) { bbn = xb; ben = xe; }
+        }
+        int c_nxt = -1;
         double v_nxt = 0.0;
-        if (t + 1 < nstep) {
-          bbn = __shfl_sync(mask, bb_l, t + 1, G);
-          ben = __shfl_sync(mask, be_l, t + 1, G);
-        } else if (base + G < ae) {
-          bbn = __shfl_sync(mask, bb_n, 0, G);
-          ben = __shfl_sync(mask, be_n, 0, G);
-        }
         if (bbn + lane < ben) { c_nxt = B.col[bbn + lane]; if (NUMERIC) v_nxt = B.val[bbn + lane]; }
-        if (c_cur >= 0) {
-          bool isnew;
-          int slot = hash_insert(keys, H, c_cur, isnew);
-          if (NUMERIC) vals[slot] = __dadd_rn(vals[slot], __dmul_rn(a, v_cur));
-          else mine += isnew ? 1 : 0;
+        if (t < nstep) {
+          if (c_cur >= 0) {
+            bool isnew;
+            int slot = hash_insert(keys, H, c_cur, isnew);
+            if (NUMERIC) vals[slot] = __dadd_rn(vals[slot], __dmul_rn(a, v_cur));
+            else mine += isnew ? 1 : 0;
+          }
+          for (int kb = bb + G + lane; kb < be; kb += G) {  // B rows longer than the group
+            bool isnew;
+            int slot = hash_insert(keys, H, B.col[kb], isnew);
+            if (NUMERIC) vals[slot] = __dadd_rn(vals[slot], __dmul_rn(a, B.val[kb]));
+            else mine += isnew ? 1 : 0;
+          }
         }
-        for (int kb = bb + G + lane; kb < be; kb += G) {  // B rows longer than the group
-          bool isnew;
-          int slot = hash_insert(keys, H, B.col[kb], isnew);
-          if (NUMERIC) vals[slot] = __dadd_rn(vals[slot], __dmul_rn(a, B.val[kb]));
-          else mine += isnew ? 1 : 0;
-        }
-        if (NUMERIC) __syncwarp(mask);
+        if (NUMERIC) __syncwarp(FULL);
         bb = bbn; be = ben; c_cur = c_nxt; v_cur = v_nxt;
       }
       a_l = a_n; bb_l = bb_n; be_l = be_n; k_n = k_nn; a_n = a_nn;
@@ -226,7 +232,7 @@ __device__ __forceinline__ void spgemm_row(const rows::Csr &A, const rows::Csr &
     if (G <= 32) {
 #pragma unroll
       for (int o = G >> 1; o > 0; o >>= 1) mine += __shfl_down_sync(mask, mine, o, G);
-      if (lane == 0) nnz_out[row] = mine;
+      if (lane == 0 && row >= 0) nnz_out[row] = mine;
     } else {
       if (mine) atomicAdd(cnt, mine);
       __syncthreads();
@@ -235,7 +241,7 @@ __device__ __forceinline__ void spgemm_row(const rows::Csr &A, const rows::Csr &
     }
     return;
   } else {
-  const int base = Cptr[row];
+  const int base = row >= 0 ? Cptr[row] : 0;
   if (!sorted) {
     // intermediate product (Q = A P): the consumer R * Q accumulates over the entries of R's rows, at most one term per
     // Q row for any output entry, so the order inside a Q row is irrelevant and the row is written as it is compacted
@@ -297,11 +303,10 @@ __global__ void k_spgemm_smem(rows::Csr A, rows::Csr B, const int *row_list, int
   double *lv = vals + (NUMERIC ? H : 0);
   int *keys = (int *)(base + 8 + (NUMERIC ? (size_t)H * (list ? 12 : 8) : 0));
   int *lk = keys + H;
-  unsigned mask = 0xffffffffu;
-  if constexpr (G < 32) mask = ((1u << G) - 1u) << ((threadIdx.x & 31) / G * G);
+  const unsigned mask = 0xffffffffu;   // G <= 32: all groups of a warp move together (see spgemm_row)
   int idx = blockIdx.x * groups + g;
-  if (idx >= nrows) return;  // G > 32: groups == 1, uniform for the whole block
-  int row = row_list[idx];
+  if (G > 32 && idx >= nrows) return;  // groups == 1, uniform for the whole block
+  int row = idx < nrows ? row_list[idx] : -1;
   spgemm_row<G, NUMERIC>(A, B, row, lane, mask, keys, vals, H, cnt, lk, lv, Cptr, Ccol, Cval, nnz_out, diag_first ? row : -2, sorted != 0);
 }
 
