@@ -198,38 +198,38 @@ __device__ __forceinline__ unsigned grp_mask() {
 }
 template <int G>
 __global__ void k_split_count(int n, const int *mptr, const int *mcol, int n_own, int *dcnt, int *ocnt, int *used) {
+  // collectives name the full warp (groups beyond the last row run predicated off): a per-group mask is serialised
   const int i = (blockIdx.x * blockDim.x + threadIdx.x) / G, lane = threadIdx.x % G;
-  if (i > n) return;
-  if (i == n) { if (lane == 0) { dcnt[i] = 0; ocnt[i] = 0; } return; }
-  const unsigned gm = grp_mask<G>();
   int d = 0, o = 0;
-  for (int k = mptr[i] + lane; k < mptr[i + 1]; k += G) {
-    int c = mcol[k];
-    if (c < n_own) ++d;
-    else { ++o; used[c - n_own] = 1; }
-  }
+  if (i < n)
+    for (int k = mptr[i] + lane; k < mptr[i + 1]; k += G) {
+      int c = mcol[k];
+      if (c < n_own) ++d;
+      else { ++o; used[c - n_own] = 1; }
+    }
 #pragma unroll
-  for (int off = G >> 1; off > 0; off >>= 1) { d += __shfl_xor_sync(gm, d, off, G); o += __shfl_xor_sync(gm, o, off, G); }
-  if (lane == 0) { dcnt[i] = d; ocnt[i] = o; }
+  for (int off = G >> 1; off > 0; off >>= 1) { d += __shfl_xor_sync(0xffffffffu, d, off, G); o += __shfl_xor_sync(0xffffffffu, o, off, G); }
+  if (lane == 0 && i <= n) { dcnt[i] = d; ocnt[i] = o; }   // i == n: the terminating zero of the count arrays
 }
 // order-preserving split: positions inside the two output rows come from ballot prefixes over each chunk of G entries
 template <int G>
 __global__ void k_split_fill2(int n, const int *mptr, const int *mcol, const double *mval, int n_own, const int *newidx,
                               const int *dptr, int *dcol, double *dval, const int *optr, int *ocol, double *oval) {
   const int i = (blockIdx.x * blockDim.x + threadIdx.x) / G, lane = threadIdx.x % G;
-  if (i >= n) return;
-  const unsigned gm = grp_mask<G>();
+  const bool act = i < n;
+  const unsigned gbits = (G >= 32) ? 0xffffffffu : ((1u << (G & 31)) - 1u);
   const int first = (threadIdx.x & 31) - lane;
   const unsigned lt = (1u << lane) - 1u;
-  int wd = dptr[i], wo = optr[i];
-  const int b = mptr[i], e = mptr[i + 1];
-  for (int base = b; base < e; base += G) {
-    const int k = base + lane;
+  int wd = act ? dptr[i] : 0, wo = act ? optr[i] : 0;
+  const int b = act ? mptr[i] : 0, e = act ? mptr[i + 1] : 0;
+  const int longest = __reduce_max_sync(0xffffffffu, e - b);   // chunk loop uniform over the warp, full-warp ballots
+  for (int off = 0; off < longest; off += G) {
+    const int k = b + off + lane;
     int c = 0;
     bool valid = k < e, isd = false;
     if (valid) { c = mcol[k]; isd = c < n_own; }
-    const unsigned bd = (__ballot_sync(gm, valid && isd) & gm) >> first;
-    const unsigned bo = (__ballot_sync(gm, valid && !isd) & gm) >> first;
+    const unsigned bd = (__ballot_sync(0xffffffffu, valid && isd) >> first) & gbits;
+    const unsigned bo = (__ballot_sync(0xffffffffu, valid && !isd) >> first) & gbits;
     if (valid) {
       if (isd) { int w = wd + __popc(bd & lt); dcol[w] = c; dval[w] = mval[k]; }
       else { int w = wo + __popc(bo & lt); ocol[w] = newidx[c - n_own]; oval[w] = mval[k]; }

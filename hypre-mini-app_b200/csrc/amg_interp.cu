@@ -22,6 +22,7 @@
 #include "amg.h"
 #include "amg_rows.cuh"
 #include <cub/cub.cuh>
+#include <cstdlib>
 
 namespace b200 {
 
@@ -488,7 +489,8 @@ void build_interp(const DCsr &Aext, const int *Sptr, const int *Scol, i64 S_nnz,
   P.nr = n_rows;
   P.ptr.alloc((size_t)n_rows + 1);
   if (n_rows == 0) { P.nnz = 0; P.ptr.zero(); return; }
-  const bool small_tier = (double)S_nnz <= 8.0 * (double)Aext.nr;
+  bool small_tier = (double)S_nnz <= 8.0 * (double)Aext.nr;
+  if (const char *e = getenv("B200_INTERP_SMALL_TIER")) small_tier = small_tier && atoi(e) != 0;   // benchmarking override
   const bool single = pmax > 0;
   DVec<signed char> Scf((size_t)std::max<i64>(S_nnz, 1));
   if (S_nnz > 0) {

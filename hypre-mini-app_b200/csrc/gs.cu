@@ -120,27 +120,34 @@ __global__ void __launch_bounds__(GS_THREADS) k_gs_sweep(int n, CsrView D, CsrVi
   const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gthreads = gridDim.x * blockDim.x;
   for (int i = gtid; i < n; i += gthreads)
     if (!mask[i]) uout[i] = uin[i];          // rows outside the set keep their value (never read from uout)
-  const int lane = threadIdx.x % G, grp = gtid / G, ngrp = gthreads / G;
-  unsigned gm = 0xffffffffu;
-  if (G < 32) gm = ((1u << (G & 31)) - 1u) << ((threadIdx.x & 31) / G * G);
+  // the row loop is uniform over the warp (its groups take consecutive rows, the tail predicated off), so the reduction
+  // shuffles name the full warp; a per-group mask would be serialised over the groups by the compiler
+  const int lane = threadIdx.x % G, ngrp = gthreads / G;
+  const int wgrp0 = (gtid - (int)(threadIdx.x & 31)) / G, gin = (threadIdx.x & 31) / G;
   unsigned long long epoch = 0;
   for (int l = 0; l < depth; ++l) {
     const int lb = lvl_off[l], le = lvl_off[l + 1];
-    for (int idx = lb + grp; idx < le; idx += ngrp) {
-      const int i = order[idx];
-      const int b = D.ptr[i], e = D.ptr[i + 1];
+    for (int idx0 = lb + wgrp0; idx0 < le; idx0 += ngrp) {
+      const int idx = idx0 + gin;
+      const bool act = idx < le;
+      int i = 0, b = 0;
       double sum = 0.0;
-      for (int q = (L1 ? b : b + 1) + lane; q < e; q += G) {
-        const int c = D.col[q];
-        const bool done = mask[c] && (dir == 0 ? c < i : c > i);
-        const double v = done ? __ldcg(uout + c) : uin[c];
-        sum += D.val[q] * v;
+      if (act) {
+        i = order[idx];
+        b = D.ptr[i];
+        const int e = D.ptr[i + 1];
+        for (int q = (L1 ? b : b + 1) + lane; q < e; q += G) {
+          const int c = D.col[q];
+          const bool done = mask[c] && (dir == 0 ? c < i : c > i);
+          const double v = done ? __ldcg(uout + c) : uin[c];
+          sum += D.val[q] * v;
+        }
+        if (O.ptr != nullptr)
+          for (int q = O.ptr[i] + lane; q < O.ptr[i + 1]; q += G) sum += O.val[q] * __ldcg(halo + O.col[q]);
       }
-      if (O.ptr != nullptr)
-        for (int q = O.ptr[i] + lane; q < O.ptr[i + 1]; q += G) sum += O.val[q] * __ldcg(halo + O.col[q]);
 #pragma unroll
-      for (int o = G >> 1; o > 0; o >>= 1) sum += __shfl_xor_sync(gm, sum, o, G);
-      if (lane == 0) {
+      for (int o = G >> 1; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o, G);
+      if (act && lane == 0) {
         const double res = f[i] - sum;
         uout[i] = L1 ? uin[i] + res / dsm[i] : res / D.val[b];
       }
