@@ -79,9 +79,9 @@ __device__ __forceinline__ bool hash_insert_capped(int *keys, int H, int c, bool
 }
 
 // Rows whose product-count bound is far above their true length (R * Q on the coarser levels: bound ~ 2000, length ~ 70)
-// are first counted by one warp in a 1024-slot table; a row whose table fills up (an insertion gives up) is marked -1 and
+// are first counted by one warp in a 256- or 1024-slot table; a row whose table fills up (an insertion gives up) is marked -1 and
 // counted again by the exact tier for its bound.  A count that completes is exact, whatever the load of the table.
-constexpr int H_TRY = 1024;
+template <int H_TRY>
 __global__ void __launch_bounds__(256) k_spgemm_count_try(rows::Csr A, rows::Csr B, const int *row_list, int nrows, int *nnz_out) {
   __shared__ int s_keys[8][H_TRY];
   const int g = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -525,16 +525,23 @@ void csr_spgemm(const DCsr &A, const DCsr &B, DCsr &C, bool diag_first, bool sor
     Bins bins;
     BinLimits L{{16, 32, 64, 128, 512, 2048, 16384}};
     make_bins(A.nr, bound.p, L, bins);
-    // bins 5, 6 and the global-memory bin (bound > 512): optimistic warp-per-row count first, exact tier for the failures
+    // optimistic warp-per-row count first, exact tier for the failures: bin 4 (128 < bound <= 512) in a 256-slot table,
+    // bins 5, 6 and the global-memory bin (bound > 512) in a 1024-slot table
     const int first_big = 5;
-    const int n_big = A.nr > 0 ? (bins.offset[NB] + bins.count[NB]) - bins.offset[first_big] : 0;
+    const int n_mid = bins.count[4];
+    const int n_big = (bins.offset[NB] + bins.count[NB]) - bins.offset[first_big];
+    if (n_mid > 0) {
+      k_spgemm_count_try<256><<<div_up(n_mid, 8), 256, 0, stream()>>>(rv(A), rv(B), bins.list.p + bins.offset[4], n_mid, nnz_row.p);
+      count_launch();
+      bins.count[4] = 0;
+    }
     if (n_big > 0) {
-      k_spgemm_count_try<<<div_up(n_big, 8), 256, 0, stream()>>>(rv(A), rv(B), bins.list.p + bins.offset[first_big], n_big, nnz_row.p);
+      k_spgemm_count_try<1024><<<div_up(n_big, 8), 256, 0, stream()>>>(rv(A), rv(B), bins.list.p + bins.offset[first_big], n_big, nnz_row.p);
       count_launch();
       for (int k = first_big; k <= NB; ++k) bins.count[k] = 0;
     }
     spgemm_pass<false>(A, B, bins, L, nullptr, nullptr, nullptr, nnz_row.p, diag_first, sorted);
-    if (n_big > 0) {
+    if (n_mid + n_big > 0) {
       DVec<int> retry((size_t)A.nr);
       k_retry_size<<<div_up(A.nr, 256), 256, 0, stream()>>>(A.nr, nnz_row.p, bound.p, retry.p);
       count_launch();
