@@ -10,6 +10,7 @@
 //   * ILU: only the default combination (ilu_type 0, fill 0, local_reordering 0, trisolve 1 = block-Jacobi ILU(0)) is built;
 //     other values are passed on and rejected by HYPRE_ILUSetup.
 #include "HypreSystem.h"
+#include "mm_text.h"
 
 #include <algorithm>
 #include <chrono>
@@ -570,119 +571,7 @@ void HypreSystem::hypre_vector_set_values(HYPRE_IJVector &v, int component) {
 // Loaders.  File grammars: SURVEY.md App. C (MatrixMarket coordinate / array, HYPRE-IJ text).  Every rank scans the whole
 // file and keeps the entries of its own block rows, as the reference does (HypreSystem.cpp:1804, :1219-1221).
 // =====================================================================================================================
-}  // namespace nalu
-
-#include <fcntl.h>
-#include <sys/mman.h>
-#include <sys/stat.h>
-#include <unistd.h>
-
-namespace nalu {
-
-namespace {
-
-// read-only memory map of a text file with a line cursor
-class TextFile {
- public:
-  explicit TextFile(const std::string &path, const char *what) : path_(path) {
-    fd_ = open(path.c_str(), O_RDONLY);
-    if (fd_ < 0) throw std::runtime_error(std::string("Cannot open ") + what + " file: " + path);
-    struct stat st;
-    if (fstat(fd_, &st) != 0) { close(fd_); throw std::runtime_error("Cannot stat " + path); }
-    size_ = (size_t)st.st_size;
-    if (size_) {
-      void *p = mmap(nullptr, size_, PROT_READ, MAP_PRIVATE, fd_, 0);
-      if (p == MAP_FAILED) { close(fd_); throw std::runtime_error("Cannot map " + path); }
-      data_ = (const char *)p;
-    }
-  }
-  ~TextFile() {
-    if (data_) munmap((void *)data_, size_);
-    if (fd_ >= 0) close(fd_);
-  }
-  // next line as [b, e) without the terminator; false at end of file
-  bool next(const char *&b, const char *&e) {
-    if (pos_ >= size_) return false;
-    b = data_ + pos_;
-    const char *nl = (const char *)memchr(b, '\n', size_ - pos_);
-    e = nl ? nl : data_ + size_;
-    pos_ = (size_t)(e - data_) + (nl ? 1 : 0);
-    if (e > b && e[-1] == '\r') --e;
-    return true;
-  }
-  const std::string &path() const { return path_; }
-
- private:
-  std::string path_;
-  int fd_ = -1;
-  size_t size_ = 0, pos_ = 0;
-  const char *data_ = nullptr;
-};
-
-inline bool blank(const char *b, const char *e) {
-  for (; b < e; ++b) if (*b != ' ' && *b != '\t') return false;
-  return true;
-}
-// numbers are parsed from a bounded copy of the line (the mapping is not NUL-terminated)
-struct LineParser {
-  char buf[512];
-  char *cur = nullptr;
-  void set(const char *b, const char *e) {
-    size_t n = std::min<size_t>((size_t)(e - b), sizeof(buf) - 1);
-    memcpy(buf, b, n);
-    buf[n] = 0;
-    cur = buf;
-  }
-  bool integer(long long &v) {
-    char *end;
-    v = strtoll(cur, &end, 10);
-    if (end == cur) return false;
-    cur = end;
-    return true;
-  }
-  bool real(double &v) {
-    char *end;
-    v = strtod(cur, &end);
-    if (end == cur) return false;
-    cur = end;
-    return true;
-  }
-};
-
-struct MMBanner { bool coordinate = false, array = false, complex_field = false, pattern = false; };
-// "%%MatrixMarket matrix <coordinate|array> <real|double|integer|complex|pattern> <general|symmetric|...>"
-MMBanner read_mm_banner(TextFile &f, const char *what) {
-  const char *b, *e;
-  if (!f.next(b, e)) throw std::runtime_error(std::string("Cannot read ") + what + " banner");
-  std::string line(b, e), tok[5];
-  std::stringstream ss(line);
-  for (auto &t : tok) ss >> t;
-  for (auto &t : tok) std::transform(t.begin(), t.end(), t.begin(), ::tolower);
-  if (tok[0] != "%%matrixmarket") throw std::runtime_error(std::string("Cannot read ") + what + " banner");
-  MMBanner m;
-  m.coordinate = tok[2] == "coordinate";
-  m.array = tok[2] == "array";
-  m.complex_field = tok[3] == "complex";
-  m.pattern = tok[3] == "pattern";
-  bool field_ok = tok[3] == "real" || tok[3] == "double" || tok[3] == "integer" || m.complex_field || m.pattern;
-  bool sym_ok = tok[4] == "general" || tok[4] == "symmetric" || tok[4] == "skew-symmetric" || tok[4] == "hermitian";
-  if (tok[1] != "matrix" || !(m.coordinate || m.array) || !field_ok || !sym_ok || (m.array && m.pattern))
-    throw std::runtime_error("Invalid matrix market file encountered");
-  return m;
-}
-// first non-comment, non-blank line after the banner
-void read_size_line(TextFile &f, LineParser &lp) {
-  const char *b, *e;
-  while (f.next(b, e)) {
-    if (b < e && *b == '%') continue;
-    if (blank(b, e)) continue;
-    lp.set(b, e);
-    return;
-  }
-  throw std::runtime_error("Cannot read sizes in file: " + f.path());
-}
-
-}  // namespace
+using namespace mmtext;
 
 void HypreSystem::read_common_linsys_keys(std::vector<std::string> &rhsfile, std::vector<std::string> &slnfile) {
   YAML::Node linsys = inpfile_["linear_system"];

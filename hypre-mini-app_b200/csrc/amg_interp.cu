@@ -28,6 +28,8 @@ namespace b200 {
 
 namespace {
 
+#include "amg_interp_flat.cuh"
+
 template <int G>
 __device__ __forceinline__ unsigned group_mask() {
   if (G >= 32) return 0xffffffffu;
@@ -443,15 +445,53 @@ __global__ void k_compact_p(int n_rows, int pmax, const int *__restrict__ lraw, 
   for (int k = 0; k < n; ++k) { Pcol[b + k] = tcol[src + k]; Pval[b + k] = tval[src + k]; }
 }
 
+bool use_v1() {
+  static int v = -1;
+  if (v < 0) { const char *e = getenv("B200_INTERP_V1"); v = (e && atoi(e) != 0) ? 1 : 0; }
+  return v == 1;
+}
+
+// tiers: (G, H, CAP, STG) = (8, 64, 32, 64) when strength rows are short, then (32, 256, 128, 192)
+template <int G, int H, int CAP, int STG, int MODE>
+void launch_flat(int grid_rows, const rows::Csr &A, const int *Sptr, const int *Scol, const signed char *Scf, const int *cf, const int *f2c,
+                 int n_own, int n_rows, double tf, int pmax, int lo, int *lraw, int *len, const int *Pptr, int *Pcol, double *Pval,
+                 const int *list) {
+  auto kern = flat::k_interp_flat<G, H, CAP, STG, MODE>;
+  constexpr size_t smem = sizeof(flat::Grp<G, H, CAP, STG>) * (256 / G);
+  static bool attr_set = false;   // per instantiation
+  if (!attr_set) {
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set = true;
+  }
+  kern<<<div_up(grid_rows, 256 / G), 256, smem, stream()>>>(A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw, len, Pptr, Pcol,
+                                                          Pval, list);
+  count_launch();
+}
+template <int MODE, bool SMALL>
+void launch_one(int grid_rows, const rows::Csr &A, const int *Sptr, const int *Scol, const signed char *Scf, const int *cf, const int *f2c,
+                int n_own, int n_rows, double tf, int pmax, int lo, int *lraw, int *len, const int *Pptr, int *Pcol, double *Pval,
+                const int *list) {
+  if (use_v1()) {
+    if (SMALL)
+      k_interp_grp<8, 64, 32, MODE><<<div_up(grid_rows, 32), 256, 0, stream()>>>(A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw,
+                                                                               len, Pptr, Pcol, Pval, list);
+    else
+      k_interp_grp<32, 256, 128, MODE><<<div_up(grid_rows, 8), 256, 0, stream()>>>(A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw,
+                                                                                 len, Pptr, Pcol, Pval, list);
+    count_launch();
+    return;
+  }
+  if (SMALL) launch_flat<8, 64, 32, 64, MODE>(grid_rows, A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw, len, Pptr, Pcol, Pval, list);
+  else launch_flat<32, 256, 128, 192, MODE>(grid_rows, A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw, len, Pptr, Pcol, Pval, list);
+}
+
 template <int MODE>
 void launch_tiers(bool small_tier, const rows::Csr &A, const int *Sptr, const int *Scol, const signed char *Scf, const int *cf,
                   const int *f2c, int n_own, int n_rows, double tf, int pmax, int *lraw, int *len, const int *Pptr, int *Pcol,
                   double *Pval) {
   int lo = -1;
   if (small_tier) {
-    k_interp_grp<8, 64, 32, MODE><<<div_up(n_rows, 32), 256, 0, stream()>>>(A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo,
-                                                                          lraw, len, Pptr, Pcol, Pval, nullptr);
-    count_launch();
+    launch_one<MODE, true>(n_rows, A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw, len, Pptr, Pcol, Pval, nullptr);
     lo = 32;
     if (MODE != 1) {
       // the rows the small tier could not hold are few (often none): run the large tier on their list only
@@ -463,17 +503,13 @@ void launch_tiers(bool small_tier, const rows::Csr &A, const int *Sptr, const in
       const int left = fetch1(cnt.p);
       if (left == 0) return;
       if (left <= CAP) {
-        k_interp_grp<32, 256, 128, MODE><<<div_up(left, 8), 256, 0, stream()>>>(A, Sptr, Scol, Scf, cf, f2c, n_own, left, tf, pmax, lo, lraw,
-                                                                               len, Pptr, Pcol, Pval, list.p);
-        count_launch();
+        launch_one<MODE, false>(left, A, Sptr, Scol, Scf, cf, f2c, n_own, left, tf, pmax, lo, lraw, len, Pptr, Pcol, Pval, list.p);
         B200_KERNEL_CHECK();
         return;
       }
     }
   }
-  k_interp_grp<32, 256, 128, MODE><<<div_up(n_rows, 8), 256, 0, stream()>>>(A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo,
-                                                                           lraw, len, Pptr, Pcol, Pval, nullptr);
-  count_launch();
+  launch_one<MODE, false>(n_rows, A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw, len, Pptr, Pcol, Pval, nullptr);
   B200_KERNEL_CHECK();
 }
 

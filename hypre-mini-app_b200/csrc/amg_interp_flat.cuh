@@ -1,0 +1,455 @@
+// amg_interp_flat.cuh -- extended+i interpolation rows, "flattened item" formulation (included by amg_interp.cu only).
+// Same contract as rows::interp_row (amg_rows.cuh): bit-identical C-hat order, weights and truncation.
+// Replaces hypre_BoomerAMGBuildExtPIInterp + hypre_BoomerAMGInterpTruncation reached from HYPRE_BoomerAMGSetup
+// (/root/reference/src/HypreSystem.cpp:197,212,232 options, :323 via :692 call).
+//
+// G lanes own one row; 256 / G rows per block.  What changed against the first kernel (profiles/r01_interp_sass_notes.md:
+// 6 078 warp instructions per row on level 1, control-flow bound):
+//   * no per-neighbour warp loop.  The work of one row is a list of ITEMS -- (strong neighbour t, entry s of its strength
+//     row) in the discovery, (distributed neighbour t, entry s of its matrix row) in the weights -- and the lanes take G
+//     consecutive items per round, so every round is a coalesced load + one hash probe at full lane occupancy;
+//   * the discovery order is the item order, so new C points take their list positions from a ballot prefix; an item that
+//     repeats inside one round is removed with match.any;
+//   * strong F neighbours of i are put into the same hash table with a MARK position: "is this entry of row i strong" is
+//     the probe the weights phase does anyway (the first kernel re-shuffled the whole strength row for every chunk);
+//   * contributions are staged neighbour-major; the denominator of a neighbour is summed in storage order by ONE lane per
+//     neighbour (all neighbours of the chunk at once, one division per lane instead of one per warp step);
+//   * every C-hat slot keeps a bit mask of the neighbours (tags) that contribute to it; a lane per slot then adds its
+//     terms in ascending tag order, which is the order of the sequential loop over the entries of row i;
+//   * the diagonal accumulates its at most one term per tag through a shuffle chain in tag order;
+//   * truncation (qsort2abs tie order, sequential by definition) runs after a block barrier with one LANE per row of the
+//     block in a single warp, instead of one lane of every group;
+//   * every collective names the full warp with width = G and every loop that contains one has a warp-uniform trip count
+//     (per-group masks make the compiler serialise collectives over the groups, profiles/r01_interp_sass_notes.md).
+#pragma once
+
+namespace flat {
+
+constexpr int MARK = 255;      // hash position of a strong F neighbour of i (not a C-hat slot)
+constexpr int DIAGSLOT = 254;  // staged contribution that goes to the diagonal (the neighbour's entry in column i)
+constexpr unsigned FULL = 0xffffffffu;
+
+template <int G, int H, int CAP, int STG>
+struct alignas(8) Grp {
+  double lv[CAP];
+  double stg_a[STG];
+  double tval[G];
+  int keys[H];
+  int lc[CAP];
+  unsigned smask[CAP];
+  int noff[G + 1];
+  int tb[G];
+  int tcnt[G];
+  int tseg[G];
+  int L, nout, row, flags;     // flags: 1 = any_off, 2 = F row with weights computed (truncate + write), 4 = write len only
+  unsigned char spos[H];
+  unsigned char stg_slot[STG];
+  unsigned char tkind[G];
+  unsigned char tneg[G];
+  int pad_odd;                 // keeps sizeof / 4 odd: lane = group accesses of the truncation warp spread over the banks
+};
+
+template <int H>
+__device__ __forceinline__ unsigned slot0(int key) {
+  return (((unsigned)key * 2654435761u) >> 7) & (unsigned)(H - 1);
+}
+// -1: absent; 0 .. CAP-1: C-hat position; MARK: strong F neighbour of i
+template <int H>
+__device__ __forceinline__ int probe(const int *keys, const unsigned char *spos, int key) {
+  unsigned h = slot0<H>(key);
+  while (true) {
+    const int k = keys[h];
+    if (k == key) return spos[h];
+    if (k == -1) return -1;
+    h = (h + 1) & (unsigned)(H - 1);
+  }
+}
+template <int H>
+__device__ __forceinline__ void insert(int *keys, unsigned char *spos, int key, int pos) {  // key is known to be absent
+  unsigned h = slot0<H>(key);
+  while (true) {
+    const int old = atomicCAS(keys + h, -1, key);
+    if (old == -1) { spos[h] = (unsigned char)pos; return; }
+    h = (h + 1) & (unsigned)(H - 1);
+  }
+}
+template <int H>
+__device__ __forceinline__ void set_pos(const int *keys, unsigned char *spos, int key, int pos) {  // key is present
+  unsigned h = slot0<H>(key);
+  while (keys[h] != key) h = (h + 1) & (unsigned)(H - 1);
+  spos[h] = (unsigned char)pos;
+}
+
+template <int G>
+__device__ __forceinline__ unsigned gballot(bool pred, int gbase) {
+  const unsigned b = __ballot_sync(FULL, pred);
+  if (G >= 32) return b;
+  return (b >> gbase) & ((1u << (G & 31)) - 1u);
+}
+// inclusive scan over the G lanes of a group (full-warp shuffle, width G)
+template <int G>
+__device__ __forceinline__ int gscan_incl(int v, int gl) {
+#pragma unroll
+  for (int d = 1; d < G; d <<= 1) {
+    const int u = __shfl_up_sync(FULL, v, d, G);
+    if (gl >= d) v += u;
+  }
+  return v;
+}
+
+// lraw / len / MODE / lo / row_list: as for the tier driver in amg_interp.cu (MODE 0 count, 1 fill at Pptr, 2 single pass at
+// i * pmax).  Scf[k] = cf[Scol[k]] as a signed char.
+template <int G, int H, int CAP, int STG, int MODE>
+__global__ void __launch_bounds__(256, 4)
+k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__ Scol, const signed char *__restrict__ Scf,
+              const int *__restrict__ cf, const int *__restrict__ f2c, int n_own, int n_rows, double tf, int pmax, int lo, int *lraw,
+              int *len, const int *__restrict__ Pptr, int *Pcol, double *Pval, const int *__restrict__ row_list) {
+  using GS = Grp<G, H, CAP, STG>;
+  static_assert(CAP <= 128 && G <= 32 && STG > CAP, "slot / tag encodings");
+  constexpr int GROUPS = 256 / G;
+  constexpr int HMAX = (H * 3) / 4;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  GS *all = reinterpret_cast<GS *>(smem_raw);
+  const int g = threadIdx.x / G, gl = threadIdx.x % G;
+  const int lane32 = threadIdx.x & 31;
+  const int gbase = lane32 - gl;
+  const unsigned ltm = (1u << gl) - 1u;
+  GS &S = all[g];
+  const int slot = blockIdx.x * GROUPS + g;
+  int i = -1;
+  if (slot < n_rows) i = row_list ? row_list[slot] : slot;
+
+  // ---- what is there to do for this row ---------------------------------------------------------------------------------
+  bool active = false;
+  if (i >= 0) {
+    bool todo;
+    if (MODE != 1) todo = (lraw[i] == -1);
+    else { const int l = lraw[i]; todo = (l > lo && l <= CAP); }
+    if (todo) {
+      const int cfi = cf[i];
+      if (cfi >= 0) {   // C point: identity row
+        if (gl == 0) {
+          if (MODE != 1) { lraw[i] = 0; len[i] = 1; }
+          if (MODE != 0) { const size_t b = (MODE == 1) ? (size_t)Pptr[i] : (size_t)i * pmax; Pcol[b] = f2c[i]; Pval[b] = 1.0; }
+        }
+      } else if (cfi == -3) {
+        if (MODE != 1 && gl == 0) { lraw[i] = 0; len[i] = 0; }
+      } else if (MODE == 1 && Pptr[i + 1] == Pptr[i]) {
+      } else active = true;
+    }
+  }
+  for (int s = gl; s < H; s += G) S.keys[s] = -1;
+  if (gl == 0) { S.L = 0; S.nout = 0; S.row = i; S.flags = 0; }
+  __syncwarp(FULL);
+
+  // ---- discovery of C-hat_i: items in sequence order ---------------------------------------------------------------------
+  int L = 0, nmark = 0;
+  bool ovf = false, any_off = false;
+  {
+    const int sb = active ? Sptr[i] : 0, se = active ? Sptr[i + 1] : 0;
+    const int nchunk = __reduce_max_sync(FULL, (se - sb + G - 1) / G);
+    for (int c = 0; c < nchunk; ++c) {
+      const int kk = sb + c * G + gl;
+      const bool valid = (kk < se) && !ovf;
+      int i1 = -1, c1 = -3;
+      if (valid) { i1 = Scol[kk]; c1 = Scf[kk]; }
+      const bool isC = valid && c1 >= 0;
+      const bool isF = valid && c1 < 0 && c1 != -3;
+      int b2 = 0, n_t = 0;
+      if (isC) { b2 = ~i1; n_t = 1; }                                 // the item is the neighbour itself
+      else if (isF) { b2 = Sptr[i1]; n_t = Sptr[i1 + 1] - b2; }       // the items are its strength row
+      const unsigned fmk = gballot<G>(isF, gbase);
+      if (L + nmark + __popc(fmk) > HMAX) ovf = true;
+      if (isF && !ovf) insert<H>(S.keys, S.spos, i1, MARK);
+      nmark += __popc(fmk);
+      const int incl = gscan_incl<G>(ovf ? 0 : n_t, gl);
+      const int T = __shfl_sync(FULL, incl, G - 1, G);
+      S.noff[gl] = incl - (ovf ? 0 : n_t);
+      if (gl == G - 1) S.noff[G] = T;
+      S.tb[gl] = b2;
+      __syncwarp(FULL);
+      const int Tmax = __reduce_max_sync(FULL, T);
+      int tp = 0;
+      for (int base = 0; base < Tmax; base += G) {
+        const int item = base + gl;
+        int key = -1;
+        bool cand = false;
+        if (item < T && !ovf) {
+          while (item >= S.noff[tp + 1]) ++tp;
+          const int bb = S.tb[tp];
+          if (bb < 0) { key = ~bb; cand = true; }
+          else { const int idx = bb + (item - S.noff[tp]); key = Scol[idx]; cand = Scf[idx] >= 0; }
+        }
+        const bool nw = cand && (probe<H>(S.keys, S.spos, key) < 0);
+        const unsigned long long mkey = nw ? (((unsigned long long)(unsigned)g << 32) | (unsigned)key)
+                                           : (0xffffffff00000000ull | (unsigned)lane32);
+        const unsigned same = __match_any_sync(FULL, mkey);
+        const bool first = nw && ((__ffs(same) - 1) == lane32);
+        const unsigned nm = gballot<G>(first, gbase);
+        const unsigned offm = gballot<G>(first && key >= n_own, gbase);
+        const int cnt = __popc(nm);
+        if (cnt) {
+          if (L + cnt > CAP || L + cnt + nmark > HMAX) ovf = true;
+          else {
+            if (first) {
+              const int pos = L + __popc(nm & ltm);
+              insert<H>(S.keys, S.spos, key, pos);
+              S.lc[pos] = key;
+            }
+            any_off |= (offm != 0u);
+            L += cnt;
+          }
+        }
+        __syncwarp(FULL);
+      }
+      __syncwarp(FULL);
+    }
+  }
+  if (ovf) active = false;   // lraw stays -1: the next tier takes the row
+  const bool full = (MODE != 0) || tf != 0.0;
+  if (!full) {   // uniform over the grid
+    if (active && gl == 0) { lraw[i] = L; len[i] = (pmax > 0 && L > pmax) ? pmax : L; }
+    return;
+  }
+
+  // ---- own-range C points first (P_diag before P_offd), stable: positions change, the table follows ---------------------
+  if (__any_sync(FULL, active && any_off)) {
+    const bool act = active && any_off;
+    int *tmp = reinterpret_cast<int *>(S.smask);
+    const int Lmax = __reduce_max_sync(FULL, act ? L : 0);
+    int nown = 0;
+    for (int base = 0; base < Lmax; base += G) {
+      const int k = base + gl;
+      const bool own = act && (k < L) && (S.lc[k] < n_own);
+      nown += __popc(gballot<G>(own, gbase));
+    }
+    int co = 0, cx = 0;
+    for (int base = 0; base < Lmax; base += G) {
+      const int k = base + gl;
+      const bool valid = act && k < L;
+      const int v = valid ? S.lc[k] : 0;
+      const bool own = valid && v < n_own, off = valid && !own;
+      const unsigned mo = gballot<G>(own, gbase), mx = gballot<G>(off, gbase);
+      if (valid) {
+        const int np = own ? (co + __popc(mo & ltm)) : (nown + cx + __popc(mx & ltm));
+        tmp[np] = v;
+        set_pos<H>(S.keys, S.spos, v, np);
+      }
+      co += __popc(mo);
+      cx += __popc(mx);
+    }
+    __syncwarp(FULL);
+    if (act)
+      for (int k = gl; k < L; k += G) S.lc[k] = tmp[k];
+    __syncwarp(FULL);
+  }
+
+  // ---- weights ------------------------------------------------------------------------------------------------------------
+  for (int k = gl; k < CAP; k += G) S.lv[k] = 0.0;
+  const int ab = active ? A.ptr[i] : 0, ae = active ? A.ptr[i + 1] : 0;
+  double diagonal = active ? A.val[ab] : 1.0;
+  const int na = active ? (ae - ab - 1) : 0;
+  const int nchunkA = __reduce_max_sync(FULL, (na + G - 1) / G);
+  __syncwarp(FULL);
+  for (int c = 0; c < nchunkA; ++c) {
+    // one entry of row i per lane (tag = lane): classification
+    const int jj = ab + 1 + c * G + gl;
+    const bool valid = active && jj < ae;
+    int kind = 3, pr = -1, b1 = 0, n_t = 0;
+    bool neg = false;
+    double aij = 0.0;
+    if (valid) {
+      const int i1 = A.col[jj];
+      aij = A.val[jj];
+      pr = probe<H>(S.keys, S.spos, i1);
+      if (pr >= 0 && pr != MARK) kind = 0;                    // direct: a_ij goes to its own C point
+      else if (pr == MARK) {                                   // strong F neighbour: distributed over C-hat and i
+        kind = 1;
+        b1 = A.ptr[i1];
+        n_t = A.ptr[i1 + 1] - b1 - 1;
+        neg = A.val[b1] < 0;
+      } else if (cf[i1] != -3) kind = 2;                       // lumped into the diagonal
+    }
+    const int ntag = active ? max(0, min(G, na - c * G)) : 0;
+    S.tb[gl] = b1 + 1;
+    S.tneg[gl] = neg ? 1 : 0;
+    S.tkind[gl] = (unsigned char)kind;
+    int lo_t = 0, rlen = G;   // tag range of the current attempt: [lo_t, lo_t + rlen)
+    while (__any_sync(FULL, active && lo_t < ntag)) {
+      const bool run = active && lo_t < ntag;
+      const bool in = run && gl >= lo_t && gl < lo_t + rlen && gl < ntag;
+      const int n_in = (in && kind == 1) ? n_t : 0;
+      const int incl = gscan_incl<G>(n_in, gl);
+      const int T = __shfl_sync(FULL, incl, G - 1, G);
+      S.noff[gl] = incl - n_in;
+      if (gl == G - 1) S.noff[G] = T;
+      S.tcnt[gl] = 0;
+      for (int k = gl; k < L; k += G) S.smask[k] = 0u;
+      __syncwarp(FULL);
+      if (in && kind == 0) atomicOr(&S.smask[pr], 1u << gl);
+      // walk: G consecutive items per round
+      const int Tmax = __reduce_max_sync(FULL, T);
+      int nstg = 0, tp = 0;
+      bool sovf = false;
+      for (int base = 0; base < Tmax; base += G) {
+        const int item = base + gl;
+        bool contrib = false;
+        int sl = 0;
+        double a = 0.0;
+        if (item < T) {
+          while (item >= S.noff[tp + 1]) ++tp;
+          const int j1 = S.tb[tp] + (item - S.noff[tp]);
+          const int i2 = A.col[j1];
+          a = A.val[j1];
+          const bool ok = S.tneg[tp] ? (a > 0) : (a < 0);
+          if (ok) {
+            if (i2 == i) { contrib = true; sl = DIAGSLOT; }
+            else {
+              const int p2 = probe<H>(S.keys, S.spos, i2);
+              if (p2 >= 0 && p2 != MARK) { contrib = true; sl = p2; }
+            }
+          }
+        }
+        const unsigned cm = gballot<G>(contrib, gbase);
+        const int cn = __popc(cm);
+        if (nstg + cn > STG) sovf = true;
+        if (contrib && !sovf) {
+          const int e = nstg + __popc(cm & ltm);
+          S.stg_slot[e] = (unsigned char)sl;
+          S.stg_a[e] = a;
+          atomicAdd(&S.tcnt[tp], 1);
+          if (sl != DIAGSLOT) atomicOr(&S.smask[sl], 1u << tp);
+        }
+        nstg += cn;
+      }
+      __syncwarp(FULL);
+      // per tag: denominator in storage order, distribute factor, diagonal term
+      const bool commit = run && !sovf;
+      const int cnt_t = S.tcnt[gl];
+      const int seg = gscan_incl<G>(cnt_t, gl) - cnt_t;
+      double tv = 0.0, dterm = 0.0;
+      bool hasd = false;
+      if (commit && in) {
+        if (kind == 1) {
+          double sum = 0.0, ai = 0.0;
+          bool hasi = false;
+          for (int e = seg; e < seg + cnt_t; ++e) {
+            const double a = S.stg_a[e];
+            sum = sum + a;
+            if (S.stg_slot[e] == DIAGSLOT) { ai = a; hasi = true; }
+          }
+          if (sum != 0.0) {
+            tv = aij / sum;
+            if (hasi) { dterm = tv * ai; hasd = true; }
+          } else { dterm = aij; hasd = true; }
+        } else if (kind == 0) tv = aij;
+        else if (kind == 2) { dterm = aij; hasd = true; }
+      }
+      S.tval[gl] = tv;
+      S.tseg[gl] = seg;
+      __syncwarp(FULL);
+      // per C-hat slot: terms in ascending tag order
+      if (commit) {
+        for (int p = gl; p < L; p += G) {
+          unsigned m = S.smask[p];
+          double acc = S.lv[p];
+          while (m) {
+            const int t = __ffs(m) - 1;
+            m &= m - 1;
+            double term;
+            if (S.tkind[t] == 1) {
+              int e = S.tseg[t];
+              while (S.stg_slot[e] != p) ++e;
+              term = S.tval[t] * S.stg_a[e];
+            } else term = S.tval[t];
+            acc = acc + term;
+          }
+          S.lv[p] = acc;
+        }
+      }
+      // diagonal: at most one term per tag, in tag order
+      const unsigned hm = gballot<G>(hasd, gbase);
+      const unsigned hall = __reduce_or_sync(FULL, hm);
+      const int tend = hall ? (32 - __clz(hall)) : 0;
+      for (int t = 0; t < tend; ++t) {
+        const double d = __shfl_sync(FULL, dterm, t, G);
+        if ((hm >> t) & 1u) diagonal = diagonal + d;
+      }
+      if (run) {
+        if (!sovf) lo_t += rlen;
+        else if (rlen == 1) { active = false; ovf = true; }   // one neighbour alone exceeds the staging area: next tier
+        else rlen >>= 1;
+      }
+      __syncwarp(FULL);
+    }
+  }
+  if (active && diagonal != 0.0) {
+    const double md = -diagonal;
+    for (int k = gl; k < L; k += G) S.lv[k] = S.lv[k] / md;
+  }
+  if (gl == 0) { S.L = L; S.nout = L; S.flags = active ? (2 | (any_off ? 1 : 0)) : 0; }
+  __syncthreads();
+
+  // ---- truncation: sequential per row (the sums and hypre's qsort2abs are order dependent); lane = row of the block -------
+  if (threadIdx.x < GROUPS) {
+    GS &T = all[threadIdx.x];
+    if (T.flags & 2) {
+      int *lc = T.lc;
+      double *lv = T.lv;
+      int n_out = T.L;
+      if (tf > 0.0 && n_out > 0) {
+        double max_coef = 0.0, row_sum = 0.0, scale = 0.0;
+        for (int k = 0; k < n_out; ++k) { const double a = fabs(lv[k]); max_coef = (a > max_coef) ? a : max_coef; }
+        max_coef = max_coef * tf;
+        int w = 0;
+        for (int k = 0; k < n_out; ++k) {
+          row_sum = row_sum + lv[k];
+          if (fabs(lv[k]) >= max_coef) { scale = scale + lv[k]; lc[w] = lc[k]; lv[w] = lv[k]; ++w; }
+        }
+        n_out = w;
+        if (scale != 0.0 && scale != row_sum) {
+          const double f = row_sum / scale;
+          for (int k = 0; k < n_out; ++k) lv[k] = lv[k] * f;
+        }
+      }
+      if (pmax > 0 && n_out > pmax) {
+        double row_sum = 0.0, scale = 0.0;
+        for (int k = 0; k < n_out; ++k) row_sum = row_sum + lv[k];
+        rows::qsort2abs(lc, lv, n_out, pmax);
+        for (int k = 0; k < pmax; ++k) scale = scale + lv[k];
+        n_out = pmax;
+        if (scale != 0.0 && scale != row_sum) {
+          const double f = row_sum / scale;
+          for (int k = 0; k < n_out; ++k) lv[k] = lv[k] * f;
+        }
+        if (T.flags & 1) {   // re-split, each part keeping the sorted order
+          for (int k = 1; k < n_out; ++k) {
+            const int v = lc[k];
+            const double x = lv[k];
+            if (v < n_own) {
+              int p = k;
+              while (p > 0 && lc[p - 1] >= n_own) { lc[p] = lc[p - 1]; lv[p] = lv[p - 1]; --p; }
+              lc[p] = v;
+              lv[p] = x;
+            }
+          }
+        }
+      }
+      T.nout = n_out;
+    }
+  }
+  __syncthreads();
+
+  // ---- write ---------------------------------------------------------------------------------------------------------------
+  if (!(S.flags & 2)) return;
+  const int n_out = S.nout;
+  if (MODE != 1 && gl == 0) { lraw[i] = L; len[i] = n_out; }
+  if (MODE == 0) return;
+  const size_t b = (MODE == 1) ? (size_t)Pptr[i] : (size_t)i * pmax;
+  for (int k = gl; k < n_out; k += G) {
+    Pcol[b + k] = f2c[S.lc[k]];
+    Pval[b + k] = S.lv[k];
+  }
+}
+
+}  // namespace flat

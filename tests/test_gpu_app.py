@@ -269,3 +269,64 @@ def test_ilu_through_the_app(app, tmp_path, method, nranks):
         assert np.abs(sol[:, 1] - 1.0).max() < (1e-3 if method == "ilu" else 1e-6), out
     m = re.search(r"final relative residual norm = ([0-9.eE+-]+)", out)
     assert float(m.group(1)) < tol
+
+
+# ---- the UNMODIFIED reference host (oracle/_ref/hypre_app_ref: /root/reference/src/{main,HypreSystem}.cpp + mmio.c compiled in
+# place against include/ and linked with libb200hypre.so, oracle/Makefile `ref`) driving the library ---------------------------
+REF_APP = os.path.join(ROOT, "oracle", "_ref", "hypre_app_ref")
+
+
+def read_ijv(path):
+    with open(path) as f:
+        lo, hi = (int(t) for t in f.readline().split())
+        v = np.array([float(l.split()[1]) for l in f])
+    assert len(v) == hi - lo + 1
+    return v
+
+
+@pytest.mark.skipif(not os.path.exists(REF_APP), reason="oracle/_ref/hypre_app_ref not built (needs /root/reference at build time)")
+@pytest.mark.parametrize("linsys_type", ["matrix_market", "hypre_ij"])
+def test_unmodified_reference_host_runs_on_the_library(app, tmp_path, linsys_type):
+    """drop-in: the reference's own main.cpp / HypreSystem.cpp, not a line changed, load, set up, solve and write the
+    solution through libb200hypre; the repo's twin of that host (app/) must produce the same solution from the same input.
+    (build_27pt_stencil is HIP-only in the reference, /root/reference/src/HypreSystem.cpp:33-37, so the loaders are used.)"""
+    n = 10
+    A = laplace3d(n).tocsr()
+    N = A.shape[0]
+    rng = np.random.default_rng(11)
+    xref = rng.standard_normal(N)
+    b = A @ xref
+    files = []
+    if linsys_type == "matrix_market":
+        write_mm_matrix(tmp_path / "mat.mm", A, shuffle=rng)
+        write_mm_vector(tmp_path / "rhs.mm", b)
+        write_mm_vector(tmp_path / "sln.mm", xref)
+        files = ["mat.mm", "rhs.mm", "sln.mm"]
+        linsys = ["type: matrix_market", "matrix_file: mat.mm", "rhs_file: rhs.mm", "sln_file: sln.mm", "write_solution: true"]
+    else:
+        half = N // 2 + 3
+        for p, (lo, hi) in enumerate([(0, half - 1), (half, N - 1)]):
+            with open(tmp_path / f"A.ij.{p:05d}", "w") as f:
+                f.write(f"{lo} {hi} {lo} {hi}\n")
+                for i in range(lo, hi + 1):
+                    for k in range(A.indptr[i], A.indptr[i + 1]):
+                        f.write(f"{i} {A.indices[k]} {A.data[k]:.14e}\n")
+            for name, v in (("b.ij", b), ("x.ij", xref)):
+                with open(tmp_path / f"{name}.{p:05d}", "w") as f:
+                    f.write(f"{lo} {hi}\n")
+                    for i in range(lo, hi + 1):
+                        f.write(f"{i} {v[i]:.14e}\n")
+            files += [f"A.ij.{p:05d}", f"b.ij.{p:05d}", f"x.ij.{p:05d}"]
+        linsys = ["type: hypre_ij", "matrix_file: A.ij", "rhs_file: b.ij", "sln_file: x.ij", "num_partitions: 2", "write_solution: true"]
+    sols = {}
+    for name, exe in (("reference", REF_APP), ("twin", app)):
+        wd = tmp_path / name
+        wd.mkdir()
+        for f in files:
+            os.symlink(tmp_path / f, wd / f)
+        rc, out = run_app(exe, str(wd), linsys)
+        assert rc == 0, out
+        assert "Timer summary" in out and "Preconditioner setup" in out and "Solve" in out, out
+        sols[name] = read_ijv(wd / "IJV0.sln.00000")
+    assert np.abs(sols["reference"] - xref).max() <= 1e-7 * max(1.0, np.abs(xref).max())
+    assert np.abs(sols["reference"] - sols["twin"]).max() <= 1e-12 * max(1.0, np.abs(xref).max())
