@@ -16,6 +16,13 @@ using namespace b200;
     API_END                                                       \
   }
 
+// the Krylov solvers skip clearing the preconditioner's output only for entry points that honour the zero-guess hint
+namespace b200 {
+bool precond_honours_zero_hint(PrecondFn f) {
+  return f == reinterpret_cast<PrecondFn>(&HYPRE_BoomerAMGSolve) || f == reinterpret_cast<PrecondFn>(&HYPRE_ILUSolve);
+}
+}  // namespace b200
+
 extern "C" {
 
 HYPRE_Int HYPRE_BoomerAMGCreate(HYPRE_Solver *solver) {
@@ -73,6 +80,8 @@ HYPRE_Int HYPRE_BoomerAMGSolve(HYPRE_Solver solver, HYPRE_ParCSRMatrix A, HYPRE_
     }
     h->num_iterations = 1;
   } else {
+    // used as a preconditioner with max_iter > 1 or tol > 0: the Krylov solver's output vector counts as zero
+    if (precond_zero_guess_hint()) vec_fill(vx->p, 0.0, as_par(A)->n);
     amg_solve(h->amg, *as_par(A), vb->p, vx->p, &h->num_iterations, &h->rel_resid);
   }
   API_END

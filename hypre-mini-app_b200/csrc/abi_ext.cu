@@ -5,6 +5,10 @@
 #include <cstring>
 
 using namespace b200;
+namespace b200 {
+bool peer_active();
+bool shm_active();
+}
 
 namespace {
 
@@ -263,6 +267,26 @@ HYPRE_Int b200hypre_amg_relax(HYPRE_Solver amg, HYPRE_Int level, HYPRE_Complex *
 HYPRE_Int b200hypre_amg_vcycle(HYPRE_Solver amg, const HYPRE_Complex *r, HYPRE_Complex *z) {
   API_ARG(amg && r && z, "b200hypre_amg_vcycle: null argument");
   API_BEGIN amg_vcycle(as_amg(amg)->amg, r, z); API_END
+}
+
+// which transport the halo exchanges of this communicator use
+const char *b200hypre_halo_transport(void) {
+  if (ctx().nranks <= 1) return "single-rank";
+  if (shm_active()) return "host-staged shm (ranks share one GPU)";
+  return peer_active() ? "NVLink peer memory (IPC arena, device flags) + NCCL all-reduce" : "NCCL send/recv + NCCL all-reduce";
+}
+
+// out = M^-1 in through a HYPRE_PtrToParSolverFcn, applied exactly as the Krylov solvers apply their preconditioner
+HYPRE_Int b200hypre_precond_apply(HYPRE_PtrToParSolverFcn fn, HYPRE_Solver precond, HYPRE_ParCSRMatrix A, const HYPRE_Complex *in,
+                                  HYPRE_Complex *out) {
+  API_ARG(fn && A && in && out, "b200hypre_precond_apply: null argument");
+  API_BEGIN
+  ParCsr *M = as_par(A);
+  ParVec pin, pout;
+  pin.g_n = pout.g_n = M->g_rows; pin.start = pout.start = M->row_start; pin.n = pout.n = M->n;
+  pin.p = const_cast<double *>(in); pout.p = out;
+  apply_precond(reinterpret_cast<PrecondFn>(fn), precond, *M, pin, pout, "b200hypre_precond_apply");
+  API_END
 }
 
 // ---- GMRES extras / instrumentation -------------------------------------------------------------------------------------

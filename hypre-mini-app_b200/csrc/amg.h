@@ -174,7 +174,9 @@ struct Krylov {
   std::vector<double> history;
   double solve_seconds = 0;
 };
-void set_precond_zero_guess_hint(bool v);  // the next preconditioner call may treat its output vector as zero (gmres.cu)
+bool precond_honours_zero_hint(PrecondFn f);  // f is one of the library's own Solve entry points (abi_amg.cu)
+void set_precond_zero_guess_hint(bool v);
+void apply_precond(PrecondFn fn, void *data, ParCsr &A, ParVec &in, ParVec &out, const char *who);  // gmres.cu  // the next preconditioner call may treat its output vector as zero (gmres.cu)
 void krylov_setup(Krylov &k, ParCsr &A, ParVec &b, ParVec &x);
 int krylov_solve(Krylov &k, ParCsr &A, ParVec &b, ParVec &x);
 
@@ -219,6 +221,7 @@ void ij_vector_set(IJVector &v, i64 n, const i64 *idx, const double *vals, int o
 void ij_vector_get(IJVector &v, i64 n, const i64 *idx, double *out);
 
 // ---- setup building blocks (amg_setup.cu), exposed for tests through include/b200hypre.h ----------------------------
+i64 checked_total(const int *counts, i64 n, const char *what);   // 64-bit sum of per-row counts, fails beyond int32 (spgemm.cu)
 void csr_transpose(const DCsr &A, DCsr &T);
 // sorted = false: rows of C are written in no particular order (enough for the intermediate Q = A P of the Galerkin product)
 void csr_spgemm(const DCsr &A, const DCsr &B, DCsr &C, bool diag_first, bool sorted = true);

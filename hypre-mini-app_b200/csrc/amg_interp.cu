@@ -576,7 +576,7 @@ void build_interp(const DCsr &Aext, const int *Sptr, const int *Scol, i64 S_nnz,
     cub::DeviceScan::ExclusiveSum(tmp.p, tb, len.p, P.ptr.p, n_rows + 1, stream());
     count_launch(2);
   }
-  P.nnz = fetch1(P.ptr.p + n_rows);
+  P.nnz = checked_total(len.p, n_rows, "build_interp");
   P.col.alloc((size_t)std::max<i64>(P.nnz, 1));
   P.val.alloc((size_t)std::max<i64>(P.nnz, 1));
   if (single) {

@@ -398,12 +398,23 @@ void amg_setup(Amg &amg, ParCsr &A) {
   B200_REQUIRE(o.coarsen_type == 8 || o.coarsen_type == 10 || o.max_levels == 1,
                "BoomerAMG: only coarsen_type 8 (PMIS; 10/HMIS is mapped to PMIS) is built in this round");
   B200_REQUIRE(o.interp_type == 6 || o.max_levels == 1, "BoomerAMG: only interp_type 6 (extended+i) is built in this round");
+  // coarsest level: Gaussian elimination (relax_type[3] = 9, what HYPRE_BoomerAMGSetRelaxType leaves there); any other
+  // coarse_relax_type (HYPRE_BoomerAMGSetCycleRelaxType(.., 3), HypreSystem.cpp:135-136) is refused rather than ignored
+  B200_REQUIRE(o.relax_type[3] == 9 || o.max_levels == 1,
+               "BoomerAMG: coarse_relax_type must be 9 (Gaussian elimination on the coarsest level); got " + std::to_string(o.relax_type[3]));
   for (int k = 0; k < 3; ++k)
     B200_REQUIRE(o.relax_type[k] == 18 || o.relax_type[k] == 7 || o.relax_type[k] == 16 || is_gs_relax(o.relax_type[k]),
                  "BoomerAMG: relax_type must be 7 (Jacobi), 18 (l1-Jacobi), 16 (Chebyshev) or hybrid Gauss-Seidel (3, 4, 6, 8, 13, 14)");
   B200_REQUIRE(o.relax_type[1] == o.relax_type[2] || (is_gs_relax(o.relax_type[1]) && is_gs_relax(o.relax_type[2]) &&
                                                       is_l1_gs_relax(o.relax_type[1]) == is_l1_gs_relax(o.relax_type[2])),
                "BoomerAMG: down and up smoothers must share their diagonal scaling (same relax_type family)");
+  if (o.coarsen_type == 10 && o.max_levels > 1 && ctx().rank == 0) {
+    static bool warned = false;
+    if (!warned)
+      fprintf(stderr, "[b200hypre] warning: coarsen_type 10 (HMIS) is run as coarsen_type 8 (PMIS): the Ruge-Stueben first pass of HMIS "
+                      "is not built; the hierarchy is the PMIS one\n");
+    warned = true;
+  }
   if (amg.graph_exec) { cudaGraphExecDestroy(amg.graph_exec); amg.graph_exec = nullptr; }
   amg.setup_phase_ms.clear();
   amg.lev.clear();

@@ -21,6 +21,17 @@ thread_local bool g_zero_guess_hint = false;
 bool precond_zero_guess_hint() { return g_zero_guess_hint; }
 void set_precond_zero_guess_hint(bool v) { g_zero_guess_hint = v; }
 
+// One preconditioner application as every Krylov solver of the library makes it.  hypre's solvers clear the output before
+// the call; the library's own preconditioners are told so instead (they skip the clear and the first residual, or clear the
+// vector themselves when they iterate), a foreign callback gets the cleared vector.  A failing callback fails the solve.
+void apply_precond(PrecondFn fn, void *data, ParCsr &A, ParVec &in, ParVec &out, const char *who) {
+  if (!precond_honours_zero_hint(fn)) vec_fill(out.p, 0.0, out.n);
+  g_zero_guess_hint = true;
+  const int rc = fn(data, &A, &in, &out);
+  g_zero_guess_hint = false;
+  B200_REQUIRE(rc == 0, std::string(who) + ": the preconditioner returned error flag " + std::to_string(rc));
+}
+
 void gmres_setup(Gmres &g, ParCsr &A, ParVec &b, ParVec &x) {
   ensure_init();
   g.n = A.n;
@@ -69,10 +80,7 @@ int gmres_solve(Gmres &g, ParCsr &A, ParVec &bvec, ParVec &xvec) {
   auto precond = [&](double *in, double *out) {
     if (g.precond) {
       pin.p = in; pout.p = out;
-      g_zero_guess_hint = true;  // out is logically zero; our own BoomerAMGSolve skips clearing / the residual
-      int rc = g.precond(g.precond_data, &A, &pin, &pout);
-      g_zero_guess_hint = false;
-      (void)rc;
+      apply_precond(g.precond, g.precond_data, A, pin, pout, "GMRES");
     } else vec_copy(out, in, n);
   };
   auto norm = [&](const double *v) { return std::sqrt(dot_host(g.dw, v, v, n)); };

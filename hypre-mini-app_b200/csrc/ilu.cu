@@ -191,6 +191,7 @@ void ilu_solve(Ilu &ilu, ParCsr &A, const double *b, double *x, bool zero_guess)
     ilu.num_iterations = 1;
     return;
   }
+  if (zero_guess) vec_fill(x, 0.0, n);   // preconditioner use with max_iter > 1 or tol > 0: the output counts as zero
   auto residual = [&]() { SpmvArgs a; a.x = x; a.y = ilu.r.p; a.b = b; par_spmv(A, SPMV_RES, a); };
   double rhs_norm = 0.0, rel = 1.0;
   residual();

@@ -41,9 +41,7 @@ struct Ops {
   void precond(double *in, double *out) {  // out = M^{-1} in (hypre clears out first; our AMG is told to treat it as zero)
     if (k.precond) {
       pin.p = in; pout.p = out;
-      set_precond_zero_guess_hint(true);
-      k.precond(k.precond_data, &A, &pin, &pout);
-      set_precond_zero_guess_hint(false);
+      apply_precond(k.precond, k.precond_data, A, pin, pout, "Krylov solver");
     } else vec_copy(out, in, n);
   }
   void matvec(const double *x, double *y) { SpmvArgs a; a.x = x; a.y = y; par_spmv(A, SPMV_AX, a); }

@@ -478,7 +478,32 @@ void exclusive_scan(const T *in, T *out, i64 n) {
   count_launch(2);
 }
 
+__global__ void k_sum_i64(const int *__restrict__ v, i64 n, unsigned long long *out) {
+  unsigned long long s = 0;
+  for (i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (i64)gridDim.x * blockDim.x) s += (unsigned long long)v[k];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0 && s) atomicAdd(out, s);
+}
+
 }  // namespace
+
+// Sum of n non-negative per-row counts in 64 bits.  Row pointers are int32 (DCsr), so every scan of counts that a product,
+// an interpolation or a transposition produces is guarded with this first: a total beyond int32 fails with a diagnostic
+// instead of wrapping silently and under-allocating the column / value arrays.
+i64 checked_total(const int *counts, i64 n, const char *what) {
+  if (n <= 0) return 0;
+  DVec<unsigned long long> acc(1);
+  acc.zero();
+  k_sum_i64<<<std::min<int>(div_up(n, 256), 4 * ctx().sm_count), 256, 0, stream()>>>(counts, n, acc.p);
+  count_launch();
+  unsigned long long h = 0;
+  B200_CUDA(cudaMemcpyAsync(&h, acc.p, sizeof(h), cudaMemcpyDeviceToHost, stream()));
+  B200_CUDA(cudaStreamSynchronize(stream()));
+  B200_REQUIRE(h < 2147483640ull, std::string(what) + ": " + std::to_string(h) +
+                                      " entries exceed the 32-bit row pointers of one rank; partition the system over more GPUs");
+  return (i64)h;
+}
 
 // T = A^T; entries of every T row keep the order of A's rows (stable).  val may be absent (pattern only) when A.val.n == 0.
 void csr_transpose(const DCsr &A, DCsr &T) {
@@ -487,6 +512,7 @@ void csr_transpose(const DCsr &A, DCsr &T) {
   T.nnz = A.nnz;
   T.ptr.alloc((size_t)T.nr + 1);
   T.col.alloc((size_t)std::max<i64>(A.nnz, 1));
+  B200_REQUIRE(A.nnz < 2147483640LL, "csr_transpose: more than 2^31 entries on one rank");
   const bool has_val = A.val.n > 0;
   if (has_val) T.val.alloc((size_t)std::max<i64>(A.nnz, 1));
   DVec<int> cnt((size_t)T.nr + 1);
@@ -550,11 +576,8 @@ void csr_spgemm(const DCsr &A, const DCsr &B, DCsr &C, bool diag_first, bool sor
       spgemm_pass<false>(A, B, again, L, nullptr, nullptr, nullptr, nnz_row.p, diag_first, sorted);
     }
   }
+  C.nnz = checked_total(nnz_row.p, C.nr, "csr_spgemm (Galerkin product)");
   exclusive_scan(nnz_row.p, C.ptr.p, (i64)C.nr + 1);
-  int last = 0;
-  B200_CUDA(cudaMemcpyAsync(&last, C.ptr.p + C.nr, sizeof(int), cudaMemcpyDeviceToHost, stream()));
-  B200_CUDA(cudaStreamSynchronize(stream()));
-  C.nnz = last;
   C.col.alloc((size_t)std::max<i64>(C.nnz, 1));
   C.val.alloc((size_t)std::max<i64>(C.nnz, 1));
   {

@@ -147,6 +147,13 @@ def plan_recv(col_map, col_starts):
     return rr[:k].copy(), ro[:k + 1].copy()
 
 
+def halo_transport():
+    import ctypes as C
+    f = lib().b200hypre_halo_transport
+    f.restype = C.c_char_p
+    return f().decode()
+
+
 def launch_count():
     return int(lib().b200hypre_launch_count())
 

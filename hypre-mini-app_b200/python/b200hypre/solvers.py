@@ -107,6 +107,12 @@ class BoomerAMG:
     def vcycle_ptr(self, r_ptr, z_ptr):
         check(lib().b200hypre_amg_vcycle(self.h, VP(r_ptr), VP(z_ptr)), "vcycle")
 
+    def apply_as_preconditioner_ptr(self, A, in_ptr, out_ptr):
+        """out = M^-1 in through HYPRE_BoomerAMGSolve as a Krylov solver calls it (device pointers)"""
+        import ctypes as C
+        fn = C.cast(lib().HYPRE_BoomerAMGSolve, VP)
+        check(lib().b200hypre_precond_apply(fn, self.h, A.object(), VP(in_ptr), VP(out_ptr)), "precond_apply")
+
     def relax_ptr(self, level, u_ptr, f_ptr):
         check(lib().b200hypre_amg_relax(self.h, level, VP(u_ptr), VP(f_ptr)), "relax")
 

@@ -55,6 +55,10 @@ HYPRE_Int b200hypre_amg_setup_phases(HYPRE_Solver amg, char *names, HYPRE_Int na
 /* one relaxation sweep of the level's smoother: u <- relax(u, f) (device pointers of the level's local length) */
 HYPRE_Int b200hypre_amg_relax(HYPRE_Solver amg, HYPRE_Int level, HYPRE_Complex *u, const HYPRE_Complex *f);
 HYPRE_Int b200hypre_amg_vcycle(HYPRE_Solver amg, const HYPRE_Complex *r, HYPRE_Complex *z);      /* z = M^-1 r, device pointers */
+const char *b200hypre_halo_transport(void);   /* what the halo exchanges of the current communicator run over */
+/* out = M^-1 in through a preconditioner callback, applied as HYPRE_ParCSRGMRESSolve applies it (output counts as zero) */
+HYPRE_Int b200hypre_precond_apply(HYPRE_PtrToParSolverFcn fn, HYPRE_Solver precond, HYPRE_ParCSRMatrix A, const HYPRE_Complex *in,
+                                  HYPRE_Complex *out);
 
 /* ---- GMRES extras ---------------------------------------------------------------------------------------------------------- */
 HYPRE_Int b200hypre_gmres_set_orthogonalization(HYPRE_Solver gmres, HYPRE_Int kind);   /* 0 = MGS (hypre), 1 = fused CGS2 (default) */

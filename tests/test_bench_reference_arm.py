@@ -36,3 +36,29 @@ def test_reference_arm_runs_on_rank_0_only():
     """under torchrun the driver starts N processes; the other ranks print nothing and exit 0"""
     env = dict(os.environ, RANK="1", LOCAL_RANK="1", WORLD_SIZE="2", MASTER_ADDR="127.0.0.1", MASTER_PORT="29571")
     assert run_reference("--gpus", "2", env=env) == []
+
+
+def test_reference_arm_ignores_torchrun_thread_cap_and_uses_virtual_ranks():
+    """torchrun exports OMP_NUM_THREADS=1: the arm sets its thread count itself (all host cores), and at N > 1 it runs the
+    N-virtual-rank oracle on the N-box global problem (round-1 verdict: the N > 1 ratios were void)"""
+    cores = len(os.sched_getaffinity(0))
+    env = dict(os.environ, RANK="0", LOCAL_RANK="0", WORLD_SIZE="2", MASTER_ADDR="127.0.0.1", MASTER_PORT="29572", OMP_NUM_THREADS="1")
+    lines = run_reference("--gpus", "2", env=env)
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["n_gpus"] == 2 and d["cpu_baseline"]["cores"] == cores
+    assert d["config"]["process_grid"] == [2, 1, 1] and d["config"]["global_rows"] == 2 * 256 ** 3
+    assert d["sample_rows"] == 2 * 20 ** 3 and "2 virtual rank(s)" in d["sample"]
+    assert d["converged"] is True and d["iterations"] > 0
+
+
+def test_both_arms_share_one_config():
+    sys.path.insert(0, ROOT)
+    import bench
+    args = bench.parse.__globals__["argparse"].Namespace(n=256, stencil=7, relax_type=18, orth="cgs2")
+    c1 = bench.arm_config(args, 1, (1, 1, 1))
+    assert c1["rows_per_gpu"] == 256 ** 3 and c1["process_grid"] == [1, 1, 1] and "lap7_256" in c1["workload"]
+    # default sample sizes: the GPU arm's own size at N = 1, about the same global size at N > 1
+    full = bench.parse.__globals__["argparse"].Namespace(n=256, cpu_n=0, steps=20, warmup=3)
+    assert bench.reference_sample(full, 1) == (256, 2, 1)
+    assert bench.reference_sample(full, 8)[0] == 128 and bench.reference_sample(full, 2)[0] == 200

@@ -282,3 +282,48 @@ def test_larger_size_properties(b200, n, stencil):
     assert np.linalg.norm(res) / np.linalg.norm(s.b.get_values()) <= 1.01e-8
     r.destroy()
     s.destroy_system()
+
+
+def test_amg_preconditioner_with_two_cycles_is_a_fixed_operator(b200):
+    """BoomerAMG with max_iterations 2 (a YAML option of the reference, HypreSystem.cpp:155) as the GMRES preconditioner takes
+    the iterative branch of HYPRE_BoomerAMGSolve: the Krylov output vector must count as zero on every application (hypre
+    clears it), otherwise the preconditioner depends on stale data and GMRES stops being GMRES.  Two cycles from a zero guess
+    are z = M r + M (r - A M r): checked against that composition of single cycles, and through the solve."""
+    import torch
+    n = 16
+    s2 = make_system(b200, n, 7, max_iterations=2, tolerance=0.0)
+    s2.solve()
+    assert s2.solver.converged == 1 and np.abs(s2.solution() - 1.0).max() < 1e-6
+    s1 = make_system(b200, n, 7)
+    s1.solve()
+    assert s2.solver.iterations < s1.solver.iterations      # two cycles per application: a stronger, still linear operator
+    # one application through the callback path with garbage in the output vector == composition of single cycles
+    rng = np.random.default_rng(5)
+    r = torch.tensor(rng.standard_normal(n ** 3), device="cuda")
+    z1 = torch.zeros_like(r)
+    torch.cuda.synchronize()
+    s1.precond.vcycle_ptr(r.data_ptr(), z1.data_ptr())
+    b200.synchronize()
+    A = b200_level0_scipy(s1)
+    zn = z1.cpu().numpy()
+    r2 = torch.tensor(r.cpu().numpy() - A @ zn, device="cuda")
+    z2 = torch.zeros_like(r)
+    torch.cuda.synchronize()
+    s1.precond.vcycle_ptr(r2.data_ptr(), z2.data_ptr())
+    b200.synchronize()
+    expect = zn + z2.cpu().numpy()
+    out = torch.full_like(r, 123.0)                           # stale contents, as left by a previous iteration
+    torch.cuda.synchronize()
+    s2.precond.apply_as_preconditioner_ptr(s2.A, r.data_ptr(), out.data_ptr())
+    b200.synchronize()
+    got = out.cpu().numpy()
+    assert np.abs(got - expect).max() / np.abs(expect).max() <= 1e-12
+    s1.destroy_system()
+    s2.destroy_system()
+
+
+def b200_level0_scipy(s):
+    import scipy.sparse as sp
+    ptr, col, val = s.precond.level_matrix(0, "A")
+    nr = len(ptr) - 1
+    return sp.csr_matrix((val, col, ptr), shape=(nr, nr))
