@@ -330,7 +330,8 @@ void halo_fwd(ParCsr &A, const T *own, T *halo) {
   }
   exchange_dev((int)h.send_rank.size(), h.send_rank.data(), sp.data(), sb.data(), (int)h.recv_rank.size(), h.recv_rank.data(),
                rp.data(), rb.data(), stream());
-  B200_CUDA(cudaStreamSynchronize(stream()));  // sbuf is released on return
+  // no host synchronisation: the exchange is enqueued on stream() and sbuf is returned to the stream-ordered pool on the same
+  // stream, so it cannot be reused before the send has read it
 }
 // reverse direction: every rank sends its halo values back to the owners; back[t] is the value a requester holds for the
 // owner's entry send_idx[t] (t in send-list order, one slot per (requester, entry))
@@ -350,7 +351,6 @@ void halo_rev(ParCsr &A, const T *halo, T *back) {
   }
   exchange_dev((int)h.recv_rank.size(), h.recv_rank.data(), sp.data(), sb.data(), (int)h.send_rank.size(), h.send_rank.data(),
                rp.data(), rb.data(), stream());
-  B200_CUDA(cudaStreamSynchronize(stream()));
 }
 
 // ---- variable-length row exchange ---------------------------------------------------------------------------------------------
@@ -401,7 +401,7 @@ void exchange_rows(const std::vector<int> &srank, const std::vector<int> &soff, 
     }
     exchange_dev((int)srank.size(), srank.data(), sp.data(), sb.data(), (int)rrank.size(), rrank.data(), rp.data(), rb.data(), stream());
   }
-  B200_CUDA(cudaStreamSynchronize(stream()));
+  // the payload exchanges stay enqueued on stream(): consumers are stream-ordered behind them
 }
 
 // rows `list[0..nrows)` of a local matrix in (own | external) numbering -> packed CSR with global columns.  Payload: the
@@ -509,11 +509,13 @@ __global__ void k_pmis_init_d(int n, const int *Sptr, const int *cnt, int seed, 
   if (m < 1.0) { cf[i] = -1; measure[i] = 0.0; }
   else { cf[i] = 0; measure[i] = m; }
 }
-__global__ void k_count_undecided_d(int n, const int *cf, int *counter) {
+// undecided points of this rank, added to a double (exact for counts below 2^53) so that the sum over ranks is one device
+// all-reduce followed by a single read-back: one host synchronisation per sweep
+__global__ void k_count_undecided_d(int n, const int *cf, double *counter) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   int u = (i < n && cf[i] == 0) ? 1 : 0;
   unsigned b = __ballot_sync(0xffffffffu, u);
-  if ((threadIdx.x & 31) == 0 && b) atomicAdd(counter, __popc(b));
+  if ((threadIdx.x & 31) == 0 && b) atomicAdd(counter, (double)__popc(b));
 }
 __global__ void k_is_init_d(int n, int nh, const int *cf, const double *measure, int *is) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -707,13 +709,13 @@ bool coarsen_level_dist(Amg &amg, AmgLevel &L, AmgLevel &Lc) {
     DLAUNCH(k_scatter_add_int, Ap.halo.n_send, Ap.halo.n_send, Ap.halo.send_idx.p, back.p, cnt.p);
     DVec<double> measure((size_t)nm + 1);
     DLAUNCH(k_pmis_init_d, n, n, L.Sptr.p, cnt.p, 2747 + c.rank, measure.p, cfm.p);
-    DVec<int> is((size_t)nm + 1), counter(1);
+    DVec<int> is((size_t)nm + 1);
+    DVec<double> counter(1);
     for (int sweep = 0; sweep < 100000; ++sweep) {
       counter.zero();
       DLAUNCH(k_count_undecided_d, n, n, cfm.p, counter.p);
-      i64 und = fetch1(counter.p);
-      allreduce_sum_host_i64(&und, 1);
-      if (und == 0) break;
+      allreduce_sum_dev(counter.p, 1);
+      if (fetch1(counter.p) == 0.0) break;
       halo_fwd<double>(Ap, measure.p, measure.p + n);
       DLAUNCH(k_is_init_d, nm, n, nh, cfm.p, measure.p, is.p);
       DLAUNCH(k_is_knock_d, n, n, L.Sptr.p, L.Scol.p, measure.p, cfm.p, is.p);

@@ -463,9 +463,38 @@ void launch_flat(int grid_rows, const rows::Csr &A, const int *Sptr, const int *
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
-  kern<<<div_up(grid_rows, 256 / G), 256, smem, stream()>>>(A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw, len, Pptr, Pcol,
-                                                          Pval, list);
-  count_launch();
+  static int timing = -1;
+  if (timing < 0) { const char *e = getenv("B200_INTERP_TIMING"); timing = (e && atoi(e) != 0) ? 1 : 0; }
+  DVec<unsigned long long> ts;
+  if (timing) { ts.alloc(8); ts.zero(); }
+  // MODE 2: rows that need truncation are handed to k_interp_trunc through a scratch area of CAP entries per row; the rows are
+  // processed in chunks so that the scratch stays at about 1.5 GB whatever the level size
+  const int chunk = (MODE == 2) ? std::max(256, (int)((size_t)(128u << 20) / CAP) / 256 * 256) : std::max(grid_rows, 1);
+  DVec<int> sc;
+  DVec<double> sv;
+  if (MODE == 2) {
+    const size_t rows_in_chunk = (size_t)std::min(chunk, std::max(grid_rows, 1));
+    sc.alloc(rows_in_chunk * CAP);
+    sv.alloc(rows_in_chunk * CAP);
+  }
+  for (int slot0 = 0; slot0 < grid_rows; slot0 += chunk) {
+    const int cnt = std::min(chunk, grid_rows - slot0);
+    kern<<<div_up(cnt, 256 / G), 256, smem, stream()>>>(A, Sptr, Scol, Scf, cf, f2c, n_own, std::min(n_rows, slot0 + cnt), tf, pmax, lo, lraw,
+                                                       len, Pptr, Pcol, Pval, list, slot0, sc.p, sv.p, ts.p);
+    count_launch();
+    if (MODE == 2) {
+      flat::k_interp_trunc<<<div_up(cnt, 256), 256, 0, stream()>>>(slot0, std::min(n_rows, slot0 + cnt), list, CAP, sc.p, sv.p, lraw, len, f2c,
+                                                                  n_own, tf, pmax, Pcol, Pval);
+      count_launch();
+    }
+  }
+  if (timing) {   // debugging aid: share of the warp-cycles of this launch per phase
+    std::vector<unsigned long long> h = ts.to_host();
+    double tot = 0;
+    for (int k = 0; k < 6; ++k) tot += (double)h[k];
+    fprintf(stderr, "[interp timing] G=%d MODE=%d rows=%d  discovery %.1f%%  weights %.1f%%  wait1 %.1f%%  trunc %.1f%%  wait2 %.1f%%  write %.1f%%  (%.3g warp-cycles)\n",
+            G, MODE, grid_rows, 100 * h[0] / tot, 100 * h[1] / tot, 100 * h[2] / tot, 100 * h[3] / tot, 100 * h[4] / tot, 100 * h[5] / tot, tot);
+  }
 }
 template <int MODE, bool SMALL>
 void launch_one(int grid_rows, const rows::Csr &A, const int *Sptr, const int *Scol, const signed char *Scf, const int *cf, const int *f2c,

@@ -103,8 +103,19 @@ template <int G, int H, int CAP, int STG, int MODE>
 __global__ void __launch_bounds__(256, 4)
 k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__ Scol, const signed char *__restrict__ Scf,
               const int *__restrict__ cf, const int *__restrict__ f2c, int n_own, int n_rows, double tf, int pmax, int lo, int *lraw,
-              int *len, const int *__restrict__ Pptr, int *Pcol, double *Pval, const int *__restrict__ row_list) {
+              int *len, const int *__restrict__ Pptr, int *Pcol, double *Pval, const int *__restrict__ row_list,
+              int slot0, int *scr_c, double *scr_v, unsigned long long *tstats) {
   using GS = Grp<G, H, CAP, STG>;
+  // tstats != nullptr (B200_INTERP_TIMING=1): cycles per phase summed over the warps of the launch -- [0] discovery,
+  // [1] weights, [2] wait at the first block barrier, [3] truncation (first warp), [4] wait at the second barrier, [5] write
+  long long tmark = tstats ? clock64() : 0;
+  auto lap = [&](int slot) {
+    if (tstats && (threadIdx.x & 31) == 0) {
+      const long long now = clock64();
+      atomicAdd(tstats + slot, (unsigned long long)(now - tmark));
+      tmark = now;
+    }
+  };
   static_assert(CAP <= 128 && G <= 32 && STG > CAP, "slot / tag encodings");
   constexpr int GROUPS = 256 / G;
   constexpr int HMAX = (H * 3) / 4;
@@ -115,7 +126,10 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
   const int gbase = lane32 - gl;
   const unsigned ltm = (1u << gl) - 1u;
   GS &S = all[g];
-  const int slot = blockIdx.x * GROUPS + g;
+  // MODE 2 defers truncation: a row that needs it is written raw (C-hat list + weights) at (slot - slot0) * CAP of the scratch
+  // arrays and finished by k_interp_trunc (one THREAD per row); this kernel then has no block barrier at all.
+  constexpr bool DEFER = (MODE == 2);
+  const int slot = slot0 + blockIdx.x * GROUPS + g;
   int i = -1;
   if (slot < n_rows) i = row_list ? row_list[slot] : slot;
 
@@ -206,6 +220,7 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
     }
   }
   if (ovf) active = false;   // lraw stays -1: the next tier takes the row
+  lap(0);
   const bool full = (MODE != 0) || tf != 0.0;
   if (!full) {   // uniform over the grid
     if (active && gl == 0) { lraw[i] = L; len[i] = (pmax > 0 && L > pmax) ? pmax : L; }
@@ -387,8 +402,25 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
     const double md = -diagonal;
     for (int k = gl; k < L; k += G) S.lv[k] = S.lv[k] / md;
   }
+  lap(1);
+  if (DEFER) {
+    if (!active) return;
+    const bool needs_trunc = (tf > 0.0 && L > 0) || (pmax > 0 && L > pmax);
+    if (needs_trunc) {
+      const size_t sb0 = (size_t)(slot - slot0) * CAP;
+      for (int k = gl; k < L; k += G) { scr_c[sb0 + k] = S.lc[k]; scr_v[sb0 + k] = S.lv[k]; }
+      if (gl == 0) { lraw[i] = L; len[i] = any_off ? -2 : -1; }   // pending: k_interp_trunc sets the final length
+    } else {
+      if (gl == 0) { lraw[i] = L; len[i] = L; }
+      const size_t b = (size_t)i * pmax;
+      for (int k = gl; k < L; k += G) { Pcol[b + k] = f2c[S.lc[k]]; Pval[b + k] = S.lv[k]; }
+    }
+    lap(5);
+    return;
+  }
   if (gl == 0) { S.L = L; S.nout = L; S.flags = active ? (2 | (any_off ? 1 : 0)) : 0; }
   __syncthreads();
+  lap(2);
 
   // ---- truncation: sequential per row (the sums and hypre's qsort2abs are order dependent); lane = row of the block -------
   if (threadIdx.x < GROUPS) {
@@ -438,7 +470,9 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
       T.nout = n_out;
     }
   }
+  lap(3);
   __syncthreads();
+  lap(4);
 
   // ---- write ---------------------------------------------------------------------------------------------------------------
   if (!(S.flags & 2)) return;
@@ -450,6 +484,67 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
     Pcol[b + k] = f2c[S.lc[k]];
     Pval[b + k] = S.lv[k];
   }
+  lap(5);
+}
+
+// Deferred truncation (MODE 2): one thread per row on the raw lists the row kernel left in the scratch arrays.  The sums and
+// hypre's qsort2abs are sequential per row by definition; here 32 rows advance per warp instruction and 64 warps per SM
+// hide the dependent-load latency, instead of one lane of a group (or one warp of a block) working alone.
+__global__ void __launch_bounds__(256)
+k_interp_trunc(int slot0, int slot_end, const int *__restrict__ row_list, int cap, int *scr_c, double *scr_v, const int *__restrict__ lraw,
+               int *len, const int *__restrict__ f2c, int n_own, double tf, int pmax, int *Pcol, double *Pval) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int slot = slot0 + t;
+  if (slot >= slot_end) return;
+  const int i = row_list ? row_list[slot] : slot;
+  const int pend = len[i];
+  if (pend >= 0) return;
+  const bool any_off = (pend == -2);
+  int *lc = scr_c + (size_t)t * cap;
+  double *lv = scr_v + (size_t)t * cap;
+  int n_out = lraw[i];
+  if (tf > 0.0 && n_out > 0) {
+    double max_coef = 0.0, row_sum = 0.0, scale = 0.0;
+    for (int k = 0; k < n_out; ++k) { const double a = fabs(lv[k]); max_coef = (a > max_coef) ? a : max_coef; }
+    max_coef = max_coef * tf;
+    int w = 0;
+    for (int k = 0; k < n_out; ++k) {
+      const double x = lv[k];
+      row_sum = row_sum + x;
+      if (fabs(x) >= max_coef) { scale = scale + x; lc[w] = lc[k]; lv[w] = x; ++w; }
+    }
+    n_out = w;
+    if (scale != 0.0 && scale != row_sum) {
+      const double f = row_sum / scale;
+      for (int k = 0; k < n_out; ++k) lv[k] = lv[k] * f;
+    }
+  }
+  if (pmax > 0 && n_out > pmax) {
+    double row_sum = 0.0, scale = 0.0;
+    for (int k = 0; k < n_out; ++k) row_sum = row_sum + lv[k];
+    rows::qsort2abs(lc, lv, n_out, pmax);
+    for (int k = 0; k < pmax; ++k) scale = scale + lv[k];
+    n_out = pmax;
+    if (scale != 0.0 && scale != row_sum) {
+      const double f = row_sum / scale;
+      for (int k = 0; k < n_out; ++k) lv[k] = lv[k] * f;
+    }
+    if (any_off) {   // re-split, each part keeping the sorted order
+      for (int k = 1; k < n_out; ++k) {
+        const int v = lc[k];
+        const double x = lv[k];
+        if (v < n_own) {
+          int p = k;
+          while (p > 0 && lc[p - 1] >= n_own) { lc[p] = lc[p - 1]; lv[p] = lv[p - 1]; --p; }
+          lc[p] = v;
+          lv[p] = x;
+        }
+      }
+    }
+  }
+  len[i] = n_out;
+  const size_t b = (size_t)i * pmax;
+  for (int k = 0; k < n_out; ++k) { Pcol[b + k] = f2c[lc[k]]; Pval[b + k] = lv[k]; }
 }
 
 }  // namespace flat

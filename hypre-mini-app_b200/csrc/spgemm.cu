@@ -254,6 +254,8 @@ __device__ __forceinline__ void spgemm_row(const rows::Csr &A, const rows::Csr &
       }
     }
     gsync<G>(mask);
+    if (nnz_out != nullptr && lane == 0 && row >= 0) nnz_out[row] = *cnt;   // single-pass mode: the length is only known now
+    gsync<G>(mask);
     return;
   }
   // compaction; the list holds sort keys (the diagonal column becomes -1 so that it ranks first)
@@ -478,6 +480,15 @@ void exclusive_scan(const T *in, T *out, i64 n) {
   count_launch(2);
 }
 
+// rows written at their slab positions (sptr, bound-strided) -> CSR positions; G lanes per row, coalesced
+template <int G>
+__global__ void k_compact_rows(int nr, const int *__restrict__ sptr, const int *__restrict__ cptr, const int *__restrict__ scol,
+                               const double *__restrict__ sval, int *__restrict__ ccol, double *__restrict__ cval) {
+  const int i = (int)(((i64)blockIdx.x * blockDim.x + threadIdx.x) / G), lane = threadIdx.x % G;
+  if (i >= nr) return;
+  const int b = cptr[i], n = cptr[i + 1] - b, sb = sptr[i];
+  for (int k = lane; k < n; k += G) { ccol[b + k] = scol[sb + k]; cval[b + k] = sval[sb + k]; }
+}
 __global__ void k_sum_i64(const int *__restrict__ v, i64 n, unsigned long long *out) {
   unsigned long long s = 0;
   for (i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (i64)gridDim.x * blockDim.x) s += (unsigned long long)v[k];
@@ -542,12 +553,52 @@ void csr_spgemm(const DCsr &A, const DCsr &B, DCsr &C, bool diag_first, bool sor
   C.ptr.alloc((size_t)C.nr + 1);
   if (A.nr == 0) { C.nnz = 0; C.ptr.zero(); return; }
   const double in_bytes = 12.0 * (double)(A.nnz + B.nnz) + 4.0 * (double)(A.nr + B.nr);
-  DVec<int> bound((size_t)A.nr), nnz_row((size_t)A.nr + 1);
+  DVec<int> bound((size_t)A.nr + 1), nnz_row((size_t)A.nr + 1);
   nnz_row.zero();
-  {
-    ProfScope prof("spgemm_symbolic", in_bytes + 4.0 * A.nr);
+  B200_CUDA(cudaMemsetAsync(bound.p + A.nr, 0, sizeof(int), stream()));
+  if (!sorted) {
+    // Intermediate product (Q = A P, rows in no particular order): ONE pass.  The product-count bound of a row is tight here
+    // (row of A x at most P_max_elmts entries per P row), so every row is accumulated in a table sized by its bound and
+    // written at a bound-strided slab position; a coalesced copy then packs the rows.  No symbolic pass.
+    ProfScope prof("spgemm_fused", in_bytes + 4.0 * A.nr);
     k_spgemm_bound<<<div_up(A.nr, 256), 256, 0, stream()>>>(rv(A), rv(B), bound.p);
     count_launch();
+    unsigned long long total_b = 0;
+    {
+      DVec<unsigned long long> acc(1);
+      acc.zero();
+      k_sum_i64<<<std::min<int>(div_up(A.nr, 256), 4 * ctx().sm_count), 256, 0, stream()>>>(bound.p, A.nr, acc.p);
+      count_launch();
+      B200_CUDA(cudaMemcpyAsync(&total_b, acc.p, sizeof(total_b), cudaMemcpyDeviceToHost, stream()));
+      B200_CUDA(cudaStreamSynchronize(stream()));
+    }
+    if (total_b < 2147483640ull) {
+      DVec<int> sptr((size_t)A.nr + 1), scol((size_t)std::max<unsigned long long>(total_b, 1));
+      DVec<double> sval((size_t)std::max<unsigned long long>(total_b, 1));
+      exclusive_scan(bound.p, sptr.p, (i64)A.nr + 1);
+      Bins bins;
+      BinLimits L{{16, 32, 64, 128, 256, 1024, 4096}};
+      make_bins(A.nr, bound.p, L, bins);
+      spgemm_pass<true>(A, B, bins, L, sptr.p, scol.p, sval.p, nnz_row.p, false, false);
+      C.nnz = checked_total(nnz_row.p, C.nr, "csr_spgemm (A P)");
+      exclusive_scan(nnz_row.p, C.ptr.p, (i64)C.nr + 1);
+      C.col.alloc((size_t)std::max<i64>(C.nnz, 1));
+      C.val.alloc((size_t)std::max<i64>(C.nnz, 1));
+      const int G = (C.nr > 0 && (double)C.nnz / C.nr > 12.0) ? 32 : 8;
+      if (G == 8) k_compact_rows<8><<<div_up((i64)C.nr * 8, 256), 256, 0, stream()>>>(C.nr, sptr.p, C.ptr.p, scol.p, sval.p, C.col.p, C.val.p);
+      else k_compact_rows<32><<<div_up((i64)C.nr * 32, 256), 256, 0, stream()>>>(C.nr, sptr.p, C.ptr.p, scol.p, sval.p, C.col.p, C.val.p);
+      count_launch();
+      B200_KERNEL_CHECK();
+      return;
+    }
+    // the slab would exceed 32-bit offsets: two passes below
+  }
+  {
+    ProfScope prof("spgemm_symbolic", in_bytes + 4.0 * A.nr);
+    if (sorted) {
+      k_spgemm_bound<<<div_up(A.nr, 256), 256, 0, stream()>>>(rv(A), rv(B), bound.p);
+      count_launch();
+    }
     Bins bins;
     BinLimits L{{16, 32, 64, 128, 512, 2048, 16384}};
     make_bins(A.nr, bound.p, L, bins);

@@ -1,0 +1,21 @@
+#!/bin/bash
+# round-2 call 2: parity + phase timing + bench of the flattened interpolation kernel with deferred truncation and of the
+# fused A*P product; then ncu --set full of one launch per interpolation tier and of the truncation kernel
+cd "$GRAFT_REPO_ROOT"
+timeout 900 python -m pytest tests/test_gpu_parity.py -x -q -m gpu 2>&1 | tail -8 > gpurun_out/r02b_pytest_parity.log
+cat gpurun_out/r02b_pytest_parity.log
+B200_INTERP_TIMING=1 timeout 300 python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e --parity-n 0 > gpurun_out/r02b_timing.json 2> gpurun_out/r02b_timing.err
+grep "interp timing" gpurun_out/r02b_timing.err | tail -12
+timeout 600 python bench.py --steps 5 --warmup 2 --no-cpu-baseline --no-e2e > gpurun_out/r02b_bench.json 2> gpurun_out/r02b_bench.err
+tail -c 400 gpurun_out/r02b_bench.err
+python - <<'PY'
+import json
+d=json.loads(open("gpurun_out/r02b_bench.json").read().strip().splitlines()[-1])
+print(d["ms_per_step"], d["setup_phases_ms"], d["iterations"], d["parity"])
+print({k:(v["ms_total"],v["calls"]) for k,v in d["kernel_classes"].items() if "interp" in k or "spgemm" in k})
+PY
+python bench.py --size 256 --steps 1 --warmup 0 --no-e2e --no-cpu-baseline --parity-n 0 > gpurun_out/r02b_plain.log 2>&1 &&
+bash profiles/prof_kernel.sh r02b_interpL0 'k_interp_flat' 0 1 --parity-n 0 &&
+bash profiles/prof_kernel.sh r02b_interpL1 'k_interp_flat<\(int\)32' 0 1 --parity-n 0 &&
+bash profiles/prof_kernel.sh r02b_trunc 'k_interp_trunc' 0 1 --parity-n 0
+ls -la gpurun_out/*.ncu-rep
