@@ -392,7 +392,11 @@ static void strength(const Csr &A, double theta, double max_row_sum, Csr &S) {
 // ---------------------------------------------------------------------------------------------------------
 // A.4 PMIS (hypre_BoomerAMGCoarsenPMIS + hypre_BoomerAMGIndepSet), sequential sweeps on the global graph.
 // ---------------------------------------------------------------------------------------------------------
-static void pmis(const Csr &S, const std::vector<int> &part, std::vector<int> &cf, std::vector<double> *measure_out) {
+// cf_init (HMIS, CF_init = 1 of hypre_BoomerAMGCoarsenPMIS): markers left by the Ruge-Stueben first pass.  Every point that
+// has an off-rank strong connection or was marked F is reset to undecided; what survives -- interior C points -- is the first
+// independent set, so the first sweep skips the selection, turns their strong dependants into F and the sweeps go on.
+static void pmis(const Csr &S, const std::vector<int> &part, std::vector<int> &cf, std::vector<double> *measure_out,
+                 const std::vector<int> *cf_init = nullptr) {
   int n = S.nr;
   std::vector<double> measure(n, 0.0);
   for (i64 k = 0; k < S.nnz(); ++k) measure[S.col[k]] += 1.0;  // |S^T_i|
@@ -410,19 +414,32 @@ static void pmis(const Csr &S, const std::vector<int> &part, std::vector<int> &c
     if (S.ptr[i + 1] == S.ptr[i]) { cf[i] = -3; measure[i] = 0.0; }  // SF_PT: no strong dependencies
     else graph.push_back(i);
   }
+  if (cf_init) {
+    for (int r = 0; r < np; ++r)
+      for (int i = part[r]; i < part[r + 1]; ++i) {
+        if (cf[i] == -3) continue;
+        bool off_rank = false;
+        for (int k = S.ptr[i]; k < S.ptr[i + 1] && !off_rank; ++k) off_rank = (S.col[k] < part[r] || S.col[k] >= part[r + 1]);
+        cf[i] = (off_rank || (*cf_init)[i] <= 0) ? 0 : 1;
+      }
+  }
   std::vector<char> is(n, 0);
+  bool first_sweep = true;
   while (true) {
     // points nobody depends on become F at once
     {
       size_t w = 0;
       for (size_t g = 0; g < graph.size(); ++g) {
         int i = graph[g];
-        if (measure[i] < 1.0) { cf[i] = -1; measure[i] = 0.0; }
+        if (cf[i] == 0 && measure[i] < 1.0) { cf[i] = -1; measure[i] = 0.0; }
         else graph[w++] = i;
       }
       graph.resize(w);
     }
     if (graph.empty()) break;
+    if (cf_init && first_sweep) {
+      for (int i : graph) is[i] = (cf[i] > 0) ? 1 : 0;   // the surviving C points of the first pass
+    } else {
     // independent set
     for (int i : graph) is[i] = (measure[i] > 1.0) ? 1 : 0;
     for (int i : graph) {
@@ -435,6 +452,8 @@ static void pmis(const Csr &S, const std::vector<int> &part, std::vector<int> &c
         }
       }
     }
+    }
+    first_sweep = false;
     for (int i : graph)
       if (is[i]) cf[i] = 1;
     // undecided points that strongly depend on a C point become F
@@ -450,6 +469,124 @@ static void pmis(const Csr &S, const std::vector<int> &part, std::vector<int> &c
       else graph[w++] = i;
     }
     graph.resize(w);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// A.4 HMIS, first half: the first pass of hypre_BoomerAMGCoarsenRuge (coarsen_type 10) on the rank-local graph S_diag.
+// measure[j] = number of local points that strongly depend on j; points are kept in a list of lists -- one FIFO bucket per
+// integer measure, points appended at the TAIL -- and the HEAD of the bucket with the largest measure becomes the next C
+// point.  Strictly sequential per rank (the tie order is the history of bucket insertions); the ranks are independent.
+// Out: cf = +1 C, -1 F, -3 no strong connections at all.  The second Ruge-Stueben pass is not run for type 10.
+// ---------------------------------------------------------------------------------------------------------
+namespace {
+struct ListOfLists {   // hypre_enter_on_lists / hypre_remove_point
+  std::vector<int> head, tail, next, prev;
+  int top = 0;
+  explicit ListOfLists(int n) : head(16, -1), tail(16, -1), next(n, -1), prev(n, -1) {}
+  void enter(int m, int j) {
+    if (m >= (int)head.size()) { head.resize(2 * m + 1, -1); tail.resize(2 * m + 1, -1); }
+    next[j] = -1;
+    prev[j] = tail[m];
+    if (tail[m] >= 0) next[tail[m]] = j; else head[m] = j;
+    tail[m] = j;
+    if (m > top) top = m;
+  }
+  void remove(int m, int j) {
+    if (prev[j] >= 0) next[prev[j]] = next[j]; else head[m] = next[j];
+    if (next[j] >= 0) prev[next[j]] = prev[j]; else tail[m] = prev[j];
+  }
+  int first() {
+    while (top > 0 && head[top] < 0) --top;
+    return head[top];
+  }
+};
+}  // namespace
+static void rs_first_pass(const Csr &S, const std::vector<int> &part, std::vector<int> &cf) {
+  const int n = S.nr, np = (int)part.size() - 1;
+  cf.assign(n, 0);
+#pragma omp parallel for schedule(dynamic, 1)
+  for (int r = 0; r < np; ++r) {
+    const int lo = part[r], hi = part[r + 1], m = hi - lo;
+    if (m == 0) continue;
+    auto local = [&](int c) { return c >= lo && c < hi; };
+    // ST = transpose of the local part of S (columns and rows in [lo, hi)), rows of ST in ascending order of the source row
+    std::vector<int> stp(m + 1, 0), stc, meas(m, 0);
+    for (int i = lo; i < hi; ++i)
+      for (int k = S.ptr[i]; k < S.ptr[i + 1]; ++k)
+        if (local(S.col[k])) ++stp[S.col[k] - lo + 1];
+    for (int j = 0; j < m; ++j) stp[j + 1] += stp[j];
+    stc.resize(stp[m]);
+    {
+      std::vector<int> w(stp.begin(), stp.end() - 1);
+      for (int i = lo; i < hi; ++i)
+        for (int k = S.ptr[i]; k < S.ptr[i + 1]; ++k)
+          if (local(S.col[k])) stc[w[S.col[k] - lo]++] = i;
+    }
+    for (int j = 0; j < m; ++j) meas[j] = stp[j + 1] - stp[j];
+    ListOfLists lol(m);
+    int num_left = 0;
+    for (int j = lo; j < hi; ++j) {
+      if (S.ptr[j + 1] == S.ptr[j]) { cf[j] = -3; meas[j - lo] = 0; }   // no strong connection, local or off-rank
+      else { cf[j] = 0; ++num_left; }
+    }
+    for (int j = lo; j < hi; ++j) {
+      if (cf[j] == -3) continue;
+      if (meas[j - lo] > 0) lol.enter(meas[j - lo], j - lo);
+      else {   // nobody depends on j: F at once, its strong influences gain a point
+        cf[j] = -1;
+        for (int k = S.ptr[j]; k < S.ptr[j + 1]; ++k) {
+          const int nb = S.col[k];
+          if (!local(nb) || cf[nb] == -3) continue;
+          if (nb < j) {
+            int nm = meas[nb - lo];
+            if (nm > 0) lol.remove(nm, nb - lo);
+            nm = ++meas[nb - lo];
+            lol.enter(nm, nb - lo);
+          } else ++meas[nb - lo];
+        }
+        --num_left;
+      }
+    }
+    while (num_left > 0) {
+      const int idx = lol.first();
+      if (idx < 0) break;
+      const int i = idx + lo;
+      cf[i] = 1;
+      lol.remove(meas[idx], idx);
+      meas[idx] = 0;
+      --num_left;
+      for (int t = stp[idx]; t < stp[idx + 1]; ++t) {   // points that depend on the new C point become F
+        const int nb = stc[t];
+        if (cf[nb] != 0) continue;
+        cf[nb] = -1;
+        lol.remove(meas[nb - lo], nb - lo);
+        --num_left;
+        for (int k = S.ptr[nb]; k < S.ptr[nb + 1]; ++k) {   // ... and make their other influences more attractive
+          const int n2 = S.col[k];
+          if (!local(n2) || cf[n2] != 0) continue;
+          lol.remove(meas[n2 - lo], n2 - lo);
+          lol.enter(++meas[n2 - lo], n2 - lo);
+        }
+      }
+      for (int k = S.ptr[i]; k < S.ptr[i + 1]; ++k) {     // points the new C point depends on lose a dependant
+        const int nb = S.col[k];
+        if (!local(nb) || cf[nb] != 0) continue;
+        lol.remove(meas[nb - lo], nb - lo);
+        const int nm = --meas[nb - lo];
+        if (nm > 0) lol.enter(nm, nb - lo);
+        else {
+          cf[nb] = -1;
+          --num_left;
+          for (int k2 = S.ptr[nb]; k2 < S.ptr[nb + 1]; ++k2) {
+            const int n2 = S.col[k2];
+            if (!local(n2) || cf[n2] != 0) continue;
+            lol.remove(meas[n2 - lo], n2 - lo);
+            lol.enter(++meas[n2 - lo], n2 - lo);
+          }
+        }
+      }
+    }
   }
 }
 
@@ -776,7 +913,11 @@ static void amg_setup(Sys &s) {
     bool last = (level >= o.max_levels - 1) || (fine <= o.max_coarse_size);
     if (!last) {
       strength(L.A, o.strong_threshold, o.max_row_sum, L.S);
-      pmis(L.S, L.part, L.cf_raw, nullptr);
+      if (o.coarsen_type == 10) {   // HMIS: Ruge-Stueben first pass on every rank's interior, PMIS finishes the job
+        std::vector<int> rs;
+        rs_first_pass(L.S, L.part, rs);
+        pmis(L.S, L.part, L.cf_raw, nullptr, &rs);
+      } else pmis(L.S, L.part, L.cf_raw, nullptr);
       int np = (int)L.part.size() - 1;
       std::vector<int> f2c(fine, -1), cpart(np + 1, 0);
       int nc = 0;
