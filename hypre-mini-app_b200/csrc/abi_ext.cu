@@ -162,6 +162,22 @@ HYPRE_Int b200hypre_generate_laplace(HYPRE_Int nx, HYPRE_Int ny, HYPRE_Int nz, H
   API_END
 }
 
+HYPRE_Int b200hypre_generate_workload(HYPRE_Int kind, HYPRE_Int n, HYPRE_BigInt ilower, HYPRE_BigInt iupper, unsigned long long seed,
+                                      HYPRE_BigInt **rows, HYPRE_BigInt **cols, HYPRE_Complex **vals, HYPRE_Complex **rhs,
+                                      HYPRE_BigInt *nnz, HYPRE_BigInt *global_rows) {
+  API_ARG(rows && cols && vals && rhs && nnz, "b200hypre_generate_workload: null output");
+  API_BEGIN
+  GenOut g;
+  generate_workload(kind, n, ilower, iupper, seed, g);
+  *rows = g.rows.p; g.rows.p = nullptr;   // ownership moves to the caller (b200hypre_free(..., HYPRE_MEMORY_DEVICE))
+  *cols = g.cols.p; g.cols.p = nullptr;
+  *vals = g.vals.p; g.vals.p = nullptr;
+  *rhs = g.rhs.p; g.rhs.p = nullptr;
+  *nnz = g.nnz;
+  if (global_rows) *global_rows = g.g_rows;
+  API_END
+}
+
 // ---- inspection ---------------------------------------------------------------------------------------------------------
 HYPRE_Int b200hypre_parcsr_sizes(HYPRE_ParCSRMatrix A, HYPRE_BigInt *sizes) {
   API_ARG(A && sizes, "b200hypre_parcsr_sizes: null argument");

@@ -9,6 +9,7 @@
 // numbering at HypreSystem.cpp:1555 is not reproduced).
 // Output: COO triplets in row order, ascending global column inside a row (= stencil order z, y, x on one rank), plus the rhs.
 #include "amg.h"
+#include "workload_rows.cuh"
 #include <cub/cub.cuh>
 
 namespace b200 {
@@ -132,6 +133,71 @@ void generate_laplace(int nx, int ny, int nz, int px, int py, int pz, int rank, 
   out.vals.alloc((size_t)nnz);
   out.rhs.alloc((size_t)b.nloc);
   k_gen_fill<<<div_up(b.nloc, 256), 256, 0, stream()>>>(b, ptr.p, out.rows.p, out.cols.p, out.vals.p, out.rhs.p);
+  count_launch(4);
+  B200_KERNEL_CHECK();
+  B200_CUDA(cudaStreamSynchronize(stream()));
+}
+
+// ---- synthetic nalu-wind-like systems (BASELINE.json configs[3] / [4]): rows [row_lo, row_hi] of the global system, built by
+// the row functions of workload_rows.cuh.  COO triplets in row order with ascending columns (the pre-sorted path of the IJ
+// assembly) and rhs = A 1.  kind 0: poisson27_hex(n), n^3 rows; kind 1: momentum3(n), 3 n^3 rows.
+namespace {
+__global__ void k_wl_count(int kind, int n, i64 row_lo, i64 nrows, int *cnt) {
+  const i64 t = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t == nrows) cnt[t] = 0;
+  if (t >= nrows) return;
+  const i64 row = row_lo + t, node = kind == 0 ? row : row / 3, nn = (i64)n * n;
+  const int c[3] = {(int)(node % n), (int)((node / n) % n), (int)(node / nn)};
+  if (kind == 0) {
+    int m = 1;
+    for (int d = 0; d < 3; ++d) m *= 1 + (c[d] > 0 ? 1 : 0) + (c[d] < n - 1 ? 1 : 0);
+    cnt[t] = m;
+  } else {
+    int m = 1;
+    for (int d = 0; d < 3; ++d) m += (c[d] > 0 ? 1 : 0) + (c[d] < n - 1 ? 1 : 0);
+    cnt[t] = 3 * m;
+  }
+}
+__global__ void __launch_bounds__(128) k_wl_fill(int kind, int n, i64 row_lo, i64 nrows, unsigned long long seed, const int *ptr, i64 *rows,
+                                                 i64 *cols, double *vals, double *rhs) {
+  const i64 t = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nrows) return;
+  const i64 row = row_lo + t;
+  long long c[27];
+  double v[27], b;
+  const int m = kind == 0 ? wl::poisson27_row(n, row, seed, 0.2, c, v, &b) : wl::momentum3_row(n, row, seed, c, v, &b);
+  const int p = ptr[t];
+  for (int k = 0; k < m; ++k) { rows[p + k] = row; cols[p + k] = c[k]; vals[p + k] = v[k]; }
+  rhs[t] = b;
+}
+}  // namespace
+
+void generate_workload(int kind, int n, i64 row_lo, i64 row_hi, unsigned long long seed, GenOut &out) {
+  ensure_init();
+  B200_REQUIRE(kind == 0 || kind == 1, "generate_workload: kind must be 0 (poisson27_hex) or 1 (momentum3)");
+  const i64 g_rows = (kind == 0 ? 1 : 3) * (i64)n * n * n;
+  B200_REQUIRE(n > 1 && row_lo >= 0 && row_hi < g_rows && row_hi >= row_lo - 1, "generate_workload: bad row range");
+  const i64 nrows = row_hi - row_lo + 1;
+  B200_REQUIRE(nrows * 27 < (1LL << 31) - 8 || kind == 1, "generate_workload: more than 2^31 nonzeros per rank");
+  B200_REQUIRE(nrows * 21 < (1LL << 31) - 8 || kind == 0, "generate_workload: more than 2^31 nonzeros per rank");
+  DVec<int> cnt((size_t)nrows + 1), ptr((size_t)nrows + 1);
+  k_wl_count<<<div_up(nrows + 1, 256), 256, 0, stream()>>>(kind, n, row_lo, nrows, cnt.p);
+  size_t tb = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt.p, ptr.p, (int)(nrows + 1), stream());
+  DVec<char> tmp(tb);
+  cub::DeviceScan::ExclusiveSum(tmp.p, tb, cnt.p, ptr.p, (int)(nrows + 1), stream());
+  int nnz = 0;
+  B200_CUDA(cudaMemcpyAsync(&nnz, ptr.p + nrows, sizeof(int), cudaMemcpyDeviceToHost, stream()));
+  B200_CUDA(cudaStreamSynchronize(stream()));
+  out.nnz = nnz;
+  out.n_local = nrows;
+  out.row_start = row_lo;
+  out.g_rows = g_rows;
+  out.rows.alloc((size_t)std::max(nnz, 1));
+  out.cols.alloc((size_t)std::max(nnz, 1));
+  out.vals.alloc((size_t)std::max(nnz, 1));
+  out.rhs.alloc((size_t)std::max<i64>(nrows, 1));
+  if (nrows > 0) k_wl_fill<<<div_up(nrows, 128), 128, 0, stream()>>>(kind, n, row_lo, nrows, seed, ptr.p, out.rows.p, out.cols.p, out.vals.p, out.rhs.p);
   count_launch(4);
   B200_KERNEL_CHECK();
   B200_CUDA(cudaStreamSynchronize(stream()));

@@ -41,6 +41,23 @@ def generate_laplace(nx, ny, nz, grid=(1, 1, 1), rank=0, stencil=7):
     return DeviceCOO(rows.value, cols.value, vals.value, rhs.value, nnz.value, nloc.value, rs.value, gr.value)
 
 
+WORKLOAD_KINDS = {"poisson27_hex": (0, 20260, 1), "momentum3": (1, 20261, 3)}   # kind id, seed, rows per node
+
+
+def generate_workload(kind, n, i_lower, i_upper):
+    """rows [i_lower, i_upper] of the synthetic systems of BASELINE.json configs[3] / [4], built on the device
+    (csrc/workload_rows.cuh; tests/workloads.py holds the numpy builders of the same matrices)"""
+    L = lib()
+    kid, seed, _ = WORKLOAD_KINDS[kind]
+    rows, cols, vals, rhs = VP(), VP(), VP(), VP()
+    nnz, gr = I64(), I64()
+    L.b200hypre_generate_workload.argtypes = [I32, I32, I64, I64, C.c_ulonglong, C.POINTER(VP), C.POINTER(VP), C.POINTER(VP), C.POINTER(VP),
+                                              C.POINTER(I64), C.POINTER(I64)]
+    check(L.b200hypre_generate_workload(kid, n, i_lower, i_upper, seed, C.byref(rows), C.byref(cols), C.byref(vals), C.byref(rhs),
+                                        C.byref(nnz), C.byref(gr)), "generate_workload")
+    return DeviceCOO(rows.value, cols.value, vals.value, rhs.value, nnz.value, i_upper - i_lower + 1, i_lower, gr.value)
+
+
 DEFAULT_AMG = dict(print_level=0, debug_flag=0, coarsen_type=8, cycle_type=1, relax_type=18, num_sweeps=1, smooth_num_sweeps=1,
                    tolerance=0.0, max_iterations=1, relax_order=0, max_levels=20, strong_threshold=0.25, interp_type=6)
 
@@ -114,6 +131,8 @@ class HypreSystem:
         kind = ls.get("type", "matrix_market")
         if kind in ("build_27pt_stencil", "build_7pt_stencil"):
             self._load_generator(ls, 27 if kind == "build_27pt_stencil" else 7)
+        elif kind in WORKLOAD_KINDS:
+            self._load_workload(ls, kind)
         elif kind == "csr":
             self._load_csr(ls)
         elif kind == "coo":
@@ -143,6 +162,23 @@ class HypreSystem:
         synchronize()
         coo.free()
         self._timer("Build 27Pt Stencil HYPRE matrix", t0)
+
+    def _load_workload(self, ls, kind):
+        """device-generated poisson27_hex / momentum3 system of `n`^3 nodes, block rows per rank (HypreSystem.cpp:525-544)"""
+        from . import block_partition
+        n = int(ls["n"])
+        g_rows = WORKLOAD_KINDS[kind][2] * n ** 3
+        part = block_partition(g_rows, self.nranks)
+        lo, hi = int(part[self.rank]), int(part[self.rank + 1]) - 1
+        t0 = time.perf_counter()
+        coo = generate_workload(kind, n, lo, hi)
+        self.global_rows = g_rows
+        self._init_system(lo, hi)
+        self.A.set_values_ptr(coo.nnz, coo.rows, coo.cols, coo.vals)
+        self.b.set_values_ptr(coo.n_local, 0, coo.rhs)
+        synchronize()
+        coo.free()
+        self._timer("Build HYPRE matrix", t0)
 
     def _load_coo(self, ls):
         """COO triplets (global ids, one entry per 'row') + rhs given as raw HOST or DEVICE addresses: exactly what

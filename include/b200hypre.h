@@ -30,6 +30,13 @@ HYPRE_Int b200hypre_generate_laplace(HYPRE_Int nx, HYPRE_Int ny, HYPRE_Int nz, H
                                      HYPRE_Int rank, HYPRE_Int stencil, HYPRE_BigInt **rows, HYPRE_BigInt **cols,
                                      HYPRE_Complex **vals, HYPRE_Complex **rhs, HYPRE_BigInt *nnz, HYPRE_BigInt *n_local,
                                      HYPRE_BigInt *row_start, HYPRE_BigInt *global_rows);
+/* Synthetic nalu-wind-like systems of BASELINE.json configs[3] / [4] generated on the device: rows [ilower, iupper] of
+ * kind 0 = perturbed-hex 27-point Poisson on n^3 nodes, kind 1 = 3-DOF upwind momentum on n^3 nodes (3 n^3 rows), as COO triplets
+ * (row order, ascending columns) + rhs = A 1; same ownership rule as b200hypre_generate_laplace.  The systems then go through the
+ * IJ interface like the reference's file-loaded systems (HypreSystem.cpp:897-1015). */
+HYPRE_Int b200hypre_generate_workload(HYPRE_Int kind, HYPRE_Int n, HYPRE_BigInt ilower, HYPRE_BigInt iupper, unsigned long long seed,
+                                      HYPRE_BigInt **rows, HYPRE_BigInt **cols, HYPRE_Complex **vals, HYPRE_Complex **rhs,
+                                      HYPRE_BigInt *nnz, HYPRE_BigInt *global_rows);
 void b200hypre_block_partition(HYPRE_BigInt n, HYPRE_Int nranks, HYPRE_BigInt *starts /* nranks + 1 */);  /* HypreSystem.cpp:525-544; host only */
 /* receive side of the halo plan for sorted halo column ids; returns the number of neighbours; host only */
 HYPRE_Int b200hypre_plan_recv(const HYPRE_BigInt *col_map, HYPRE_Int n_halo, const HYPRE_BigInt *col_starts, HYPRE_Int nranks,

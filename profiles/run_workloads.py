@@ -25,7 +25,7 @@ def run(bh, name, linear_system, solver, amg, repeat=2):
     stream = torch.cuda.ExternalStream(bh.stream_ptr())
     best = None
     for k in range(repeat):
-        s = bh.HypreSystem({"linear_system": linear_system, "solver_settings": solver, "boomeramg_settings": amg})
+        s = bh.HypreSystem({"linear_system": linear_system, "solver_settings": solver, "boomeramg_settings": amg}, *RANKS)
         s.setup_precon_and_solver()
         s.load()
         s.assemble_system()
@@ -52,13 +52,19 @@ def run(bh, name, linear_system, solver, amg, repeat=2):
         s.destroy_system()
         if best is None or rec["setup_s"] + rec["solve_s"] < best["setup_s"] + best["solve_s"]:
             best = rec
-    print(json.dumps(best), flush=True)
+    best["pool_high_water_gib"] = round(bh.pool_stats()["used_high"] / 2 ** 30, 1)
+    if RANKS[0] == 0:
+        print(json.dumps(best), flush=True)
 
 
 def main():
     quick = "--quick" in sys.argv
     big = "--big" in sys.argv      # only the two host-built workloads, at the largest size that is practical to build with numpy
+    full = "--full" in sys.argv    # BASELINE.json configs[3] / [4] at their STATED sizes, generated on the device
     import b200hypre as bh
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if full:
+        return run_full_size(bh, world)
     bh.comm_init(0, 1)
     bh.pool_reserve(int((8 if quick else 60) * 2 ** 30))
     from workloads import momentum3, poisson27_hex
@@ -75,6 +81,41 @@ def main():
             sv.update(relax_type=18, relax_order=0, strong_threshold=0.25, max_iterations=100)
         run(bh, f"{method}_{n7}", {"type": "build_7pt_stencil", "nx": n7, "ny": n7, "nz": n7}, sv, {})
     run_host_built(bh, gm, 32 if quick else 144, 24 if quick else 128)
+
+
+def run_full_size(bh, world):
+    """configs[3]: perturbed-hex 27-point Poisson, 368^3 = 49.8 M rows, 1.34 G non-zeros, Chebyshev smoother, one GPU.
+    configs[4]: 3-DOF momentum, 322^3 x 3 = 100.2 M rows, 2.10 G non-zeros -- beyond 32-bit row pointers on one rank, so it runs
+    under torchrun on >= 2 GPUs (block rows per rank); one GPU takes the largest size below 2^31 non-zeros (272^3 x 3 = 60.4 M rows).
+        python profiles/run_workloads.py --full
+        python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 profiles/run_workloads.py --full"""
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+        dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ.get("LOCAL_RANK", rank))))
+        bh.comm_init_torch()
+    else:
+        bh.comm_init(0, 1)
+    gm = {"method": "gmres", "preconditioner": "boomeramg", "tolerance": 1e-8, "kspace": 50, "max_iterations": 400}
+    global RANKS
+    RANKS = (rank, world)
+    if world == 1:
+        run(bh, "poisson27_hex_368 (49.8 M rows, device generated)", {"type": "poisson27_hex", "n": 368}, gm,
+            {"relax_type": 16, "strong_threshold": 0.5}, repeat=1)
+        n = 272
+    else:
+        n = 322
+    tag = f"momentum3_{n} ({3 * n ** 3 / 1e6:.1f} M rows, {world} GPU(s), device generated)"
+    run(bh, tag + " gmres+jacobi", {"type": "momentum3", "n": n}, gm, {"max_levels": 1, "relax_type": 18}, repeat=1)
+    run(bh, tag + " bicg+jacobi", {"type": "momentum3", "n": n}, dict(gm, method="bicg"), {"max_levels": 1, "relax_type": 18}, repeat=1)
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+RANKS = (0, 1)
 
 
 def run_host_built(bh, gm, n_poisson, n_momentum):

@@ -129,3 +129,34 @@ def test_momentum3_cgs2_krylov_dominated(b200):
         assert np.abs(s.solution() - 1.0).max() < 1e-5
         s.destroy_system()
     assert abs(its["mgs"] - its["cgs2"]) <= 1
+
+
+@pytest.mark.parametrize("kind,n", [("poisson27_hex", 9), ("momentum3", 8)])
+def test_device_generated_workload_equals_numpy_builder(b200, kind, n):
+    """BASELINE.json configs[3] / [4] at their stated size are generated on the device (csrc/workload_rows.cuh); at small size
+    the device-generated system, assembled through the IJ path, is the matrix of the numpy builder (momentum: every bit;
+    hex Poisson: up to the summation order of the element contributions), and it solves to x == 1"""
+    import scipy.sparse as sp
+    A, b = poisson27_hex(n) if kind == "poisson27_hex" else momentum3(n)
+    amg = {"relax_type": 16, "strong_threshold": 0.5} if kind == "poisson27_hex" else {"max_levels": 1, "relax_type": 18}
+    s = b200.HypreSystem({"linear_system": {"type": kind, "n": n},
+                          "solver_settings": {"method": "gmres", "preconditioner": "boomeramg", "tolerance": 1e-8, "kspace": 50,
+                                              "max_iterations": 400},
+                          "boomeramg_settings": amg})
+    s.setup_precon_and_solver()
+    s.load()
+    s.assemble_system()
+    ptr, col, val, _ = b200.parcsr_to_host(s.A.object())
+    G = sp.csr_matrix((val, col, ptr), shape=A.shape)
+    G.sort_indices()
+    R = A.tocsr()
+    R.sort_indices()
+    assert np.array_equal(G.indptr, R.indptr) and np.array_equal(G.indices, R.indices)
+    scale = np.abs(R.data).max()
+    if kind == "momentum3":
+        assert np.array_equal(G.data, R.data) and np.array_equal(s.b.get_values(), b)
+    else:
+        assert np.abs(G.data - R.data).max() <= 1e-13 * scale and np.abs(s.b.get_values() - b).max() <= 1e-12 * scale
+    s.solve()
+    assert s.solver.converged == 1 and np.abs(s.solution() - 1.0).max() < 1e-5
+    s.destroy_system()

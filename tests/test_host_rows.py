@@ -52,3 +52,34 @@ def test_interpolation_kernels_use_full_warp_collectives():
         name = b.split("\n", 1)[0]
         assert b.count(" MATCH.") <= 1, f"per-group collective in {name}"
         assert " VOTEU" not in b or b.count(" VOTEU") <= 4, f"vote loop in {name}"
+
+
+@pytest.mark.skipif(shutil.which("nvcc") is None, reason="nvcc not on PATH")
+@pytest.mark.parametrize("kind,n", [("momentum", 5), ("poisson", 5), ("poisson", 3)])
+def test_device_workload_rows_match_numpy_builders(tmp_path, kind, n):
+    """BASELINE.json configs[3] / [4] are generated on the device at their stated sizes by the row functions of
+    csrc/workload_rows.cuh; at small size the same functions, compiled for the host, must give the matrices of the numpy
+    builders in tests/workloads.py (same counter-based random numbers): momentum bit for bit, the hex Poisson matrix up to the
+    summation order of the element contributions (1e-13)"""
+    import numpy as np
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import workloads
+    exe = tmp_path / "workload_rows"
+    subprocess.check_call(["nvcc", "-std=c++17", "-O1", "-fmad=false", "-Wno-deprecated-gpu-targets", "-I", CSRC, "-o", str(exe),
+                           os.path.join(ROOT, "tests", "host", "workload_rows.cu")])
+    seed = 20261 if kind == "momentum" else 20260
+    out = subprocess.run([str(exe), kind, str(n), str(seed)], capture_output=True, text=True, check=True).stdout.splitlines()
+    ent = np.array([[float(t) for t in l.split()] for l in out if not l.startswith("b")])
+    rhs = np.array([float(l.split()[2]) for l in out if l.startswith("b")])
+    A, b = (workloads.momentum3(n) if kind == "momentum" else workloads.poisson27_hex(n))
+    A = A.tocsr()
+    A.sort_indices()
+    coo = A.tocoo()
+    assert len(ent) == A.nnz
+    assert np.array_equal(ent[:, 0].astype(np.int64), coo.row) and np.array_equal(ent[:, 1].astype(np.int64), coo.col)
+    if kind == "momentum":
+        assert np.array_equal(ent[:, 2], coo.data) and np.array_equal(rhs, b)
+    else:
+        assert np.abs(ent[:, 2] - coo.data).max() <= 1e-13 * np.abs(coo.data).max()
+        assert np.abs(rhs - b).max() <= 1e-12 * np.abs(coo.data).max()

@@ -6,14 +6,27 @@ TEST / BENCH INPUT GENERATORS ONLY (numpy + scipy on the host); the product read
 
 * poisson27_hex(n): nalu-wind-like pressure Poisson.  Trilinear-hexahedron Galerkin Laplacian (2x2x2 Gauss) on the
   n^3 interior nodes of an (n+2)^3 grid with homogeneous Dirichlet boundary; interior nodes displaced by
-  0.2 h U(-1,1) (default_rng(20260)).  27-point stencil, nnz = (3n-2)^3, symmetric positive definite, positive and
+  0.2 h U(-1,1) (counter-based generator, seed 20260).  27-point stencil, nnz = (3n-2)^3, symmetric positive definite, positive and
   negative off-diagonals.  rhs = A 1.
 * momentum3(n): nalu-wind-like momentum.  n^3 nodes x 3 DOF, node-blocked 3x3, 7-point first-order upwind
-  advection-diffusion at cell Peclet 2 with velocity (1, 0.5, 0.25) + 0.1 U(-1,1) (default_rng(20261)), a time term
+  advection-diffusion at cell Peclet 2 with velocity (1, 0.5, 0.25) + 0.1 U(-1,1) (counter-based generator, seed 20261), a time term
   on the diagonal, and a weak constant inter-component coupling.  Nonsymmetric, nnz = 9 (7 n^3 - 6 n^2).  rhs = A 1.
 """
 import numpy as np
 import scipy.sparse as sp
+
+
+def uniform_pm1(seed, idx):
+    """U[-1, 1) as a pure function of (seed, index): splitmix64 finaliser, top 53 bits.  The same generator as
+    hypre-mini-app_b200/csrc/workload_rows.cuh (wl::uniform_pm1), so that the device generators of these systems and the numpy
+    builders below produce the same matrices."""
+    idx = np.asarray(idx, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        z = np.full(idx.shape, (int(seed) + 1) * 0x9E3779B97F4A7C15 % 2 ** 64, dtype=np.uint64) + idx * np.uint64(0xD1B54A32D192ED03)
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        z = z ^ (z >> np.uint64(31))
+    return 2.0 * ((z >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)) - 1.0
 
 
 def _hex_element_matrices(X):
@@ -44,8 +57,7 @@ def poisson27_hex(n, seed=20260, jitter=0.2):
     ax = np.arange(m) * h
     Z, Y, Xc = np.meshgrid(ax, ax, ax, indexing="ij")  # node id = (k * m + j) * m + i
     xyz = np.stack([Xc, Y, Z], axis=-1)
-    rng = np.random.default_rng(seed)
-    disp = jitter * h * rng.uniform(-1.0, 1.0, size=(n, n, n, 3))
+    disp = jitter * h * uniform_pm1(seed, np.arange(3 * n ** 3)).reshape(n, n, n, 3)   # [k][j][i][xyz]
     xyz[1:-1, 1:-1, 1:-1, :] += disp
     xyz = xyz.reshape(-1, 3)
     e = np.arange(m - 1)
@@ -68,9 +80,8 @@ def poisson27_hex(n, seed=20260, jitter=0.2):
 
 
 def momentum3(n, seed=20261, peclet=2.0, coupling=0.05, time_term=0.5):
-    rng = np.random.default_rng(seed)
     u0 = np.array([1.0, 0.5, 0.25])
-    vel = u0[None, :] + 0.1 * rng.uniform(-1.0, 1.0, size=(n ** 3, 3))
+    vel = u0[None, :] + 0.1 * uniform_pm1(seed, np.arange(3 * n ** 3)).reshape(n ** 3, 3)
     nu = np.linalg.norm(u0) / peclet  # h = 1
     idx = np.arange(n ** 3)
     i, j, k = idx % n, (idx // n) % n, idx // (n * n)
