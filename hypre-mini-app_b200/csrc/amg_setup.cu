@@ -84,16 +84,6 @@ __global__ void k_pmis_init(int n, const int *Sptr, const int *cnt, int seed, i6
   if (m < 1.0) { cf[i] = -1; measure[i] = 0.0; }
   else { cf[i] = 0; measure[i] = m; }
 }
-__global__ void k_count_undecided(int n, const int *cf, int *counter) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  int u = (i < n && cf[i] == 0) ? 1 : 0;
-  unsigned b = __ballot_sync(0xffffffffu, u);
-  if ((threadIdx.x & 31) == 0 && b) atomicAdd(counter, __popc(b));
-}
-__global__ void k_is_init(int n, const int *cf, const double *measure, signed char *is) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) is[i] = (cf[i] == 0 && measure[i] > 1.0) ? 1 : 0;
-}
 __global__ void k_is_knock(int n, const int *Sptr, const int *Scol, const double *measure, const int *cf, signed char *is) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) rows::pmis_knock_row(Sptr, Scol, measure, cf, is, i);
@@ -102,13 +92,25 @@ __global__ void k_set_c(int n, const signed char *is, int *cf) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n && is[i]) cf[i] = 1;
 }
-__global__ void k_set_f(int n, const int *Sptr, const int *Scol, int *cf) {
+// end of a PMIS sweep in one pass over the rows: an undecided point that strongly depends on a C point becomes F
+// (pmis_setf_row), decided points leave the graph (measure := 0), the points still undecided are counted, and the candidate flag
+// of the next sweep's independent-set selection is written (is = undecided and measure > 1).  Row i only reads the markers of
+// its neighbours, which this kernel changes from 0 to -1 at most -- invisible to the test `> 0` -- so one pass is race free.
+__global__ void k_pmis_finish_sweep(int n, const int *Sptr, const int *Scol, int *cf, double *measure, signed char *is, int *counter) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) rows::pmis_setf_row(Sptr, Scol, cf, i);
-}
-__global__ void k_clear_measure(int n, const int *cf, double *measure) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n && cf[i] != 0) measure[i] = 0.0;
+  int und = 0;
+  if (i < n) {
+    int c = cf[i];
+    if (c == 0) {
+      for (int k = Sptr[i]; k < Sptr[i + 1]; ++k)
+        if (cf[Scol[k]] > 0) { c = -1; break; }
+      if (c != 0) cf[i] = c;
+    }
+    if (c != 0) { measure[i] = 0.0; is[i] = 0; }
+    else { und = 1; is[i] = (measure[i] > 1.0) ? 1 : 0; }
+  }
+  unsigned b = __ballot_sync(0xffffffffu, und);
+  if ((threadIdx.x & 31) == 0 && b) atomicAdd(counter, __popc(b));
 }
 __global__ void k_c_flags(int n, const int *cf, int *flag) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -305,19 +307,21 @@ bool coarsen_level(Amg &amg, AmgLevel &L, AmgLevel &Lc) {
     DVec<signed char> is((size_t)n);
     DVec<int> counter(1);
     count_launch(2);
+    // sweep = knock-out (independent set among the candidates) -> selected points become C -> k_pmis_finish_sweep.
+    // The count of undecided points and the candidate flags of the first sweep come from the same kernel run on the
+    // initial markers (no C point yet, so it decides nothing).
+    counter.zero();
+    k_pmis_finish_sweep<<<g, 256, 0, stream()>>>(n, L.Sptr.p, L.Scol.p, L.cf_raw.p, measure.p, is.p, counter.p);
+    count_launch();
     for (int sweep = 0; sweep < 10000; ++sweep) {
-      counter.zero();
-      k_count_undecided<<<g, 256, 0, stream()>>>(n, L.cf_raw.p, counter.p);
       i64 und = fetch(counter.p);
       allreduce_sum_host_i64(&und, 1);
-      count_launch();
       if (und == 0) break;
-      k_is_init<<<g, 256, 0, stream()>>>(n, L.cf_raw.p, measure.p, is.p);
       k_is_knock<<<g, 256, 0, stream()>>>(n, L.Sptr.p, L.Scol.p, measure.p, L.cf_raw.p, is.p);
       k_set_c<<<g, 256, 0, stream()>>>(n, is.p, L.cf_raw.p);
-      k_set_f<<<g, 256, 0, stream()>>>(n, L.Sptr.p, L.Scol.p, L.cf_raw.p);
-      k_clear_measure<<<g, 256, 0, stream()>>>(n, L.cf_raw.p, measure.p);
-      count_launch(5);
+      counter.zero();
+      k_pmis_finish_sweep<<<g, 256, 0, stream()>>>(n, L.Sptr.p, L.Scol.p, L.cf_raw.p, measure.p, is.p, counter.p);
+      count_launch(3);
     }
     B200_KERNEL_CHECK();
     // coarse numbering: exclusive scan of the C flags

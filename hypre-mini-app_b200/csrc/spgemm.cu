@@ -254,8 +254,6 @@ __device__ __forceinline__ void spgemm_row(const rows::Csr &A, const rows::Csr &
       }
     }
     gsync<G>(mask);
-    if (nnz_out != nullptr && lane == 0 && row >= 0) nnz_out[row] = *cnt;   // single-pass mode: the length is only known now
-    gsync<G>(mask);
     return;
   }
   // compaction; the list holds sort keys (the diagonal column becomes -1 so that it ranks first)
@@ -284,7 +282,6 @@ __device__ __forceinline__ void spgemm_row(const rows::Csr &A, const rows::Csr &
     Ccol[base + rank] = (key == -1) ? diag_col : key;
     Cval[base + rank] = lv[t];
   }
-  if (nnz_out != nullptr && lane == 0 && row >= 0) nnz_out[row] = n;   // single-pass mode
   gsync<G>(mask);
   }
 }
@@ -481,15 +478,6 @@ void exclusive_scan(const T *in, T *out, i64 n) {
   count_launch(2);
 }
 
-// rows written at their slab positions (sptr, bound-strided) -> CSR positions; G lanes per row, coalesced
-template <int G>
-__global__ void k_compact_rows(int nr, const int *__restrict__ sptr, const int *__restrict__ cptr, const int *__restrict__ scol,
-                               const double *__restrict__ sval, int *__restrict__ ccol, double *__restrict__ cval) {
-  const int i = (int)(((i64)blockIdx.x * blockDim.x + threadIdx.x) / G), lane = threadIdx.x % G;
-  if (i >= nr) return;
-  const int b = cptr[i], n = cptr[i + 1] - b, sb = sptr[i];
-  for (int k = lane; k < n; k += G) { ccol[b + k] = scol[sb + k]; cval[b + k] = sval[sb + k]; }
-}
 __global__ void k_sum_i64(const int *__restrict__ v, i64 n, unsigned long long *out) {
   unsigned long long s = 0;
   for (i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (i64)gridDim.x * blockDim.x) s += (unsigned long long)v[k];
@@ -557,46 +545,10 @@ void csr_spgemm(const DCsr &A, const DCsr &B, DCsr &C, bool diag_first, bool sor
   DVec<int> bound((size_t)A.nr + 1), nnz_row((size_t)A.nr + 1);
   nnz_row.zero();
   B200_CUDA(cudaMemsetAsync(bound.p + A.nr, 0, sizeof(int), stream()));
-  // product-count bound per row and its total
-  unsigned long long total_b = 0;
-  {
-    k_spgemm_bound<<<div_up(A.nr, 256), 256, 0, stream()>>>(rv(A), rv(B), bound.p);
-    DVec<unsigned long long> acc(1);
-    acc.zero();
-    k_sum_i64<<<std::min<int>(div_up(A.nr, 256), 4 * ctx().sm_count), 256, 0, stream()>>>(bound.p, A.nr, acc.p);
-    count_launch(2);
-    B200_CUDA(cudaMemcpyAsync(&total_b, acc.p, sizeof(total_b), cudaMemcpyDeviceToHost, stream()));
-    B200_CUDA(cudaStreamSynchronize(stream()));
-  }
-  // ONE pass when the bound is close to the result: every row is accumulated in a table sized by its bound and written at a
-  // bound-strided slab position, a coalesced copy then packs the rows -- no symbolic pass.  That is the intermediate product
-  // Q = A P (row of A x at most P_max_elmts entries per P row: bound <= 28 for the 7-point level 0) and R Q on the levels where
-  // the rows of R are short (mean bound <= 256; on the coarser levels the bound is 10-30x the row length and the counting pass
-  // with its small optimistic tables is the cheaper way to size the hash tables).
-  const double mean_b = (double)total_b / std::max(A.nr, 1);
-  const bool fused = total_b < 2147483640ull && (double)total_b * 12.0 < 24e9 && (!sorted || mean_b <= 256.0);
-  if (fused) {
-    ProfScope prof("spgemm_fused", in_bytes + 4.0 * A.nr);
-    DVec<int> sptr((size_t)A.nr + 1), scol((size_t)std::max<unsigned long long>(total_b, 1));
-    DVec<double> sval((size_t)std::max<unsigned long long>(total_b, 1));
-    exclusive_scan(bound.p, sptr.p, (i64)A.nr + 1);
-    Bins bins;
-    BinLimits L{{16, 32, 64, 128, 256, 1024, 4096}};
-    make_bins(A.nr, bound.p, L, bins);
-    spgemm_pass<true>(A, B, bins, L, sptr.p, scol.p, sval.p, nnz_row.p, diag_first, sorted);
-    C.nnz = checked_total(nnz_row.p, C.nr, "csr_spgemm");
-    exclusive_scan(nnz_row.p, C.ptr.p, (i64)C.nr + 1);
-    C.col.alloc((size_t)std::max<i64>(C.nnz, 1));
-    C.val.alloc((size_t)std::max<i64>(C.nnz, 1));
-    const int G = (C.nr > 0 && (double)C.nnz / C.nr > 12.0) ? 32 : 8;
-    if (G == 8) k_compact_rows<8><<<div_up((i64)C.nr * 8, 256), 256, 0, stream()>>>(C.nr, sptr.p, C.ptr.p, scol.p, sval.p, C.col.p, C.val.p);
-    else k_compact_rows<32><<<div_up((i64)C.nr * 32, 256), 256, 0, stream()>>>(C.nr, sptr.p, C.ptr.p, scol.p, sval.p, C.col.p, C.val.p);
-    count_launch();
-    B200_KERNEL_CHECK();
-    return;
-  }
   {
     ProfScope prof("spgemm_symbolic", in_bytes + 4.0 * A.nr);
+    k_spgemm_bound<<<div_up(A.nr, 256), 256, 0, stream()>>>(rv(A), rv(B), bound.p);
+    count_launch();
     Bins bins;
     BinLimits L{{16, 32, 64, 128, 512, 2048, 16384}};
     make_bins(A.nr, bound.p, L, bins);
