@@ -5,6 +5,11 @@
 //
 // G lanes own one row; 256 / G rows per block.  What changed against the first kernel (profiles/r01_interp_sass_notes.md:
 // 6 078 warp instructions per row on level 1, control-flow bound):
+//   * the walks run over C-COMPRESSED rows.  Of the row of a distributed neighbour j only the entries whose column is a C
+//     point can be in C-hat_i, plus the one back-edge a_ji; of its strength row only the C entries can enter C-hat_i.  Those
+//     are 14-31 % of the entries, so the tier driver builds, once per level and for F rows only, copies of A and S restricted
+//     to C columns (CComp: original entry positions kept, they define the summation order) and the back-edge is found by a
+//     binary search per neighbour (own rows are sorted by column after the diagonal; fetched halo rows are scanned);
 //   * no per-neighbour warp loop.  The work of one row is a list of ITEMS -- (strong neighbour t, entry s of its strength
 //     row) in the discovery, (distributed neighbour t, entry s of its matrix row) in the weights -- and the lanes take G
 //     consecutive items per round, so every round is a coalesced load + one hash probe at full lane occupancy;
@@ -26,8 +31,15 @@
 namespace flat {
 
 constexpr int MARK = 255;      // hash position of a strong F neighbour of i (not a C-hat slot)
-constexpr int DIAGSLOT = 254;  // staged contribution that goes to the diagonal (the neighbour's entry in column i)
 constexpr unsigned FULL = 0xffffffffu;
+
+// C-compressed copies of the level matrix and of the strength pattern (rows of non-isolated F points only, other rows empty):
+// entry e of row j of AC is the entry acpos[e] of A (acpos ascending inside a row), whose column accol[e] is a C point.
+struct CComp {
+  const int *acptr, *accol, *acpos;
+  const double *acval;
+  const int *scptr, *sccol;
+};
 
 template <int G, int H, int CAP, int STG>
 struct alignas(8) Grp {
@@ -41,6 +53,7 @@ struct alignas(8) Grp {
   int tb[G];
   int tcnt[G];
   int tseg[G];
+  int stg_k[STG];
   int L, nout, row, flags;     // flags: 1 = any_off, 2 = F row with weights computed (truncate + write), 4 = write len only
   unsigned char spos[H];
   unsigned char stg_slot[STG];
@@ -102,7 +115,7 @@ __device__ __forceinline__ int gscan_incl(int v, int gl) {
 template <int G, int H, int CAP, int STG, int MODE>
 __global__ void __launch_bounds__(256, 4)
 k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__ Scol, const signed char *__restrict__ Scf,
-              const int *__restrict__ cf, const int *__restrict__ f2c, int n_own, int n_rows, double tf, int pmax, int lo, int *lraw,
+              CComp cc, const int *__restrict__ cf, const int *__restrict__ f2c, int n_own, int n_rows, double tf, int pmax, int lo, int *lraw,
               int *len, const int *__restrict__ Pptr, int *Pcol, double *Pval, const int *__restrict__ row_list,
               int slot0, int *scr_c, double *scr_v, unsigned long long *tstats) {
   using GS = Grp<G, H, CAP, STG>;
@@ -171,7 +184,7 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
       const bool isF = valid && c1 < 0 && c1 != -3;
       int b2 = 0, n_t = 0;
       if (isC) { b2 = ~i1; n_t = 1; }                                 // the item is the neighbour itself
-      else if (isF) { b2 = Sptr[i1]; n_t = Sptr[i1 + 1] - b2; }       // the items are its strength row
+      else if (isF) { b2 = cc.scptr[i1]; n_t = cc.scptr[i1 + 1] - b2; }   // the items are the C entries of its strength row
       const unsigned fmk = gballot<G>(isF, gbase);
       if (L + nmark + __popc(fmk) > HMAX) ovf = true;
       if (isF && !ovf) insert<H>(S.keys, S.spos, i1, MARK);
@@ -192,7 +205,7 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
           while (item >= S.noff[tp + 1]) ++tp;
           const int bb = S.tb[tp];
           if (bb < 0) { key = ~bb; cand = true; }
-          else { const int idx = bb + (item - S.noff[tp]); key = Scol[idx]; cand = Scf[idx] >= 0; }
+          else { key = cc.sccol[bb + (item - S.noff[tp])]; cand = true; }
         }
         const bool nw = cand && (probe<H>(S.keys, S.spos, key) < 0);
         const unsigned long long mkey = nw ? (((unsigned long long)(unsigned)g << 32) | (unsigned)key)
@@ -270,9 +283,9 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
     // one entry of row i per lane (tag = lane): classification
     const int jj = ab + 1 + c * G + gl;
     const bool valid = active && jj < ae;
-    int kind = 3, pr = -1, b1 = 0, n_t = 0;
+    int kind = 3, pr = -1, b1 = 0, n_t = 0, kb = -1;   // kb: position of the back-edge a_{i1,i} in A (-1: none / wrong sign)
     bool neg = false;
-    double aij = 0.0;
+    double aij = 0.0, ab_val = 0.0;
     if (valid) {
       const int i1 = A.col[jj];
       aij = A.val[jj];
@@ -280,13 +293,31 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
       if (pr >= 0 && pr != MARK) kind = 0;                    // direct: a_ij goes to its own C point
       else if (pr == MARK) {                                   // strong F neighbour: distributed over C-hat and i
         kind = 1;
-        b1 = A.ptr[i1];
-        n_t = A.ptr[i1 + 1] - b1 - 1;
-        neg = A.val[b1] < 0;
+        const int rb = A.ptr[i1], re = A.ptr[i1 + 1];
+        b1 = cc.acptr[i1];
+        n_t = cc.acptr[i1 + 1] - b1;
+        neg = A.val[rb] < 0;
+        // back-edge a_{i1,i}: entries after the diagonal are sorted by column in own rows, in storage order of the owner in
+        // fetched halo rows
+        if (i1 < n_own) {
+          int lo_k = rb + 1, hi_k = re;
+          while (lo_k < hi_k) {
+            const int mid = (lo_k + hi_k) >> 1;
+            if (A.col[mid] < i) lo_k = mid + 1; else hi_k = mid;
+          }
+          if (lo_k < re && A.col[lo_k] == i) kb = lo_k;
+        } else {
+          for (int k = rb + 1; k < re; ++k)
+            if (A.col[k] == i) { kb = k; break; }
+        }
+        if (kb >= 0) {
+          ab_val = A.val[kb];
+          if (!(neg ? (ab_val > 0) : (ab_val < 0))) kb = -1;   // wrong sign: does not take part
+        }
       } else if (cf[i1] != -3) kind = 2;                       // lumped into the diagonal
     }
     const int ntag = active ? max(0, min(G, na - c * G)) : 0;
-    S.tb[gl] = b1 + 1;
+    S.tb[gl] = b1;
     S.tneg[gl] = neg ? 1 : 0;
     S.tkind[gl] = (unsigned char)kind;
     int lo_t = 0, rlen = G;   // tag range of the current attempt: [lo_t, lo_t + rlen)
@@ -311,18 +342,15 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
         bool contrib = false;
         int sl = 0;
         double a = 0.0;
+        int kpos = 0;
         if (item < T) {
           while (item >= S.noff[tp + 1]) ++tp;
-          const int j1 = S.tb[tp] + (item - S.noff[tp]);
-          const int i2 = A.col[j1];
-          a = A.val[j1];
+          const int e1 = S.tb[tp] + (item - S.noff[tp]);
+          a = cc.acval[e1];
           const bool ok = S.tneg[tp] ? (a > 0) : (a < 0);
           if (ok) {
-            if (i2 == i) { contrib = true; sl = DIAGSLOT; }
-            else {
-              const int p2 = probe<H>(S.keys, S.spos, i2);
-              if (p2 >= 0 && p2 != MARK) { contrib = true; sl = p2; }
-            }
+            const int p2 = probe<H>(S.keys, S.spos, cc.accol[e1]);
+            if (p2 >= 0 && p2 != MARK) { contrib = true; sl = p2; kpos = cc.acpos[e1]; }
           }
         }
         const unsigned cm = gballot<G>(contrib, gbase);
@@ -332,8 +360,9 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
           const int e = nstg + __popc(cm & ltm);
           S.stg_slot[e] = (unsigned char)sl;
           S.stg_a[e] = a;
+          S.stg_k[e] = kpos;
           atomicAdd(&S.tcnt[tp], 1);
-          if (sl != DIAGSLOT) atomicOr(&S.smask[sl], 1u << tp);
+          atomicOr(&S.smask[sl], 1u << tp);
         }
         nstg += cn;
       }
@@ -346,16 +375,17 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
       bool hasd = false;
       if (commit && in) {
         if (kind == 1) {
-          double sum = 0.0, ai = 0.0;
-          bool hasi = false;
+          // denominator: contributing entries of the neighbour row in storage order; the back-edge joins at its position
+          double sum = 0.0;
+          bool pending = (kb >= 0);
           for (int e = seg; e < seg + cnt_t; ++e) {
-            const double a = S.stg_a[e];
-            sum = sum + a;
-            if (S.stg_slot[e] == DIAGSLOT) { ai = a; hasi = true; }
+            if (pending && kb < S.stg_k[e]) { sum = sum + ab_val; pending = false; }
+            sum = sum + S.stg_a[e];
           }
+          if (pending) sum = sum + ab_val;
           if (sum != 0.0) {
             tv = aij / sum;
-            if (hasi) { dterm = tv * ai; hasd = true; }
+            if (kb >= 0) { dterm = tv * ab_val; hasd = true; }
           } else { dterm = aij; hasd = true; }
         } else if (kind == 0) tv = aij;
         else if (kind == 2) { dterm = aij; hasd = true; }
@@ -488,11 +518,18 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
 }
 
 // Deferred truncation (MODE 2): one thread per row on the raw lists the row kernel left in the scratch arrays.  The sums and
-// hypre's qsort2abs are sequential per row by definition; here 32 rows advance per warp instruction and 64 warps per SM
-// hide the dependent-load latency, instead of one lane of a group (or one warp of a block) working alone.
-__global__ void __launch_bounds__(256)
+// hypre's qsort2abs are sequential per row by definition; here 32 rows advance per warp instruction, instead of one lane of a
+// group (or one warp of a block) working alone.  Lists of up to TRUNC_STAGE entries (nearly all) are sorted in shared memory
+// (row stride TRUNC_STAGE + 1: lanes that touch the same entry index hit different banks); longer ones in the global scratch.
+// The first version worked on the global scratch only and was bound by dependent L1 / L2 loads (ncu: long scoreboard 64
+// cycles per issue, profiles/r02b_trunc_ncu_summary.txt).
+constexpr int TRUNC_STAGE = 32;
+constexpr int TRUNC_THREADS = 96;    // 96 x 33 x 12 B = 38 KB of static shared memory, 5 blocks per SM
+__global__ void __launch_bounds__(TRUNC_THREADS)
 k_interp_trunc(int slot0, int slot_end, const int *__restrict__ row_list, int cap, int *scr_c, double *scr_v, const int *__restrict__ lraw,
                int *len, const int *__restrict__ f2c, int n_own, double tf, int pmax, int *Pcol, double *Pval) {
+  __shared__ double s_v[TRUNC_THREADS][TRUNC_STAGE + 1];
+  __shared__ int s_c[TRUNC_THREADS][TRUNC_STAGE + 1];
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const int slot = slot0 + t;
   if (slot >= slot_end) return;
@@ -500,9 +537,16 @@ k_interp_trunc(int slot0, int slot_end, const int *__restrict__ row_list, int ca
   const int pend = len[i];
   if (pend >= 0) return;
   const bool any_off = (pend == -2);
+  int n_out = lraw[i];
   int *lc = scr_c + (size_t)t * cap;
   double *lv = scr_v + (size_t)t * cap;
-  int n_out = lraw[i];
+  if (n_out <= TRUNC_STAGE) {
+    int *sc = s_c[threadIdx.x];
+    double *sv = s_v[threadIdx.x];
+    for (int k = 0; k < n_out; ++k) { sc[k] = lc[k]; sv[k] = lv[k]; }
+    lc = sc;
+    lv = sv;
+  }
   if (tf > 0.0 && n_out > 0) {
     double max_coef = 0.0, row_sum = 0.0, scale = 0.0;
     for (int k = 0; k < n_out; ++k) { const double a = fabs(lv[k]); max_coef = (a > max_coef) ? a : max_coef; }
