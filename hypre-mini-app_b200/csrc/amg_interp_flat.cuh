@@ -46,6 +46,7 @@ struct alignas(8) Grp {
   double lv[CAP];
   double stg_a[STG];
   double tval[G];
+  double tdv[G];
   int keys[H];
   int lc[CAP];
   unsigned smask[CAP];
@@ -98,6 +99,16 @@ __device__ __forceinline__ unsigned gballot(bool pred, int gbase) {
   const unsigned b = __ballot_sync(FULL, pred);
   if (G >= 32) return b;
   return (b >> gbase) & ((1u << (G & 31)) - 1u);
+}
+// tag of an item: the last t with noff[t] <= item (noff[0 .. G] exclusive offsets, non-decreasing, item < noff[G]).  Binary
+// search: log2 G shared-memory reads, whatever the number of empty tags in between
+template <int G>
+__device__ __forceinline__ int tag_of(const int *noff, int item) {
+  int t = 0;
+#pragma unroll
+  for (int step = G >> 1; step > 0; step >>= 1)
+    if (noff[t + step] <= item) t += step;
+  return t;
 }
 // inclusive scan over the G lanes of a group (full-warp shuffle, width G)
 template <int G>
@@ -196,13 +207,12 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
       S.tb[gl] = b2;
       __syncwarp(FULL);
       const int Tmax = __reduce_max_sync(FULL, T);
-      int tp = 0;
       for (int base = 0; base < Tmax; base += G) {
         const int item = base + gl;
         int key = -1;
         bool cand = false;
         if (item < T && !ovf) {
-          while (item >= S.noff[tp + 1]) ++tp;
+          const int tp = tag_of<G>(S.noff, item);
           const int bb = S.tb[tp];
           if (bb < 0) { key = ~bb; cand = true; }
           else { key = cc.sccol[bb + (item - S.noff[tp])]; cand = true; }
@@ -335,16 +345,16 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
       if (in && kind == 0) atomicOr(&S.smask[pr], 1u << gl);
       // walk: G consecutive items per round
       const int Tmax = __reduce_max_sync(FULL, T);
-      int nstg = 0, tp = 0;
+      int nstg = 0;
       bool sovf = false;
       for (int base = 0; base < Tmax; base += G) {
         const int item = base + gl;
         bool contrib = false;
         int sl = 0;
         double a = 0.0;
-        int kpos = 0;
+        int kpos = 0, tp = 0;
         if (item < T) {
-          while (item >= S.noff[tp + 1]) ++tp;
+          tp = tag_of<G>(S.noff, item);
           const int e1 = S.tb[tp] + (item - S.noff[tp]);
           a = cc.acval[e1];
           const bool ok = S.tneg[tp] ? (a > 0) : (a < 0);
@@ -412,13 +422,14 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
           S.lv[p] = acc;
         }
       }
-      // diagonal: at most one term per tag, in tag order
-      const unsigned hm = gballot<G>(hasd, gbase);
-      const unsigned hall = __reduce_or_sync(FULL, hm);
-      const int tend = hall ? (32 - __clz(hall)) : 0;
-      for (int t = 0; t < tend; ++t) {
-        const double d = __shfl_sync(FULL, dterm, t, G);
-        if ((hm >> t) & 1u) diagonal = diagonal + d;
+      // diagonal: at most one term per tag, in tag order; every lane of the group keeps the same running value
+      unsigned hm = gballot<G>(hasd, gbase);
+      S.tdv[gl] = dterm;
+      __syncwarp(FULL);
+      while (hm) {
+        const int t = __ffs(hm) - 1;
+        hm &= hm - 1;
+        diagonal = diagonal + S.tdv[t];
       }
       if (run) {
         if (!sovf) lo_t += rlen;
