@@ -107,7 +107,7 @@ __global__ void k_compact_p(int n_rows, int pmax, const int *__restrict__ lraw, 
   for (int k = 0; k < n; ++k) { Pcol[b + k] = tcol[src + k]; Pval[b + k] = tval[src + k]; }
 }
 
-// tiers: (G, H, CAP, STG) = (8, 64, 32, 64) when strength rows are short, then (32, 256, 128, 192)
+// tiers: (G, H, CAP, STG) = (8, 64, 32, 48) when strength rows are short, then (32, 256, 128, 192)
 template <int G, int H, int CAP, int STG, int MODE>
 void launch_flat(int grid_rows, const rows::Csr &A, const int *Sptr, const int *Scol, const signed char *Scf, const int *cf, const int *f2c,
                  int n_own, int n_rows, double tf, int pmax, int lo, int *lraw, int *len, const int *Pptr, int *Pcol, double *Pval,
@@ -156,7 +156,7 @@ template <int MODE, bool SMALL>
 void launch_one(int grid_rows, const rows::Csr &A, const int *Sptr, const int *Scol, const signed char *Scf, const int *cf, const int *f2c,
                 int n_own, int n_rows, double tf, int pmax, int lo, int *lraw, int *len, const int *Pptr, int *Pcol, double *Pval,
                 const int *list) {
-  if (SMALL) launch_flat<8, 64, 32, 64, MODE>(grid_rows, A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw, len, Pptr, Pcol, Pval, list);
+  if (SMALL) launch_flat<8, 64, 32, 48, MODE>(grid_rows, A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw, len, Pptr, Pcol, Pval, list);
   else launch_flat<32, 256, 128, 192, MODE>(grid_rows, A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw, len, Pptr, Pcol, Pval, list);
 }
 

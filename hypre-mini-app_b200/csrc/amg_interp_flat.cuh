@@ -46,15 +46,15 @@ struct alignas(8) Grp {
   double lv[CAP];
   double stg_a[STG];
   double tval[G];
-  double tdv[G];
   int keys[H];
   int lc[CAP];
   unsigned smask[CAP];
   int noff[G + 1];
   int tb[G];
+  int trb[G];
   int tcnt[G];
-  int tseg[G];
-  int stg_k[STG];
+  unsigned short tseg[G];
+  unsigned short stg_k[STG];   // position of the staged entry inside its row of A (rows of 65535+ entries take the fallback)
   int L, nout, row, flags;     // flags: 1 = any_off, 2 = F row with weights computed (truncate + write), 4 = write len only
   unsigned char spos[H];
   unsigned char stg_slot[STG];
@@ -293,8 +293,8 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
     // one entry of row i per lane (tag = lane): classification
     const int jj = ab + 1 + c * G + gl;
     const bool valid = active && jj < ae;
-    int kind = 3, pr = -1, b1 = 0, n_t = 0, kb = -1;   // kb: position of the back-edge a_{i1,i} in A (-1: none / wrong sign)
-    bool neg = false;
+    int kind = 3, pr = -1, b1 = 0, n_t = 0, kb = -1, rb0 = 0;   // kb: position of the back-edge a_{i1,i} inside row i1 (-1: none / wrong sign)
+    bool neg = false, long_row = false;
     double aij = 0.0, ab_val = 0.0;
     if (valid) {
       const int i1 = A.col[jj];
@@ -304,6 +304,7 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
       else if (pr == MARK) {                                   // strong F neighbour: distributed over C-hat and i
         kind = 1;
         const int rb = A.ptr[i1], re = A.ptr[i1 + 1];
+        rb0 = rb;
         b1 = cc.acptr[i1];
         n_t = cc.acptr[i1 + 1] - b1;
         neg = A.val[rb] < 0;
@@ -322,13 +323,19 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
         }
         if (kb >= 0) {
           ab_val = A.val[kb];
+          kb -= rb;                                            // position inside the row, like the staged entries
           if (!(neg ? (ab_val > 0) : (ab_val < 0))) kb = -1;   // wrong sign: does not take part
         }
+        if (re - rb >= 65535) long_row = true;
       } else if (cf[i1] != -3) kind = 2;                       // lumped into the diagonal
     }
     const int ntag = active ? max(0, min(G, na - c * G)) : 0;
     S.tb[gl] = b1;
+    S.trb[gl] = rb0;
     S.tneg[gl] = neg ? 1 : 0;
+    if (__any_sync(FULL, long_row)) {   // 16-bit positions do not reach: the group gives the row to the fallback path
+      if (gballot<G>(long_row, gbase)) { active = false; ovf = true; }
+    }
     S.tkind[gl] = (unsigned char)kind;
     int lo_t = 0, rlen = G;   // tag range of the current attempt: [lo_t, lo_t + rlen)
     while (__any_sync(FULL, active && lo_t < ntag)) {
@@ -360,7 +367,7 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
           const bool ok = S.tneg[tp] ? (a > 0) : (a < 0);
           if (ok) {
             const int p2 = probe<H>(S.keys, S.spos, cc.accol[e1]);
-            if (p2 >= 0 && p2 != MARK) { contrib = true; sl = p2; kpos = cc.acpos[e1]; }
+            if (p2 >= 0 && p2 != MARK) { contrib = true; sl = p2; kpos = cc.acpos[e1] - S.trb[tp]; }
           }
         }
         const unsigned cm = gballot<G>(contrib, gbase);
@@ -370,7 +377,7 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
           const int e = nstg + __popc(cm & ltm);
           S.stg_slot[e] = (unsigned char)sl;
           S.stg_a[e] = a;
-          S.stg_k[e] = kpos;
+          S.stg_k[e] = (unsigned short)kpos;
           atomicAdd(&S.tcnt[tp], 1);
           atomicOr(&S.smask[sl], 1u << tp);
         }
@@ -389,7 +396,7 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
           double sum = 0.0;
           bool pending = (kb >= 0);
           for (int e = seg; e < seg + cnt_t; ++e) {
-            if (pending && kb < S.stg_k[e]) { sum = sum + ab_val; pending = false; }
+            if (pending && kb < (int)S.stg_k[e]) { sum = sum + ab_val; pending = false; }
             sum = sum + S.stg_a[e];
           }
           if (pending) sum = sum + ab_val;
@@ -401,7 +408,7 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
         else if (kind == 2) { dterm = aij; hasd = true; }
       }
       S.tval[gl] = tv;
-      S.tseg[gl] = seg;
+      S.tseg[gl] = (unsigned short)seg;
       __syncwarp(FULL);
       // per C-hat slot: terms in ascending tag order
       if (commit) {
@@ -424,12 +431,13 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
       }
       // diagonal: at most one term per tag, in tag order; every lane of the group keeps the same running value
       unsigned hm = gballot<G>(hasd, gbase);
-      S.tdv[gl] = dterm;
+      __syncwarp(FULL);          // the slot pass has read tval: reuse it for the diagonal terms
+      S.tval[gl] = dterm;
       __syncwarp(FULL);
       while (hm) {
         const int t = __ffs(hm) - 1;
         hm &= hm - 1;
-        diagonal = diagonal + S.tdv[t];
+        diagonal = diagonal + S.tval[t];
       }
       if (run) {
         if (!sovf) lo_t += rlen;
