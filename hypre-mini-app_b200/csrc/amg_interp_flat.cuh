@@ -158,13 +158,38 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
   if (slot < n_rows) i = row_list ? row_list[slot] : slot;
 
   // ---- what is there to do for this row ---------------------------------------------------------------------------------
+  // all header words of the row are requested together (one round trip to memory instead of four dependent ones)
   bool active = false;
+  int h_lraw = 0, h_cf = 1, h_sb = 0, h_se = 0, h_ab = 0, h_ae = 0;
+  if (i >= 0) {
+    h_lraw = lraw[i];
+    h_cf = cf[i];
+    h_sb = Sptr[i];
+    h_se = Sptr[i + 1];
+    h_ab = A.ptr[i];
+    h_ae = A.ptr[i + 1];
+  }
+  // the first chunk of row i and the extents of its neighbour rows do not depend on the discovery: their loads are issued
+  // now and are in flight while C-hat is built (classification after the discovery only adds the hash probe)
+  int p_i1 = -1, p_rb = 0, p_re = 0, p_b1 = 0, p_nt = 0;
+  double p_aij = 0.0;
+  {
+    const int jj = h_ab + 1 + gl;
+    if (i >= 0 && jj < h_ae) {
+      p_i1 = A.col[jj];
+      p_aij = A.val[jj];
+      p_rb = A.ptr[p_i1];
+      p_re = A.ptr[p_i1 + 1];
+      p_b1 = cc.acptr[p_i1];
+      p_nt = cc.acptr[p_i1 + 1] - p_b1;
+    }
+  }
   if (i >= 0) {
     bool todo;
-    if (MODE != 1) todo = (lraw[i] == -1);
-    else { const int l = lraw[i]; todo = (l > lo && l <= CAP); }
+    if (MODE != 1) todo = (h_lraw == -1);
+    else todo = (h_lraw > lo && h_lraw <= CAP);
     if (todo) {
-      const int cfi = cf[i];
+      const int cfi = h_cf;
       if (cfi >= 0) {   // C point: identity row
         if (gl == 0) {
           if (MODE != 1) { lraw[i] = 0; len[i] = 1; }
@@ -184,7 +209,7 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
   int L = 0, nmark = 0;
   bool ovf = false, any_off = false;
   {
-    const int sb = active ? Sptr[i] : 0, se = active ? Sptr[i + 1] : 0;
+    const int sb = active ? h_sb : 0, se = active ? h_se : 0;
     const int nchunk = __reduce_max_sync(FULL, (se - sb + G - 1) / G);
     for (int c = 0; c < nchunk; ++c) {
       const int kk = sb + c * G + gl;
@@ -284,7 +309,7 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
 
   // ---- weights ------------------------------------------------------------------------------------------------------------
   for (int k = gl; k < CAP; k += G) S.lv[k] = 0.0;
-  const int ab = active ? A.ptr[i] : 0, ae = active ? A.ptr[i + 1] : 0;
+  const int ab = active ? h_ab : 0, ae = active ? h_ae : 0;
   double diagonal = active ? A.val[ab] : 1.0;
   const int na = active ? (ae - ab - 1) : 0;
   const int nchunkA = __reduce_max_sync(FULL, (na + G - 1) / G);
@@ -297,16 +322,21 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
     bool neg = false, long_row = false;
     double aij = 0.0, ab_val = 0.0;
     if (valid) {
-      const int i1 = A.col[jj];
-      aij = A.val[jj];
+      int i1, rb, re;
+      if (c == 0) { i1 = p_i1; aij = p_aij; rb = p_rb; re = p_re; b1 = p_b1; n_t = p_nt; }
+      else {
+        i1 = A.col[jj];
+        aij = A.val[jj];
+        rb = A.ptr[i1];
+        re = A.ptr[i1 + 1];
+        b1 = cc.acptr[i1];
+        n_t = cc.acptr[i1 + 1] - b1;
+      }
       pr = probe<H>(S.keys, S.spos, i1);
       if (pr >= 0 && pr != MARK) kind = 0;                    // direct: a_ij goes to its own C point
       else if (pr == MARK) {                                   // strong F neighbour: distributed over C-hat and i
         kind = 1;
-        const int rb = A.ptr[i1], re = A.ptr[i1 + 1];
         rb0 = rb;
-        b1 = cc.acptr[i1];
-        n_t = cc.acptr[i1 + 1] - b1;
         neg = A.val[rb] < 0;
         // back-edge a_{i1,i}: entries after the diagonal are sorted by column in own rows, in storage order of the owner in
         // fetched halo rows
