@@ -11,6 +11,7 @@ import glob
 import hashlib
 import json
 import os
+import re
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -39,8 +40,8 @@ def main():
             continue
         for c, pats in CLASSES.items():
             if any(p in r[name] for p in pats):
-                # symbolic / numeric instantiations of k_spgemm_smem differ by their last template argument
-                if c == "spgemm_numeric" and "false>" in r[name].replace(" ", "").replace("(bool)0", "false").replace("(bool)1", "true"):
+                # symbolic / numeric instantiations of k_spgemm_smem / k_spgemm_gmem differ by their last template argument
+                if c == "spgemm_numeric" and re.search(r"k_spgemm_(smem<\d+, |gmem<)0>", r[name]):
                     c = "spgemm_symbolic"
                 tot[c] += float(r[value].replace(",", "")) * scale.get(r[unit], 1.0)
                 launches[c] += 1 if r[metric].endswith("read.sum") else 0
