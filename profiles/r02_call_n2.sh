@@ -12,3 +12,5 @@ import json
 d=json.loads(open("gpurun_out/r02n2_bench.json").read().strip().splitlines()[-1])
 print("N=2", d["ms_per_step"], d["value"], d["setup_phases_ms"], d["iterations"], d["parity"], d["e2e"])
 PY
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29613 bench.py --impl reference --gpus 2 --steps 5 --warmup 3 > gpurun_out/r02n2_reference.json 2> gpurun_out/r02n2_reference.err
+tail -c 300 gpurun_out/r02n2_reference.err; cut -c1-700 gpurun_out/r02n2_reference.json
