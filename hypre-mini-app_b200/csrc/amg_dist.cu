@@ -75,7 +75,7 @@ int sort_unique(const i64 *keys, i64 n, DVec<i64> &out) {
 __device__ __forceinline__ int lower_bound_dev(const i64 *a, int n, i64 key) {
   int lo = 0, hi = n;
   while (lo < hi) {
-    int mid = (lo + hi) >> 1;
+    int mid = lo + ((hi - lo) >> 1);
     if (a[mid] < key) lo = mid + 1;
     else hi = mid;
   }

@@ -343,7 +343,7 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
         if (i1 < n_own) {
           int lo_k = rb + 1, hi_k = re;
           while (lo_k < hi_k) {
-            const int mid = (lo_k + hi_k) >> 1;
+            const int mid = lo_k + ((hi_k - lo_k) >> 1);   // entry positions reach 2^31: no lo + hi
             if (A.col[mid] < i) lo_k = mid + 1; else hi_k = mid;
           }
           if (lo_k < re && A.col[lo_k] == i) kb = lo_k;

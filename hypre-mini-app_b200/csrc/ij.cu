@@ -114,7 +114,7 @@ __global__ void k_row_counts(i64 n, const i64 *rows, const i64 *cols, i64 ilower
 __device__ __forceinline__ int lower_bound_i64(const i64 *a, int n, i64 key) {
   int lo = 0, hi = n;
   while (lo < hi) {
-    int mid = (lo + hi) >> 1;
+    int mid = lo + ((hi - lo) >> 1);
     if (a[mid] < key) lo = mid + 1;
     else hi = mid;
   }

@@ -39,7 +39,7 @@ __global__ void k_ilu0_level(int cnt, const int *__restrict__ rows, const int *_
       else {
         int lo = b + 1, hi = e;
         while (lo < hi) {
-          int mid = (lo + hi) >> 1;
+          int mid = lo + ((hi - lo) >> 1);
           if (col[mid] < j) lo = mid + 1;
           else hi = mid;
         }
