@@ -682,7 +682,10 @@ bool coarsen_level_dist(Amg &amg, AmgLevel &L, AmgLevel &Lc) {
   a_colmap.from_host(Ap.col_map_offd.data(), Ap.col_map_offd.size());
   if (nh == 0) a_colmap.alloc(1);
   DCsr Am;
-  merge_parcsr(Ap, Am);
+  {
+    PhaseTimerD t0(amg, "merge");
+    merge_parcsr(Ap, Am);
+  }
   rows::Csr am = rv(Am);
   // ---- strength on the merged rows -----------------------------------------------------------------------------------------
   {
@@ -750,6 +753,7 @@ bool coarsen_level_dist(Amg &amg, AmgLevel &L, AmgLevel &Lc) {
   {
     PhaseTimerD t(amg, "interp");
     // codes (global coarse id or negative marker) of own + halo points
+    std::unique_ptr<PhaseTimerD> st(new PhaseTimerD(amg, "interp.fetch_rows"));
     DVec<i64> code((size_t)nm + 1);
     DLAUNCH(k_codes, n, n, cfm.p, f2c.p, cstart, code.p);
     halo_fwd<i64>(Ap, code.p, code.p + n);
@@ -759,6 +763,8 @@ bool coarsen_level_dist(Amg &amg, AmgLevel &L, AmgLevel &Lc) {
     fetch_halo_rows(Ap, Am.ptr.p, Am.col.p, Am.val.p, nullptr, Nh, extA);
     fetch_halo_rows(Ap, L.Sptr.p, L.Scol.p, nullptr, code.p, Nh, extS);
     // distance-2 points: columns of the fetched rows that are neither own nor halo
+    st.reset();
+    st.reset(new PhaseTimerD(amg, "interp.extend"));
     DVec<i64> newg;
     int nnew = collect_unknown(extA.col.p, extA.nnz, Nh, newg);
     const int ntot = nm + nnew;
@@ -785,13 +791,20 @@ bool coarsen_level_dist(Amg &amg, AmgLevel &L, AmgLevel &Lc) {
     }
     DLAUNCH(k_f2c_ext, ntot, n, ntot, code_ext.p, f2c.p, nc, xc0.p, nxc0, f2c_ext.p);
     Pm.nc = nc + nxc0;
+    st.reset();
     {
       PhaseTimerD t2(amg, "interp.build");
       build_interp(Aext, Sext.ptr.p, Sext.col.p, Sext.nnz, cf_ext.p, f2c_ext.p, n, n, o.trunc_factor, o.p_max_elmts, Pm);
     }
-    split_merged(Pm, nc, xc0.p, nxc0, L.P);
+    {
+      PhaseTimerD t3(amg, "interp.split");
+      split_merged(Pm, nc, xc0.p, nxc0, L.P);
+    }
     set_par_shape(L.P, n, nc, Ap.row_start, cstart, gn, gnc);
-    build_partition_and_halo(L.P);
+    {
+      PhaseTimerD t4(amg, "interp.halo_plan");
+      build_partition_and_halo(L.P);
+    }
     L.cf.alloc((size_t)std::max(n, 1));
     DLAUNCH(k_fold_sf_d, n, n, L.cf_raw.p, L.cf.p);
     B200_KERNEL_CHECK();
@@ -877,6 +890,7 @@ bool coarsen_level_dist(Amg &amg, AmgLevel &L, AmgLevel &Lc) {
       B200_REQUIRE(fetch1(bad.p) == 0, "A*P: column renumbering failed");
       DCsr Pext;
       stack_rows(n, Pm.ptr.p, Pm.col.p, Pm.val.p, Pm.nnz, extP, Nq, nc + nxq, true, Pext);
+      PhaseTimerD t2(amg, "rap.AP.spgemm");
       csr_spgemm(Am, Pext, Q, false, false);
     }
     // A_c = R_merged * Q_ext
@@ -907,11 +921,14 @@ bool coarsen_level_dist(Amg &amg, AmgLevel &L, AmgLevel &Lc) {
         PhaseTimerD t2(amg, "rap.RQ.spgemm");
         csr_spgemm(Rm, Qext, Acm, true);
       }
-      PhaseTimerD t3(amg, "rap.RQ.split");
       Lc.A_own.reset(new ParCsr());
       Lc.A = Lc.A_own.get();
-      split_merged(Acm, nc, xa.p, nxa, *Lc.A);
+      {
+        PhaseTimerD t3(amg, "rap.RQ.split");
+        split_merged(Acm, nc, xa.p, nxa, *Lc.A);
+      }
       set_par_shape(*Lc.A, nc, nc, cstart, cstart, gnc, gnc);
+      PhaseTimerD t4(amg, "rap.RQ.halo_plan");
       build_partition_and_halo(*Lc.A);
     }
   }

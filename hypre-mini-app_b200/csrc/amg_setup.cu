@@ -431,6 +431,8 @@ void amg_setup(Amg &amg, ParCsr &A) {
     bool last = (level >= o.max_levels - 1) || (fine <= o.max_coarse_size);
     if (!last) {
       std::unique_ptr<AmgLevel> Lc(new AmgLevel());
+      const std::string lname = "level." + std::to_string(level);   // whole coarsening step of this level (all phases)
+      PhaseTimer tl(amg, lname.c_str());
       const bool ok = (ctx().nranks > 1) ? coarsen_level_dist(amg, L, *Lc) : coarsen_level(amg, L, *Lc);
       if (ok) amg.lev.push_back(std::move(Lc));
       else last = true;
