@@ -8,7 +8,7 @@ RE=${2:-}
 SKIP=${3:-0}
 CNT=${4:-3}
 mkdir -p gpurun_out
-CMD="python bench.py --size 256 --steps 1 --warmup 1 --no-e2e --no-cpu-baseline"
+CMD="python bench.py --size 256 --steps 1 --warmup 1 --no-e2e --no-cpu-baseline --parity-n 0"
 $CMD > gpurun_out/plain_$TAG.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 8000 --csv --log-file gpurun_out/launches_$TAG.csv $CMD > gpurun_out/ncu_list_$TAG.log 2>&1
 if [ -n "$RE" ]; then
