@@ -40,7 +40,7 @@ __device__ __forceinline__ void epilogue(const SpmvArgs &a, int i, double t) {
 // U rows per lane group are in flight at once: a short row is a chain of three dependent loads (row pointer -> column /
 // value -> x), so one row per group leaves the memory system idle two thirds of the time (P and R of the first levels:
 // 2.5 - 3.2 TB/s with U = 1).  The U rows of a group are a block-stride apart, so every load phase stays coalesced.
-template <int G, int MODE, bool XS, int U>
+template <int G, int MODE, bool XS, int U, bool IL>
 __global__ void __launch_bounds__(256) k_csr_vec(CsrView A, SpmvArgs a) {
   constexpr int RPB = 256 / G;                       // rows per block and batch
   const int lane = threadIdx.x & (G - 1);
@@ -73,14 +73,38 @@ __global__ void __launch_bounds__(256) k_csr_vec(CsrView A, SpmvArgs a) {
       sum[u] = v[u] * xv;
     }
   }
+  // rows longer than the group.  IL (matrices with long rows, e.g. the level-1 operator: 29 entries on 4 lanes = 7 more
+  // rounds): the remaining rounds keep the U rows interleaved (load phase for all rows, then gather phase) like the first one;
+  // measured -0.1 ms per GMRES iteration at 256^3.  Short rows (P, R of level 0: at most two more rounds) are faster row by row.
+  if constexpr (IL) {
+    bool more = false;
 #pragma unroll
-  for (int u = 0; u < U; ++u) {
-    for (int k = kb[u] + G; k < ke[u]; k += G) {
-      int cc = __ldg(A.col + k);
-      double vv = __ldg(A.val + k);
-      double xv = a.x[cc];
-      if (XS) xv *= a.xs[cc];
-      sum[u] += vv * xv;
+    for (int u = 0; u < U; ++u) { kb[u] += G; more |= kb[u] < ke[u]; }
+    while (more) {
+      more = false;
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (kb[u] < ke[u]) { c[u] = __ldg(A.col + kb[u]); v[u] = __ldg(A.val + kb[u]); }
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (kb[u] < ke[u]) {
+          double xv = a.x[c[u]];
+          if (XS) xv *= a.xs[c[u]];
+          sum[u] += v[u] * xv;
+          kb[u] += G;
+          more |= kb[u] < ke[u];
+        }
+    }
+  } else {
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      for (int k = kb[u] + G; k < ke[u]; k += G) {
+        int cc = __ldg(A.col + k);
+        double vv = __ldg(A.val + k);
+        double xv = a.x[cc];
+        if (XS) xv *= a.xs[cc];
+        sum[u] += vv * xv;
+      }
     }
   }
 #pragma unroll
@@ -163,9 +187,15 @@ __global__ void k_sell_fill(int nr, CsrView A, const i64 *__restrict__ slice_off
 template <int G, int MODE>
 void launch_csr(const DCsr &A, const SpmvArgs &a) {
   constexpr int U = (G <= 8) ? 4 : (G == 16 ? 2 : 1);
-  int grid = div_up((i64)A.nr, (i64)(256 / G) * U);
-  if (a.xs) k_csr_vec<G, MODE, true, U><<<grid, 256, 0, stream()>>>(A.view(), a);
-  else k_csr_vec<G, MODE, false, U><<<grid, 256, 0, stream()>>>(A.view(), a);
+  const int grid = div_up((i64)A.nr, (i64)(256 / G) * U);
+  const bool il = U > 1 && A.nr > 0 && (double)A.nnz > 3.0 * G * (double)A.nr;   // more than two rounds beyond the first
+  if (il) {
+    if (a.xs) k_csr_vec<G, MODE, true, U, true><<<grid, 256, 0, stream()>>>(A.view(), a);
+    else k_csr_vec<G, MODE, false, U, true><<<grid, 256, 0, stream()>>>(A.view(), a);
+  } else {
+    if (a.xs) k_csr_vec<G, MODE, true, U, false><<<grid, 256, 0, stream()>>>(A.view(), a);
+    else k_csr_vec<G, MODE, false, U, false><<<grid, 256, 0, stream()>>>(A.view(), a);
+  }
 }
 template <int MODE>
 void dispatch_csr(const DCsr &A, int lanes, const SpmvArgs &a) {
