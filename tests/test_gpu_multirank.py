@@ -169,8 +169,17 @@ def test_multirank_block_jacobi_ilu(b200, method):
         assert np.abs(x - xo).max() / np.abs(xo).max() <= 1e-8
 
 
-def compare_with_oracle(res, n, grid, stencil, theta):
-    o = Oracle(strong_threshold=theta)
+@pytest.mark.parametrize("pmax,tf", [(0, 0.0), (4, 0.15), (0, 0.2)])
+def test_multirank_truncation_modes(b200, pmax, tf):
+    """the truncation paths of the interpolation kernels with off-rank C points in the rows (P_diag / P_offd re-split after the
+    sort): 2 ranks on one GPU against the 2-virtual-rank oracle"""
+    n, grid = (10, 10, 10), (2, 1, 1)
+    res = run_ranks(2, settings(n, grid, 7, strong_threshold=0.25, p_max_elmts=pmax, trunc_factor=tf))
+    compare_with_oracle(res, n, grid, 7, 0.25, p_max_elmts=pmax, trunc_factor=tf)
+
+
+def compare_with_oracle(res, n, grid, stencil, theta, **extra):
+    o = Oracle(strong_threshold=theta, **extra)
     o.threads(8)
     o.gen_laplace(n, p=grid, stencil=stencil)
     o.setup()

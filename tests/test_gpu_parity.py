@@ -327,3 +327,32 @@ def b200_level0_scipy(s):
     ptr, col, val = s.precond.level_matrix(0, "A")
     nr = len(ptr) - 1
     return sp.csr_matrix((val, col, ptr), shape=(nr, nr))
+
+
+@pytest.mark.parametrize("n,stencil,theta,pmax,tf", [
+    (20, 7, 0.25, 0, 0.0),     # no truncation at all: count pass + fill pass (rows as long as C-hat)
+    (14, 27, 0.25, 0, 0.0),
+    (20, 7, 0.25, 0, 0.2),     # trunc_factor only (HypreSystem.cpp:230-233): truncation inside the row kernel
+    (20, 7, 0.25, 4, 0.1),     # both rules, the deferred thread-per-row truncation
+    (14, 27, 0.57, 2, 0.0),    # P_max 2: ties in |w| everywhere on the uniform stencil -> qsort2abs tie order decides
+    (24, 7, 0.25, 6, 0.3),
+])
+def test_interpolation_truncation_modes_bit_exact(b200, n, stencil, theta, pmax, tf):
+    """every combination of P_max_elmts (HYPRE_BoomerAMGSetPMaxElmts) and trunc_factor (YAML `trunc_factor`) takes a different
+    path through the interpolation kernels (count / fill / single pass, in-kernel or deferred truncation): same hierarchy,
+    bit for bit, as the sequential definition in the oracle"""
+    s = make_system(b200, n, stencil, strong_threshold=theta, p_max_elmts=pmax, trunc_factor=tf)
+    s.solve()
+    o = make_oracle(n, stencil, strong_threshold=theta, p_max_elmts=pmax, trunc_factor=tf)
+    o.setup()
+    xo = o.solve()
+    amg = s.precond
+    assert amg.num_levels == o.num_levels
+    for l in range(o.num_levels):
+        assert_same_csr(amg.level_matrix(l, "A"), o.matrix(l, "A"), f"A[{l}]")
+        if l + 1 < o.num_levels:
+            assert np.array_equal(amg.level_cf(l), o.cf(l)), f"CF[{l}] differs"
+            assert_same_csr(amg.level_matrix(l, "P"), o.matrix(l, "P"), f"P[{l}]")
+    assert abs(s.solver.iterations - o.iterations) <= 1
+    assert np.abs(s.solution() - 1.0).max() < 1e-6
+    s.destroy_system()
