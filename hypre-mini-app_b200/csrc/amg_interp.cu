@@ -152,24 +152,29 @@ void launch_flat(int grid_rows, const rows::Csr &A, const int *Sptr, const int *
             G, MODE, grid_rows, 100 * h[0] / tot, 100 * h[1] / tot, 100 * h[2] / tot, 100 * h[3] / tot, 100 * h[4] / tot, 100 * h[5] / tot, tot);
   }
 }
-template <int MODE, bool SMALL>
-void launch_one(int grid_rows, const rows::Csr &A, const int *Sptr, const int *Scol, const signed char *Scf, const int *cf, const int *f2c,
-                int n_own, int n_rows, double tf, int pmax, int lo, int *lraw, int *len, const int *Pptr, int *Pcol, double *Pval,
+// tiers (G lanes per row, hash slots, C-hat capacity, staging): rows that exceed a tier (C-hat or hash load) go to the next one
+//   8  : <8, 64, 32, 48>      4 rows per warp  -- short strength rows (7-point level 0)
+//   16 : <16, 128, 64, 96>    2 rows per warp  -- rows of up to ~40 entries (the coarser levels of the 7-point hierarchy: 24 - 30
+//                                                 entries and ~50 compressed items per row keep at most 16 lanes busy)
+//   32 : <32, 256, 128, 192>  1 row per warp   -- everything else
+template <int MODE>
+void launch_one(int tier, int grid_rows, const rows::Csr &A, const int *Sptr, const int *Scol, const signed char *Scf, const int *cf,
+                const int *f2c, int n_own, int n_rows, double tf, int pmax, int *lraw, int *len, const int *Pptr, int *Pcol, double *Pval,
                 const int *list) {
-  if (SMALL) launch_flat<8, 64, 32, 48, MODE>(grid_rows, A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw, len, Pptr, Pcol, Pval, list);
+  const int lo = -1;   // (unused by the kernels since the fill pass marks filled rows)
+  if (tier == 8) launch_flat<8, 64, 32, 48, MODE>(grid_rows, A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw, len, Pptr, Pcol, Pval, list);
+  else if (tier == 16) launch_flat<16, 128, 64, 96, MODE>(grid_rows, A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw, len, Pptr, Pcol, Pval, list);
   else launch_flat<32, 256, 128, 192, MODE>(grid_rows, A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw, len, Pptr, Pcol, Pval, list);
 }
 
 template <int MODE>
-void launch_tiers(bool small_tier, const rows::Csr &A, const int *Sptr, const int *Scol, const signed char *Scf, const int *cf,
+void launch_tiers(int first_tier, const rows::Csr &A, const int *Sptr, const int *Scol, const signed char *Scf, const int *cf,
                   const int *f2c, int n_own, int n_rows, double tf, int pmax, int *lraw, int *len, const int *Pptr, int *Pcol,
                   double *Pval) {
-  int lo = -1;
-  if (small_tier) {
-    launch_one<MODE, true>(n_rows, A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw, len, Pptr, Pcol, Pval, nullptr);
-    lo = 32;
+  if (first_tier != 32) {
+    launch_one<MODE>(first_tier, n_rows, A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lraw, len, Pptr, Pcol, Pval, nullptr);
     if (MODE != 1) {
-      // the rows the small tier could not hold are few (often none): run the large tier on their list only
+      // the rows the first tier could not hold are few (often none): run the large tier on their list only
       constexpr int CAP = 1 << 20;
       DVec<int> cnt(1), list((size_t)CAP);
       cnt.zero();
@@ -178,13 +183,13 @@ void launch_tiers(bool small_tier, const rows::Csr &A, const int *Sptr, const in
       const int left = fetch1(cnt.p);
       if (left == 0) return;
       if (left <= CAP) {
-        launch_one<MODE, false>(left, A, Sptr, Scol, Scf, cf, f2c, n_own, left, tf, pmax, lo, lraw, len, Pptr, Pcol, Pval, list.p);
+        launch_one<MODE>(32, left, A, Sptr, Scol, Scf, cf, f2c, n_own, left, tf, pmax, lraw, len, Pptr, Pcol, Pval, list.p);
         B200_KERNEL_CHECK();
         return;
       }
     }
   }
-  launch_one<MODE, false>(n_rows, A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lo, lraw, len, Pptr, Pcol, Pval, nullptr);
+  launch_one<MODE>(32, n_rows, A, Sptr, Scol, Scf, cf, f2c, n_own, n_rows, tf, pmax, lraw, len, Pptr, Pcol, Pval, nullptr);
   B200_KERNEL_CHECK();
 }
 
@@ -200,8 +205,13 @@ void build_interp(const DCsr &Aext, const int *Sptr, const int *Scol, i64 S_nnz,
   P.nr = n_rows;
   P.ptr.alloc((size_t)n_rows + 1);
   if (n_rows == 0) { P.nnz = 0; P.ptr.zero(); return; }
-  bool small_tier = (double)S_nnz <= 8.0 * (double)Aext.nr;
-  if (const char *e = getenv("B200_INTERP_SMALL_TIER")) small_tier = small_tier && atoi(e) != 0;   // benchmarking override
+  // first tier from the mean lengths of the strength rows and of the matrix rows (see launch_one)
+  int first_tier = 32;
+  if ((double)S_nnz <= 8.0 * (double)Aext.nr) first_tier = 8;
+  else if ((double)Aext.nnz <= 40.0 * (double)Aext.nr) first_tier = 16;
+  if (const char *e = getenv("B200_INTERP_MID_TIER")) {   // benchmarking override: 0 = no 16-lane tier
+    if (atoi(e) == 0 && first_tier == 16) first_tier = 32;
+  }
   const bool single = pmax > 0;
   DVec<signed char> Scf((size_t)std::max<i64>(S_nnz, 1));
   if (S_nnz > 0) {
@@ -242,9 +252,9 @@ void build_interp(const DCsr &Aext, const int *Sptr, const int *Scol, i64 S_nnz,
   if (single) {
     tcol.alloc((size_t)n_rows * pmax);
     tval.alloc((size_t)n_rows * pmax);
-    launch_tiers<2>(small_tier, A, Sptr, Scol, Scf.p, cf, f2c, n_own, n_rows, tf, pmax, lraw.p, len.p, nullptr, tcol.p, tval.p);
+    launch_tiers<2>(first_tier, A, Sptr, Scol, Scf.p, cf, f2c, n_own, n_rows, tf, pmax, lraw.p, len.p, nullptr, tcol.p, tval.p);
   } else {
-    launch_tiers<0>(small_tier, A, Sptr, Scol, Scf.p, cf, f2c, n_own, n_rows, tf, pmax, lraw.p, len.p, nullptr, nullptr, nullptr);
+    launch_tiers<0>(first_tier, A, Sptr, Scol, Scf.p, cf, f2c, n_own, n_rows, tf, pmax, lraw.p, len.p, nullptr, nullptr, nullptr);
   }
   }
   // rows beyond the last tier
@@ -280,7 +290,7 @@ void build_interp(const DCsr &Aext, const int *Sptr, const int *Scol, i64 S_nnz,
     k_compact_p<<<div_up(n_rows, 256), 256, 0, stream()>>>(n_rows, pmax, lraw.p, P.ptr.p, tcol.p, tval.p, P.col.p, P.val.p);
     count_launch();
   } else {
-    launch_tiers<1>(small_tier, A, Sptr, Scol, Scf.p, cf, f2c, n_own, n_rows, tf, pmax, lraw.p, len.p, P.ptr.p, P.col.p, P.val.p);
+    launch_tiers<1>(first_tier, A, Sptr, Scol, Scf.p, cf, f2c, n_own, n_rows, tf, pmax, lraw.p, len.p, P.ptr.p, P.col.p, P.val.p);
   }
   if (novf > 0) {
     k_interp_ovf<<<div_up(novf, 64), 64, 0, stream()>>>(A, Sptr, Scol, cf, f2c, n_own, tf, pmax, todo.p, novf, sc.p, sv.p, ocap, len.p,

@@ -185,19 +185,23 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
     }
   }
   if (i >= 0) {
+    // MODE 0 / 2: rows not computed yet (lraw == -1).  MODE 1 (fill): rows counted but not filled yet (lraw >= 0) that fit this
+    // tier; a filled row is marked lraw = -2 - L, so a row that this tier has to give up (hash load) is still taken by the next
     bool todo;
     if (MODE != 1) todo = (h_lraw == -1);
-    else todo = (h_lraw > lo && h_lraw <= CAP);
+    else todo = (h_lraw >= 0 && h_lraw <= CAP);
     if (todo) {
       const int cfi = h_cf;
       if (cfi >= 0) {   // C point: identity row
         if (gl == 0) {
           if (MODE != 1) { lraw[i] = 0; len[i] = 1; }
           if (MODE != 0) { const size_t b = (MODE == 1) ? (size_t)Pptr[i] : (size_t)i * pmax; Pcol[b] = f2c[i]; Pval[b] = 1.0; }
+          if (MODE == 1) lraw[i] = -2;
         }
       } else if (cfi == -3) {
-        if (MODE != 1 && gl == 0) { lraw[i] = 0; len[i] = 0; }
+        if (gl == 0) { if (MODE != 1) { lraw[i] = 0; len[i] = 0; } else lraw[i] = -2; }
       } else if (MODE == 1 && Pptr[i + 1] == Pptr[i]) {
+        if (gl == 0) lraw[i] = -2;
       } else active = true;
     }
   }
@@ -557,6 +561,7 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
   if (!(S.flags & 2)) return;
   const int n_out = S.nout;
   if (MODE != 1 && gl == 0) { lraw[i] = L; len[i] = n_out; }
+  if (MODE == 1 && gl == 0) lraw[i] = -2 - L;
   if (MODE == 0) return;
   const size_t b = (MODE == 1) ? (size_t)Pptr[i] : (size_t)i * pmax;
   for (int k = gl; k < n_out; k += G) {
