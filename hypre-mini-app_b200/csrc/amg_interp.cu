@@ -113,7 +113,7 @@ void launch_flat(int grid_rows, const rows::Csr &A, const int *Sptr, const int *
                  int n_own, int n_rows, double tf, int pmax, int lo, int *lraw, int *len, const int *Pptr, int *Pcol, double *Pval,
                  const int *list) {
   auto kern = flat::k_interp_flat<G, H, CAP, STG, MODE>;
-  constexpr size_t smem = sizeof(flat::Grp<G, H, CAP, STG>) * (256 / G);
+  constexpr size_t smem = sizeof(flat::Grp<G, H, CAP, STG>) * (flat::BT / G);
   static bool attr_set = false;   // per instantiation
   if (!attr_set) {
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -135,7 +135,7 @@ void launch_flat(int grid_rows, const rows::Csr &A, const int *Sptr, const int *
   }
   for (int slot0 = 0; slot0 < grid_rows; slot0 += chunk) {
     const int cnt = std::min(chunk, grid_rows - slot0);
-    kern<<<div_up(cnt, 256 / G), 256, smem, stream()>>>(A, Sptr, Scol, Scf, g_cc, cf, f2c, n_own, std::min(n_rows, slot0 + cnt), tf, pmax, lo, lraw,
+    kern<<<div_up(cnt, flat::BT / G), flat::BT, smem, stream()>>>(A, Sptr, Scol, Scf, g_cc, cf, f2c, n_own, std::min(n_rows, slot0 + cnt), tf, pmax, lo, lraw,
                                                        len, Pptr, Pcol, Pval, list, slot0, sc.p, sv.p, ts.p);
     count_launch();
     if (MODE == 2) {

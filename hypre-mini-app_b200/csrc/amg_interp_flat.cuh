@@ -32,6 +32,11 @@ namespace flat {
 
 constexpr int MARK = 255;      // hash position of a strong F neighbour of i (not a C-hat slot)
 constexpr unsigned FULL = 0xffffffffu;
+// threads per block of the row kernel.  128 (8 resident blocks per SM) instead of 256 (4): a block keeps its shared memory until
+// its slowest warp is done while the warps of C points leave at once, and the smaller the block the shorter that tail
+// (ncu r02f: 36 % of the warp slots occupied at a limit of 50 % with 256 threads; measured: interp 48.2 -> 45.7 ms; 64 threads: no
+// further gain)
+constexpr int BT = 128;
 
 // C-compressed copies of the level matrix and of the strength pattern (rows of non-isolated F points only, other rows empty):
 // entry e of row j of AC is the entry acpos[e] of A (acpos ascending inside a row), whose column accol[e] is a C point.
@@ -124,7 +129,7 @@ __device__ __forceinline__ int gscan_incl(int v, int gl) {
 // lraw / len / MODE / lo / row_list: as for the tier driver in amg_interp.cu (MODE 0 count, 1 fill at Pptr, 2 single pass at
 // i * pmax).  Scf[k] = cf[Scol[k]] as a signed char.
 template <int G, int H, int CAP, int STG, int MODE>
-__global__ void __launch_bounds__(256, 4)
+__global__ void __launch_bounds__(BT, 1024 / BT)
 k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__ Scol, const signed char *__restrict__ Scf,
               CComp cc, const int *__restrict__ cf, const int *__restrict__ f2c, int n_own, int n_rows, double tf, int pmax, int lo, int *lraw,
               int *len, const int *__restrict__ Pptr, int *Pcol, double *Pval, const int *__restrict__ row_list,
@@ -141,7 +146,10 @@ k_interp_flat(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__
     }
   };
   static_assert(CAP <= 128 && G <= 32 && STG > CAP, "slot / tag encodings");
-  constexpr int GROUPS = 256 / G;
+  // 1024 resident threads per SM: 227 KB of shared memory, 1 KB per block reserved by the system.  The kernel is latency bound,
+  // occupancy is what hides its dependent loads (r02c: a footprint one block too large cost the whole gain of that step)
+  static_assert((sizeof(GS) * (BT / G) + 1024) * (1024 / BT) <= 227 * 1024, "shared memory of the resident blocks exceeds the SM");
+  constexpr int GROUPS = BT / G;
   constexpr int HMAX = (H * 3) / 4;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   GS *all = reinterpret_cast<GS *>(smem_raw);
