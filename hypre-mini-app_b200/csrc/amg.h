@@ -100,6 +100,8 @@ struct AmgLevel {
   std::vector<double> cheby_coef;
   DVec<double> u, f, r, t0, t1;   // work vectors of the cycle
   GsPlan gs[3][2];                // [all | C | F points][forward | backward], built for the Gauss-Seidel smoothers only
+  DCsr tri[2];                    // two-stage Gauss-Seidel (relax 11 / 12): strictly lower / upper triangle of the own diag block
+  SpmvPlan tri_plan[2];
 };
 
 struct Amg {
@@ -121,6 +123,7 @@ struct Amg {
   ~Amg();
 };
 
+inline bool is_two_stage_gs(int relax_type) { return relax_type == 11 || relax_type == 12; }
 bool is_gs_relax(int relax_type);
 bool is_l1_gs_relax(int relax_type);
 void gs_smoother_diag(ParCsr &A, int relax_type, double *d);

@@ -94,6 +94,28 @@ void relax_sweep(Amg &amg, AmgLevel &L, LevelBufs &b, int rtype, bool down, bool
     }
     return;
   }
+  if (is_two_stage_gs(rtype)) {
+    // Two-stage Gauss-Seidel (hypre relax 11 forward / 12 backward, one inner iteration; SURVEY.md section 8f.1 asks for a Gauss-Seidel
+    // that suits the device): the triangular solve replaced by the first two terms of its Neumann series, all SpMV-class passes,
+    //     r = f - A u;  z = w D^-1 r;  u += z;  z = D^-1 (T z);  u -= z      T = strictly lower / upper triangle of the own diag block
+    // In place on b.cur (no buffer flip), no C/F ordering.
+    const int side = rtype - 11;
+    double *r = L.r.p, *z = L.t0.p, *t = L.t1.p;
+    const double *res = b.f;
+    if (!zero_guess) {
+      SpmvArgs a; a.x = b.cur; a.y = r; a.b = b.f;
+      par_spmv(A, SPMV_RES, a);
+      res = r;
+    }
+    vec_pointwise_div(z, res, L.dsm.p, o.relax_weight, nullptr, 0, n);
+    if (zero_guess) vec_copy(b.cur, z, n);
+    else vec_axpy(1.0, z, b.cur, n);
+    SpmvArgs ta; ta.x = z; ta.y = t;
+    spmv(L.tri[side], nullptr, L.tri_plan[side], SPMV_AX, ta);
+    vec_pointwise_div(z, t, L.dsm.p, 1.0, nullptr, 0, n);
+    vec_axpy(-1.0, z, b.cur, n);
+    return;
+  }
   if (is_gs_relax(rtype)) {
     // hybrid Gauss-Seidel (gs.cu): every pass reads b.cur and writes b.other; the halo is gathered once per call
     const bool fwd = (rtype != 4 && rtype != 14), bwd = (rtype == 4 || rtype == 14 || rtype == 6 || rtype == 8);
@@ -132,7 +154,7 @@ void relax_sweep(Amg &amg, AmgLevel &L, LevelBufs &b, int rtype, bool down, bool
 }
 
 int flips_per_sweep(const AmgOptions &o, int rtype) {
-  if (rtype == 16) return 0;
+  if (rtype == 16 || is_two_stage_gs(rtype)) return 0;
   const int npass = (o.relax_order == 1) ? 2 : 1;
   if (is_gs_relax(rtype)) return npass * ((rtype == 6 || rtype == 8) ? 2 : 1);
   return npass;
@@ -146,7 +168,7 @@ void init_bufs(Amg &amg, const double *rhs, double *z, std::vector<LevelBufs> &b
     AmgLevel &L = *amg.lev[l];
     bool coarsest = (l == nl - 1);
     double *A0 = (l == 0) ? z : L.u.p, *B0 = L.t0.p;
-    if (o.relax_type[1] == 16) B0 = nullptr;  // Chebyshev works in place (t0/t1 are its scratch)
+    if (o.relax_type[1] == 16 || is_two_stage_gs(o.relax_type[1])) B0 = nullptr;  // Chebyshev / two-stage GS work in place (t0/t1 are scratch)
     // number of buffer flips this level will see, so that the final result lands in A0
     int flips = 0;
     if (coarsest) {

@@ -122,6 +122,23 @@ __global__ void k_fold_sf(int n, const int *cf_raw, int *cf) {
   if (i < n) cf[i] = (cf_raw[i] == -3) ? -1 : cf_raw[i];
 }
 
+// ---- two-stage Gauss-Seidel (relax 11 / 12): strictly lower (upper = 0) or upper triangle of the own diag block ------------
+__global__ void k_tri_count(CsrView A, int upper, int *cnt) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i > A.nr) return;
+  int c = 0;
+  if (i < A.nr)
+    for (int k = A.ptr[i]; k < A.ptr[i + 1]; ++k) c += (upper ? A.col[k] > i : A.col[k] < i) ? 1 : 0;
+  cnt[i] = c;
+}
+__global__ void k_tri_fill(CsrView A, int upper, const int *tptr, int *tcol, double *tval) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= A.nr) return;
+  int w = tptr[i];
+  for (int k = A.ptr[i]; k < A.ptr[i + 1]; ++k)
+    if (upper ? A.col[k] > i : A.col[k] < i) { tcol[w] = A.col[k]; tval[w] = A.val[k]; ++w; }
+}
+
 // ---- smoother diagonal / dense coarse matrix ------------------------------------------------------------------------
 __global__ void k_smoother_diag(rows::Csr A, int relax_type, double *d) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -407,10 +424,13 @@ void amg_setup(Amg &amg, ParCsr &A) {
   B200_REQUIRE(o.relax_type[3] == 9 || o.max_levels == 1,
                "BoomerAMG: coarse_relax_type must be 9 (Gaussian elimination on the coarsest level); got " + std::to_string(o.relax_type[3]));
   for (int k = 0; k < 3; ++k)
-    B200_REQUIRE(o.relax_type[k] == 18 || o.relax_type[k] == 7 || o.relax_type[k] == 16 || is_gs_relax(o.relax_type[k]),
-                 "BoomerAMG: relax_type must be 7 (Jacobi), 18 (l1-Jacobi), 16 (Chebyshev) or hybrid Gauss-Seidel (3, 4, 6, 8, 13, 14)");
-  B200_REQUIRE(o.relax_type[1] == o.relax_type[2] || (is_gs_relax(o.relax_type[1]) && is_gs_relax(o.relax_type[2]) &&
-                                                      is_l1_gs_relax(o.relax_type[1]) == is_l1_gs_relax(o.relax_type[2])),
+    B200_REQUIRE(o.relax_type[k] == 18 || o.relax_type[k] == 7 || o.relax_type[k] == 16 || is_gs_relax(o.relax_type[k]) ||
+                     is_two_stage_gs(o.relax_type[k]),
+                 "BoomerAMG: relax_type must be 7 (Jacobi), 18 (l1-Jacobi), 16 (Chebyshev), hybrid Gauss-Seidel (3, 4, 6, 8, 13, 14) or "
+                 "two-stage Gauss-Seidel (11, 12)");
+  B200_REQUIRE(o.relax_type[1] == o.relax_type[2] || (is_two_stage_gs(o.relax_type[1]) && is_two_stage_gs(o.relax_type[2])) ||
+                   (is_gs_relax(o.relax_type[1]) && is_gs_relax(o.relax_type[2]) &&
+                    is_l1_gs_relax(o.relax_type[1]) == is_l1_gs_relax(o.relax_type[2])),
                "BoomerAMG: down and up smoothers must share their diagonal scaling (same relax_type family)");
   if (o.coarsen_type == 10 && o.max_levels > 1 && ctx().rank == 0) {
     static bool warned = false;
@@ -456,8 +476,25 @@ void amg_setup(Amg &amg, ParCsr &A) {
         gs_smoother_diag(Al, rt, L.dsm.p);
       } else {
         L.dsm.alloc((size_t)std::max(n, 1));
-        if (ctx().nranks > 1) smoother_diag_dist(Al, rt, L.dsm.p);
-        else if (n) { k_smoother_diag<<<div_up(n, 256), 256, 0, stream()>>>(rv(Al.diag), rt, L.dsm.p); count_launch(); }
+        const int drt = is_two_stage_gs(rt) ? 7 : rt;   // two-stage Gauss-Seidel scales with a_ii
+        if (ctx().nranks > 1) smoother_diag_dist(Al, drt, L.dsm.p);
+        else if (n) { k_smoother_diag<<<div_up(n, 256), 256, 0, stream()>>>(rv(Al.diag), drt, L.dsm.p); count_launch(); }
+        for (int side = 0; side < 2; ++side) {
+          const bool need = (o.relax_type[1] == 11 + side) || (o.relax_type[2] == 11 + side);
+          if (!need || n == 0) continue;
+          DCsr &T = L.tri[side];
+          T.nr = n; T.nc = Al.diag.nc;
+          DVec<int> cnt((size_t)n + 1);
+          T.ptr.alloc((size_t)n + 1);
+          k_tri_count<<<div_up((i64)n + 1, 256), 256, 0, stream()>>>(Al.diag.view(), side, cnt.p);
+          exclusive_scan(cnt.p, T.ptr.p, (i64)n + 1);
+          T.nnz = fetch(T.ptr.p + n);
+          T.col.alloc((size_t)std::max<i64>(T.nnz, 1));
+          T.val.alloc((size_t)std::max<i64>(T.nnz, 1));
+          k_tri_fill<<<div_up(n, 256), 256, 0, stream()>>>(Al.diag.view(), side, T.ptr.p, T.col.p, T.val.p);
+          count_launch(2);
+          L.tri_plan[side] = make_plan(T, nullptr);
+        }
       }
       i64 ld = ((i64)n + 1) & ~1LL;
       L.u.alloc(ld); L.f.alloc(ld); L.r.alloc(ld); L.t0.alloc(ld); L.t1.alloc(ld);

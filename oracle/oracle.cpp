@@ -774,7 +774,7 @@ static void l1_norms(const Csr &A, int relax_type, const std::vector<int> &part,
     int b = A.ptr[i], e = A.ptr[i + 1];
     if (b == e) { l1[i] = 1.0; continue; }
     double d = A.val[b];
-    if (relax_type == 7 || relax_type == 3 || relax_type == 4 || relax_type == 6) { l1[i] = d; continue; }
+    if (relax_type == 7 || relax_type == 3 || relax_type == 4 || relax_type == 6 || relax_type == 11 || relax_type == 12) { l1[i] = d; continue; }
     if (is_l1_gs(relax_type)) {
       // A.7: hypre_ParCSRComputeL1Norms option 4 (truncated, for Gauss-Seidel): |a_ii| + 1/2 sum_offd |a_ij|,
       // reset to |a_ii| when it does not exceed 4/3 |a_ii|; negated for a negative diagonal
@@ -1066,6 +1066,36 @@ static void relax(Level &L, const Options &o, double *u, const double *f, int po
     }
     return;
   }
+  if (o.relax_type == 11 || o.relax_type == 12) {
+    // Two-stage Gauss-Seidel (hypre_BoomerAMGRelaxTwoStageGaussSeidel, relax 11 forward / 12 backward, one inner iteration): the
+    // triangular solve of Gauss-Seidel replaced by the first two terms of its Neumann series,
+    //     r = w (f - A u);  z = D^-1 r;  u += z;  z = D^-1 (T z);  u -= z        T = strictly lower (11) / upper (12) triangle
+    // of the rank's own diagonal block (hybrid: off-rank couplings enter through the residual only).  No C/F ordering.
+    double *r = L.tmp.data(), *z = L.tmp2.data(), *t = L.vtemp.data();
+    const double w = o.relax_weight;
+    if (zero_guess) {
+#pragma omp parallel for schedule(static)
+      for (int i = 0; i < n; ++i) r[i] = f[i];
+    } else residual(A, u, f, r);
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < n; ++i) { z[i] = w * r[i] / L.l1[i]; u[i] = (zero_guess ? 0.0 : u[i]) + z[i]; }
+    std::vector<int> lo(n, 0), hi(n, n);
+    for (size_t q = 0; q + 1 < L.part.size(); ++q)
+      for (int i = L.part[q]; i < L.part[q + 1]; ++i) { lo[i] = L.part[q]; hi[i] = L.part[q + 1]; }
+    const bool lower = (o.relax_type == 11);
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < n; ++i) {
+      double sacc = 0.0;
+      for (int q = A.ptr[i]; q < A.ptr[i + 1]; ++q) {
+        const int c = A.col[q];
+        if (c >= lo[i] && c < hi[i] && (lower ? c < i : c > i)) sacc += A.val[q] * z[c];
+      }
+      t[i] = sacc;
+    }
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < n; ++i) u[i] = u[i] - 1.0 * t[i] / L.l1[i];
+    return;
+  }
   // Jacobi-type (relax 7 / 18): u <- u + w (f - A u) ./ d, out of place
   double w = o.relax_weight;
   double *un = L.tmp.data();
@@ -1087,7 +1117,7 @@ static void relax(Level &L, const Options &o, double *u, const double *f, int po
 static void relax_sweeps(Level &L, const Options &o, double *u, const double *f, bool down, bool zero_guess) {
   for (int sw = 0; sw < o.num_sweeps; ++sw) {
     bool zg = zero_guess && sw == 0;
-    if (o.relax_order == 1 && o.relax_type != 16) {
+    if (o.relax_order == 1 && o.relax_type != 16 && o.relax_type != 11 && o.relax_type != 12) {
       int first = down ? 1 : -1;
       relax(L, o, u, f, first, zg);
       relax(L, o, u, f, -first, false);

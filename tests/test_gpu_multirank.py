@@ -178,6 +178,15 @@ def test_multirank_truncation_modes(b200, pmax, tf):
     compare_with_oracle(res, n, grid, 7, 0.25, p_max_elmts=pmax, trunc_factor=tf)
 
 
+@pytest.mark.parametrize("relax", [11, 12])
+def test_multirank_two_stage_gauss_seidel(b200, relax):
+    """relax 11 / 12 on 2 ranks: the triangle is taken from every rank's own diagonal block (hybrid), off-rank couplings enter
+    through the residual; compared with the 2-virtual-rank oracle"""
+    n, grid = (12, 12, 12), (2, 1, 1)
+    res = run_ranks(2, settings(n, grid, 7, strong_threshold=0.25, relax_type=relax))
+    compare_with_oracle(res, n, grid, 7, 0.25, relax_type=relax)
+
+
 def compare_with_oracle(res, n, grid, stencil, theta, **extra):
     o = Oracle(strong_threshold=theta, **extra)
     o.threads(8)

@@ -62,7 +62,8 @@ def test_hierarchy_bit_exact(b200, n, stencil, theta):
     s.destroy_system()
 
 
-@pytest.mark.parametrize("n,stencil,relax,order", [(24, 7, 18, 0), (24, 7, 18, 1), (24, 7, 7, 0), (16, 27, 18, 0), (24, 7, 16, 0)])
+@pytest.mark.parametrize("n,stencil,relax,order", [(24, 7, 18, 0), (24, 7, 18, 1), (24, 7, 7, 0), (16, 27, 18, 0), (24, 7, 16, 0),
+                                                   (24, 7, 11, 0), (24, 7, 12, 0), (16, 27, 11, 1)])   # 11 / 12: two-stage Gauss-Seidel
 def test_solve_parity(b200, n, stencil, relax, order):
     s = make_system(b200, n, stencil, relax_type=relax, relax_order=order)
     s.solver.destroy()
