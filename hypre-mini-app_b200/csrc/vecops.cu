@@ -5,6 +5,7 @@
 // (double2), grid = multiple of the SM count, warp-shuffle + shared-memory block reduction, per-block partials
 // summed in a fixed order by the last block (deterministic, no floating-point atomics).
 #include "common.h"
+#include "abi_util.h"   // error-flag plumbing of the one C-ABI entry point defined here (b200hypre_multi_dot_noalloc)
 
 namespace b200 {
 
@@ -334,4 +335,73 @@ double dot_host(DotWork &w, const double *a, const double *b, i64 n) {
   return h;
 }
 
+// ---- multi-dot that allocates nothing (b200hypre_multi_dot_noalloc, include/b200hypre.h) ------------------------------------------
+// Same kernel and same grid as multi_dot above; the per-block partials and the ticket word live in a file-scope device array
+// instead of a DotWork buffer, so that callers that cannot reach cudaMalloc (stream capture, serving loops) can use it.
+// Every GPU that loads the library holds these NOALLOC_BYTES until the process exits.
+namespace {
+constexpr int NOALLOC_MAX_BLOCKS = 2048;                                            // launch grid the partials have room for
+constexpr int NOALLOC_MAX_K = 64;                                                   // vectors per call (8 per pass over x)
+constexpr size_t NOALLOC_PARTIAL_BYTES = (size_t)NOALLOC_MAX_BLOCKS * 8 * sizeof(double);   // partial[block][8]
+constexpr size_t NOALLOC_BYTES = NOALLOC_PARTIAL_BYTES + 256;                       // + the ticket word in a line of its own
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_BYTES];
+// In host code g_noalloc_scratch is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress, once per
+// device, with that device current.
+constexpr int NOALLOC_MAX_DEVICES = 64;
+unsigned char *g_noalloc_addr[NOALLOC_MAX_DEVICES] = {};
+
+unsigned char *noalloc_scratch_on_current_device() {
+  int dev = -1;
+  B200_CUDA(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < NOALLOC_MAX_DEVICES, "multi_dot_noalloc: device ordinal beyond 63");
+  if (!g_noalloc_addr[dev]) {
+    void *p = nullptr;
+    B200_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    B200_REQUIRE(p != nullptr, "multi_dot_noalloc: cudaGetSymbolAddress returned a null address");
+    g_noalloc_addr[dev] = static_cast<unsigned char *>(p);
+  }
+  return g_noalloc_addr[dev];
+}
+}  // namespace
+
+// out[j] = <V_j, x> over the n local entries, j < k; V_j = V + j ld.  Device pointers; ordered on stream(), not synchronised.
+void multi_dot_noalloc(const double *V, i64 ld, int k, const double *x, i64 n, double *out) {
+  B200_REQUIRE(ctx().initialised, "multi_dot_noalloc: library not initialised (HYPRE_Init creates the stream; this call creates nothing)");
+  B200_REQUIRE(k >= 1 && k <= NOALLOC_MAX_K, "multi_dot_noalloc: k = " + std::to_string(k) + " vectors, the static scratch serves 1 .. " +
+                                                 std::to_string(NOALLOC_MAX_K) + " per call");
+  B200_REQUIRE(n >= 0 && (k == 1 || ld >= n), "multi_dot_noalloc: n < 0 or ld < n");
+  B200_REQUIRE((k == 1 || (ld & 1) == 0) && ((uintptr_t)V & 15) == 0 && ((uintptr_t)x & 15) == 0,
+               "multi_dot_noalloc: vectors must be 16-byte aligned and ld even");
+  int dev = -1;
+  B200_CUDA(cudaGetDevice(&dev));
+  B200_REQUIRE(dev == ctx().device, "multi_dot_noalloc: the current device is not the one the library was initialised on");
+  const int grid = stream_grid(n > 0 ? n : 1, 8);
+  B200_REQUIRE(grid <= NOALLOC_MAX_BLOCKS, "multi_dot_noalloc: launch grid of " + std::to_string(grid) + " blocks (n = " + std::to_string(n) +
+                                               ") exceeds the " + std::to_string(NOALLOC_MAX_BLOCKS) + " blocks the static scratch has partials for");
+  unsigned char *scr = noalloc_scratch_on_current_device();
+  double *partial = reinterpret_cast<double *>(scr);
+  unsigned int *ticket = reinterpret_cast<unsigned int *>(scr + NOALLOC_PARTIAL_BYTES);
+  // the array keeps what the last call left: the ticket must start at zero (a call that died mid-kernel may have left a count);
+  // the partials are written before they are read
+  B200_CUDA(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), stream()));
+  for (int j0 = 0; j0 < k; j0 += 8) {
+    const int kv = (k - j0 < 8) ? (k - j0) : 8;
+    const double *Vj = V + (i64)j0 * ld;
+    if (kv <= 1) k_multi_dot<1><<<grid, VB, 0, stream()>>>(Vj, ld, kv, x, n, partial, out + j0, ticket);
+    else if (kv <= 2) k_multi_dot<2><<<grid, VB, 0, stream()>>>(Vj, ld, kv, x, n, partial, out + j0, ticket);
+    else if (kv <= 4) k_multi_dot<4><<<grid, VB, 0, stream()>>>(Vj, ld, kv, x, n, partial, out + j0, ticket);
+    else k_multi_dot<8><<<grid, VB, 0, stream()>>>(Vj, ld, kv, x, n, partial, out + j0, ticket);
+    count_launch();
+  }
+  B200_KERNEL_CHECK();
+}
+
 }  // namespace b200
+
+extern "C" HYPRE_Int b200hypre_multi_dot_noalloc(const HYPRE_Complex *V, HYPRE_BigInt ld, HYPRE_Int k, const HYPRE_Complex *x, HYPRE_BigInt n,
+                                                 HYPRE_Complex *out) {
+  API_ARG(V && x && out, "b200hypre_multi_dot_noalloc: null pointer");
+  API_BEGIN
+  b200::multi_dot_noalloc(V, ld, k, x, n, out);
+  API_END
+}

@@ -95,6 +95,23 @@ void *b200hypre_vector_data(HYPRE_ParVector v);    /* device pointer of the loca
 HYPRE_Int b200hypre_vector_local_size(HYPRE_ParVector v);
 const char *b200hypre_spmv_kernel_name(HYPRE_ParCSRMatrix A);   /* "sell32" or "csr_vec<G>" chosen for the diag block */
 
+/* ---- allocation-free local inner products ---------------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  out[j] = <V_j, x> over n local entries for j < k,
+ * V_j = V + j * ld; V, x and out are DEVICE pointers of the caller (V and x 16-byte aligned, ld even and >= n when k > 1).  It is the
+ * multi-dot kernel of the GMRES path (what HYPRE_ParVectorInnerProd runs for k = 1) with the same launch grid, but its per-block
+ * partial sums and its arrival counter live in a file-scope device array of 128 KiB + 256 B inside the library (held by every
+ * GPU that loads the library until the process exits) instead of an allocated work buffer; the call makes no cudaMalloc /
+ * cudaFree / pool allocation and creates no stream or event.  Limits, rejected with an error flag and a message
+ * (b200hypre_last_error): k <= 64 vectors per call, a launch grid of at most 2048 blocks (the grid is min(ceil(n / 2048), 8 x SM
+ * count): 1184 on B200, any n).  HYPRE_Init must have run (it creates the library stream); the first call on a device resolves the
+ * array's address with cudaGetSymbolAddress, so make that call outside a capture.  The work is ordered on b200hypre_stream() and
+ * NOT synchronised; local to the rank (no all-reduce).  All calls share the one array and it keeps the last call's contents (the
+ * counter is cleared at the start of every call, the partials are written before they are read): calls that overlap on the GPU
+ * -- issued from several host threads or replayed from graphs on different streams -- race; issue them in stream order. */
+HYPRE_Int b200hypre_multi_dot_noalloc(const HYPRE_Complex *V, HYPRE_BigInt ld, HYPRE_Int k, const HYPRE_Complex *x, HYPRE_BigInt n,
+                                      HYPRE_Complex *out);
+
 /* ---- test hooks: building blocks on host CSR arrays (int32 indices), results returned in malloc'ed host arrays that the
  * caller releases with b200hypre_host_free ---------------------------------------------------------------------------------- */
 HYPRE_Int b200hypre_test_spgemm(HYPRE_Int a_nr, HYPRE_Int a_nc, const HYPRE_Int *a_ptr, const HYPRE_Int *a_col, const HYPRE_Complex *a_val,
