@@ -230,6 +230,10 @@ void csr_transpose(const DCsr &A, DCsr &T);
 void csr_spgemm(const DCsr &A, const DCsr &B, DCsr &C, bool diag_first, bool sorted = true);
 void build_interp(const DCsr &Aext, const int *Sptr, const int *Scol, i64 S_nnz, const int *cf, const int *f2c, int n_own, int n_rows,
                   double tf, int pmax, DCsr &P);
+// interp_type 0 (classical modified interpolation), same contract
+void build_interp_classical(const DCsr &Aext, const int *Sptr, const int *Scol, i64 S_nnz, const int *cf, const int *f2c, int n_own, int n_rows,
+                  double tf, int pmax, DCsr &P);
+inline bool interp_type_built(int t) { return t == 6 || t == 0; }
 
 // ---- generator (generator.cu): laplace_3d_weak_scaling semantics --------------------------------------------------------
 // fills device COO (global ids) + rhs for this rank's box; returns nnz.  Arrays are allocated by the callee.

@@ -794,7 +794,8 @@ bool coarsen_level_dist(Amg &amg, AmgLevel &L, AmgLevel &Lc) {
     st.reset();
     {
       PhaseTimerD t2(amg, "interp.build");
-      build_interp(Aext, Sext.ptr.p, Sext.col.p, Sext.nnz, cf_ext.p, f2c_ext.p, n, n, o.trunc_factor, o.p_max_elmts, Pm);
+      if (o.interp_type == 0) build_interp_classical(Aext, Sext.ptr.p, Sext.col.p, Sext.nnz, cf_ext.p, f2c_ext.p, n, n, o.trunc_factor, o.p_max_elmts, Pm);
+      else build_interp(Aext, Sext.ptr.p, Sext.col.p, Sext.nnz, cf_ext.p, f2c_ext.p, n, n, o.trunc_factor, o.p_max_elmts, Pm);
     }
     {
       PhaseTimerD t3(amg, "interp.split");

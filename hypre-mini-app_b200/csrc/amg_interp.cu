@@ -300,4 +300,87 @@ void build_interp(const DCsr &Aext, const int *Sptr, const int *Scol, i64 S_nnz,
   B200_KERNEL_CHECK();
 }
 
+// ---- classical "modified" interpolation (interp_type 0) ------------------------------------------------------------------------------
+// Replaces hypre_BoomerAMGBuildInterp + hypre_BoomerAMGInterpTruncation, which the reference reaches when its input sets
+// interp_type: 0 (/root/reference/src/HypreSystem.cpp:195-198; its sample input etc/hypre_app.yaml:41 does).  rows::classical_row is
+// the definition.  A row only touches its own entries and the rows of its strong F neighbours, and its interpolatory set is a subset of
+// its strength row, so one thread per row works in place in a scratch laid out like the strength pattern (entry k of row i at
+// Sptr[i] + k): no capacity tiers, no overflow path.  The second kernel packs the rows.
+namespace {
+
+// CAP: strength rows of up to CAP entries build their row in thread-local arrays (registers / L1-resident local memory) and write
+// it to the scratch once; with the list in global memory every `w_j += ...` of the walk is a dependent round trip to L2 (measured
+// at 256^3: the phase took as long as the whole ext+i interpolation).  Longer rows work in place in the scratch.
+template <int CAP>
+__global__ void __launch_bounds__(128) k_classical_rows(rows::Csr A, const int *__restrict__ Sptr, const int *__restrict__ Scol,
+                                                        const int *__restrict__ cf, const int *__restrict__ f2c, int n_own, int n_rows,
+                                                        double tf, int pmax, int *sc, double *sv, int *len) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_rows) return;
+  int L;
+  if (cf[i] >= 0) L = 1;
+  else if (cf[i] == -3) L = 0;
+  else {
+    const int sb = Sptr[i];
+    if (Sptr[i + 1] - sb <= CAP) {
+      int lc[CAP];
+      double lv[CAP];
+      L = rows::classical_row(A, Sptr, Scol, cf, f2c, n_own, i, tf, pmax, sc + sb, sv + sb, lc, lv);
+    } else {
+      L = rows::classical_row(A, Sptr, Scol, cf, f2c, n_own, i, tf, pmax, sc + sb, sv + sb, sc + sb, sv + sb);
+    }
+  }
+  len[i] = L;
+}
+
+__global__ void k_classical_pack(int n_rows, const int *__restrict__ Sptr, const int *__restrict__ cf, const int *__restrict__ f2c,
+                                 const int *__restrict__ sc, const double *__restrict__ sv, const int *__restrict__ Pptr, int *Pcol,
+                                 double *Pval) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_rows) return;
+  const int b = Pptr[i], L = Pptr[i + 1] - b;
+  if (cf[i] >= 0) {
+    Pcol[b] = f2c[i];
+    Pval[b] = 1.0;
+    return;
+  }
+  const int s = Sptr[i];
+  for (int k = 0; k < L; ++k) {
+    Pcol[b + k] = sc[s + k];
+    Pval[b + k] = sv[s + k];
+  }
+}
+
+}  // namespace
+
+void build_interp_classical(const DCsr &Aext, const int *Sptr, const int *Scol, i64 S_nnz, const int *cf, const int *f2c, int n_own,
+                            int n_rows, double tf, int pmax, DCsr &P) {
+  rows::Csr A{Aext.nr, Aext.nc, Aext.ptr.p, Aext.col.p, Aext.val.p};
+  P.nr = n_rows;
+  P.ptr.alloc((size_t)n_rows + 1);
+  if (n_rows == 0) { P.nnz = 0; P.ptr.zero(); return; }
+  DVec<int> sc((size_t)std::max<i64>(S_nnz, 1)), len((size_t)n_rows + 1);
+  DVec<double> sv((size_t)std::max<i64>(S_nnz, 1));
+  B200_CUDA(cudaMemsetAsync(len.p + n_rows, 0, sizeof(int), stream()));
+  {
+    // algorithmic bytes: A and S read once, markers, the rows of P written once
+    ProfScope prof("interp_rows", 12.0 * (double)Aext.nnz + 4.0 * (double)S_nnz + 16.0 * (double)Aext.nr + 12.0 * (double)S_nnz * 0.5);
+    k_classical_rows<32><<<div_up(n_rows, 128), 128, 0, stream()>>>(A, Sptr, Scol, cf, f2c, n_own, n_rows, tf, pmax, sc.p, sv.p, len.p);
+    count_launch();
+  }
+  {
+    size_t tb = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tb, len.p, P.ptr.p, n_rows + 1, stream());
+    DVec<char> tmp(tb);
+    cub::DeviceScan::ExclusiveSum(tmp.p, tb, len.p, P.ptr.p, n_rows + 1, stream());
+    count_launch(2);
+  }
+  P.nnz = checked_total(len.p, n_rows, "build_interp_classical");
+  P.col.alloc((size_t)std::max<i64>(P.nnz, 1));
+  P.val.alloc((size_t)std::max<i64>(P.nnz, 1));
+  k_classical_pack<<<div_up(n_rows, 128), 128, 0, stream()>>>(n_rows, Sptr, cf, f2c, sc.p, sv.p, P.ptr.p, P.col.p, P.val.p);
+  count_launch();
+  B200_KERNEL_CHECK();
+}
+
 }  // namespace b200

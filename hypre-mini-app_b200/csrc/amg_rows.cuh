@@ -130,6 +130,55 @@ B200_HD int list_find(const int *lc, int L, int key) {
   return -1;
 }
 
+// ---- hypre_BoomerAMGInterpTruncation on one row whose columns are still fine ids (lc) with weights lv: relative threshold, then
+// the p_max largest by qsort2abs' order, each with its rescaling; own-range columns (< n_own) stay in front.  Writes the coarse
+// columns f2c[lc[k]] and the weights to oc / ov (may alias lc / lv) and returns the final length.
+B200_HD int trunc_emit(int *lc, double *lv, int L, bool any_off, int n_own, const int *f2c, double trunc_factor, int p_max, int *oc,
+                       double *ov) {
+  // keep fine ids for the own/off test during re-splitting; translate at the end
+  int len = L;
+  if (trunc_factor > 0.0 && len > 0) {
+    double max_coef = 0.0, row_sum = 0.0, scale = 0.0;
+    for (int k = 0; k < len; ++k) { double a = fabs(lv[k]); max_coef = (a > max_coef) ? a : max_coef; }
+    max_coef = max_coef * trunc_factor;
+    int w = 0;
+    for (int k = 0; k < len; ++k) {
+      row_sum = row_sum + lv[k];
+      if (fabs(lv[k]) >= max_coef) { scale = scale + lv[k]; lc[w] = lc[k]; lv[w] = lv[k]; ++w; }
+    }
+    len = w;
+    if (scale != 0.0 && scale != row_sum) {
+      double f = row_sum / scale;
+      for (int k = 0; k < len; ++k) lv[k] = lv[k] * f;
+    }
+  }
+  if (p_max > 0 && len > p_max) {
+    double row_sum = 0.0, scale = 0.0;
+    for (int k = 0; k < len; ++k) row_sum = row_sum + lv[k];
+    qsort2abs(lc, lv, len, p_max);
+    for (int k = 0; k < p_max; ++k) scale = scale + lv[k];
+    len = p_max;
+    if (scale != 0.0 && scale != row_sum) {
+      double f = row_sum / scale;
+      for (int k = 0; k < len; ++k) lv[k] = lv[k] * f;
+    }
+    if (any_off) {  // re-split, each part keeping the sorted order
+      for (int k = 1; k < len; ++k) {
+        int v = lc[k];
+        double x = lv[k];
+        if (v < n_own) {
+          int p = k;
+          while (p > 0 && lc[p - 1] >= n_own) { lc[p] = lc[p - 1]; lv[p] = lv[p - 1]; --p; }
+          lc[p] = v;
+          lv[p] = x;
+        }
+      }
+    }
+  }
+  for (int k = 0; k < len; ++k) { oc[k] = f2c[lc[k]]; ov[k] = lv[k]; }
+  return len;
+}
+
 // ---- A.5 extended+i interpolation row + truncation.
 // A, S in local (extended) numbering; rows/cols < n_own are owned by this rank.  f2c maps a fine point to its coarse
 // column index in the same (extended) coarse numbering; a coarse column is "own" iff its fine point is < n_own.
@@ -218,55 +267,76 @@ B200_HD int interp_row(const Csr &A, const int *Sptr, const int *Scol, const int
     double md = -diagonal;
     for (int k = 0; k < L; ++k) lv[k] = lv[k] / md;
   }
-  // own/off flags are needed after the columns are translated: remember the split point
-  int n_own_entries = L;
-  if (any_off) {
-    n_own_entries = 0;
-    while (n_own_entries < L && lc[n_own_entries] < n_own) ++n_own_entries;
+  return trunc_emit(lc, lv, L, any_off, n_own, f2c, trunc_factor, p_max, oc, ov);
+}
+
+// ---- classical "modified" interpolation row (interp_type 0, hypre_BoomerAMGBuildInterp) + truncation: the reference's sample input
+// selects it (/root/reference/etc/hypre_app.yaml:41 through src/HypreSystem.cpp:195-198).  Same conventions as interp_row.  The
+// interpolatory set is C_i = the strong C neighbours of i in the order of the strength row; a strong F neighbour k is distributed over
+// C_i in proportion to the a_km (m in C_i) whose sign is opposite to a_kk, or goes to the diagonal when there is none; weak neighbours
+// go to the diagonal.  lc / lv: scratch of at least (length of the strength row of i) entries; oc / ov may alias them.
+// Rows of C points (one entry, 1.0) and of special points (empty) are the caller's: call this for cf[i] == -1 only.
+B200_HD int classical_row(const Csr &A, const int *Sptr, const int *Scol, const int *cf, const int *f2c, int n_own, int i,
+                          double trunc_factor, int p_max, int *oc, double *ov, int *lc, double *lv) {
+  int L = 0;
+  bool any_off = false;
+  for (int kk = Sptr[i]; kk < Sptr[i + 1]; ++kk) {
+    const int j = Scol[kk];
+    if (cf[j] >= 0) { lc[L++] = j; any_off |= (j >= n_own); }
   }
-  (void)n_own_entries;
-  // keep fine ids for the own/off test during re-splitting; translate at the end
-  int len = L;
-  if (trunc_factor > 0.0 && len > 0) {
-    double max_coef = 0.0, row_sum = 0.0, scale = 0.0;
-    for (int k = 0; k < len; ++k) { double a = fabs(lv[k]); max_coef = (a > max_coef) ? a : max_coef; }
-    max_coef = max_coef * trunc_factor;
-    int w = 0;
-    for (int k = 0; k < len; ++k) {
-      row_sum = row_sum + lv[k];
-      if (fabs(lv[k]) >= max_coef) { scale = scale + lv[k]; lc[w] = lc[k]; lv[w] = lv[k]; ++w; }
-    }
-    len = w;
-    if (scale != 0.0 && scale != row_sum) {
-      double f = row_sum / scale;
-      for (int k = 0; k < len; ++k) lv[k] = lv[k] * f;
-    }
-  }
-  if (p_max > 0 && len > p_max) {
-    double row_sum = 0.0, scale = 0.0;
-    for (int k = 0; k < len; ++k) row_sum = row_sum + lv[k];
-    qsort2abs(lc, lv, len, p_max);
-    for (int k = 0; k < p_max; ++k) scale = scale + lv[k];
-    len = p_max;
-    if (scale != 0.0 && scale != row_sum) {
-      double f = row_sum / scale;
-      for (int k = 0; k < len; ++k) lv[k] = lv[k] * f;
-    }
-    if (any_off) {  // re-split, each part keeping the sorted order
-      for (int k = 1; k < len; ++k) {
-        int v = lc[k];
-        double x = lv[k];
-        if (v < n_own) {
-          int p = k;
-          while (p > 0 && lc[p - 1] >= n_own) { lc[p] = lc[p - 1]; lv[p] = lv[p - 1]; --p; }
-          lc[p] = v;
-          lv[p] = x;
-        }
+  if (any_off) {  // own-range C points first (P_diag before P_offd); a no-op for rows stored diag | offd
+    for (int k = 1; k < L; ++k) {
+      const int v = lc[k];
+      if (v < n_own) {
+        int p = k;
+        while (p > 0 && lc[p - 1] >= n_own) { lc[p] = lc[p - 1]; --p; }
+        lc[p] = v;
       }
     }
   }
-  for (int k = 0; k < len; ++k) { oc[k] = f2c[lc[k]]; ov[k] = lv[k]; }
-  return len;
+  for (int k = 0; k < L; ++k) lv[k] = 0.0;
+  double diagonal = A.val[A.ptr[i]];
+  int sp = Sptr[i];
+  const int se = Sptr[i + 1];
+  for (int jj = A.ptr[i] + 1; jj < A.ptr[i + 1]; ++jj) {
+    const int j = A.col[jj];
+    const double aij = A.val[jj];
+    const bool strong = (sp < se) && (Scol[sp] == j);
+    if (strong) ++sp;
+    if (strong && cf[j] >= 0) {
+      const int pos = list_find(lc, L, j);
+      lv[pos] = lv[pos] + aij;
+    } else if (strong && cf[j] != -3) {
+      const int b1 = A.ptr[j], e1 = A.ptr[j + 1];
+      const double sgn = (A.val[b1] < 0) ? -1.0 : 1.0;
+      double sum = 0.0;
+      for (int j1 = b1 + 1; j1 < e1; ++j1) {
+        const double a = A.val[j1];
+        if ((sgn * a) < 0 && list_find(lc, L, A.col[j1]) >= 0) sum = sum + a;
+      }
+      if (sum != 0.0) {
+        const double distribute = aij / sum;
+        for (int j1 = b1 + 1; j1 < e1; ++j1) {
+          const double a = A.val[j1];
+          if ((sgn * a) < 0) {
+            const int p2 = list_find(lc, L, A.col[j1]);
+            if (p2 >= 0) { const double t = distribute * a; lv[p2] = lv[p2] + t; }
+          }
+        }
+      } else {
+        diagonal = diagonal + aij;
+      }
+    } else if (cf[j] != -3) {
+      diagonal = diagonal + aij;
+    }
+  }
+  if (diagonal == 0.0) {
+    for (int k = 0; k < L; ++k) lv[k] = 0.0;
+  } else {
+    const double md = -diagonal;
+    for (int k = 0; k < L; ++k) lv[k] = lv[k] / md;
+  }
+  return trunc_emit(lc, lv, L, any_off, n_own, f2c, trunc_factor, p_max, oc, ov);
 }
 
 // ---- smoother diagonal: relax 7 -> a_ii ; relax 18 -> l1 norm (sign of a_ii), SURVEY.md A.7

@@ -357,7 +357,8 @@ bool coarsen_level(Amg &amg, AmgLevel &L, AmgLevel &Lc) {
     PhaseTimer t(amg, "interp");
     DCsr &P = L.P.diag;
     P.nc = nc;
-    build_interp(A, L.Sptr.p, L.Scol.p, L.S_nnz, L.cf_raw.p, f2c.p, n, n, o.trunc_factor, o.p_max_elmts, P);
+    if (o.interp_type == 0) build_interp_classical(A, L.Sptr.p, L.Scol.p, L.S_nnz, L.cf_raw.p, f2c.p, n, n, o.trunc_factor, o.p_max_elmts, P);
+    else build_interp(A, L.Sptr.p, L.Scol.p, L.S_nnz, L.cf_raw.p, f2c.p, n, n, o.trunc_factor, o.p_max_elmts, P);
     L.cf.alloc((size_t)n);
     k_fold_sf<<<g, 256, 0, stream()>>>(n, L.cf_raw.p, L.cf.p);
     count_launch();
@@ -416,9 +417,11 @@ void amg_setup(Amg &amg, ParCsr &A) {
   cudaEventCreate(&e1);
   cudaEventRecord(e0, stream());
   const AmgOptions &o = amg.opt;
-  B200_REQUIRE(o.coarsen_type == 8 || o.coarsen_type == 10 || o.max_levels == 1,
-               "BoomerAMG: only coarsen_type 8 (PMIS; 10/HMIS is mapped to PMIS) is built in this round");
-  B200_REQUIRE(o.interp_type == 6 || o.max_levels == 1, "BoomerAMG: only interp_type 6 (extended+i) is built in this round");
+  B200_REQUIRE(o.coarsen_type == 8 || o.coarsen_type == 10 || o.coarsen_type == 6 || o.max_levels == 1,
+               "BoomerAMG: coarsen_type must be 8 (PMIS); 10 (HMIS) and 6 (Falgout) are accepted and run as PMIS with a warning; got " +
+                   std::to_string(o.coarsen_type));
+  B200_REQUIRE(interp_type_built(o.interp_type) || o.max_levels == 1,
+               "BoomerAMG: interp_type must be 6 (extended+i) or 0 (classical modified); got " + std::to_string(o.interp_type));
   // coarsest level: Gaussian elimination (relax_type[3] = 9, what HYPRE_BoomerAMGSetRelaxType leaves there); any other
   // coarse_relax_type (HYPRE_BoomerAMGSetCycleRelaxType(.., 3), HypreSystem.cpp:135-136) is refused rather than ignored
   B200_REQUIRE(o.relax_type[3] == 9 || o.max_levels == 1,
@@ -432,12 +435,15 @@ void amg_setup(Amg &amg, ParCsr &A) {
                    (is_gs_relax(o.relax_type[1]) && is_gs_relax(o.relax_type[2]) &&
                     is_l1_gs_relax(o.relax_type[1]) == is_l1_gs_relax(o.relax_type[2])),
                "BoomerAMG: down and up smoothers must share their diagonal scaling (same relax_type family)");
-  if (o.coarsen_type == 10 && o.max_levels > 1 && ctx().rank == 0) {
-    static bool warned = false;
-    if (!warned)
-      fprintf(stderr, "[b200hypre] warning: coarsen_type 10 (HMIS) is run as coarsen_type 8 (PMIS): the Ruge-Stueben first pass of HMIS "
-                      "is not built; the hierarchy is the PMIS one\n");
-    warned = true;
+  if ((o.coarsen_type == 10 || o.coarsen_type == 6) && o.max_levels > 1 && ctx().rank == 0) {
+    static bool warned[2] = {false, false};
+    const int w = o.coarsen_type == 10 ? 0 : 1;
+    if (!warned[w])
+      fprintf(stderr, w == 0 ? "[b200hypre] warning: coarsen_type 10 (HMIS) is run as coarsen_type 8 (PMIS): the Ruge-Stueben first pass of HMIS "
+                               "is not built; the hierarchy is the PMIS one\n"
+                             : "[b200hypre] warning: coarsen_type 6 (Falgout) is run as coarsen_type 8 (PMIS): the Ruge-Stueben passes and CLJP "
+                               "are not built; the hierarchy is the PMIS one\n");
+    warned[w] = true;
   }
   if (amg.graph_exec) { cudaGraphExecDestroy(amg.graph_exec); amg.graph_exec = nullptr; }
   amg.setup_phase_ms.clear();

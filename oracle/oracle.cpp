@@ -758,6 +758,137 @@ static void interp_extpi(const Csr &A, const Csr &S, const std::vector<int> &cf,
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// Classical "modified" interpolation (interp_type 0: hypre_BoomerAMGBuildInterp, parcsr_ls/par_interp.c) followed by the same
+// hypre_BoomerAMGInterpTruncation.  The reference's sample input asks for it (/root/reference/etc/hypre_app.yaml:41 through
+// src/HypreSystem.cpp:195-198).  For an F point i the interpolatory set is C_i = its strong C neighbours, in the order of the
+// strength row (own-range columns first: P_diag before P_offd).  Walking row i after its diagonal, in storage order:
+//   a strong C neighbour j            adds a_ij to w_j;
+//   a strong F neighbour k            is distributed over C_i: with sgn = sign(a_kk) and sum = sum of the a_km, m in C_i, of
+//                                     sign opposite to a_kk (row k in storage order), every such m gets (a_ik / sum) a_km;
+//                                     when sum == 0 the entry goes to the diagonal instead;
+//   any other neighbour (weak)        goes to the diagonal, unless it is a special point (CF -3).
+// Then w_j /= -diagonal (all zero when the diagonal vanished).  Unlike ext+i (above) there is no distance-two C point and no
+// a_ki term.  Same conventions as interp_extpi for cf, cpart and the order of the truncated rows.
+// ---------------------------------------------------------------------------------------------------------
+static int truncate_row(int *lc, double *lv, int len, int c0, int c1, double trunc_factor, int p_max) {
+  if (trunc_factor > 0.0 && len > 0) {
+    double max_coef = 0.0, row_sum = 0.0, scale = 0.0;
+    for (int k = 0; k < len; ++k) max_coef = std::max(max_coef, std::fabs(lv[k]));
+    max_coef *= trunc_factor;
+    int w = 0;
+    for (int k = 0; k < len; ++k) {
+      row_sum += lv[k];
+      if (std::fabs(lv[k]) >= max_coef) { scale += lv[k]; lc[w] = lc[k]; lv[w] = lv[k]; ++w; }
+    }
+    len = w;
+    if (scale != 0.0 && scale != row_sum) {
+      double f = row_sum / scale;
+      for (int k = 0; k < len; ++k) lv[k] *= f;
+    }
+  }
+  if (p_max > 0 && len > p_max) {
+    double row_sum = 0.0, scale = 0.0;
+    for (int k = 0; k < len; ++k) row_sum += lv[k];
+    qsort2abs(lc, lv, 0, len - 1);
+    for (int k = 0; k < p_max; ++k) scale += lv[k];
+    len = p_max;
+    if (scale != 0.0 && scale != row_sum) {
+      double f = row_sum / scale;
+      for (int k = 0; k < len; ++k) lv[k] *= f;
+    }
+    std::vector<int> tc;      // re-split: own-range coarse columns first, each part keeping the sorted order
+    std::vector<double> tv;
+    for (int k = 0; k < len; ++k)
+      if (lc[k] >= c0 && lc[k] < c1) { tc.push_back(lc[k]); tv.push_back(lv[k]); }
+    for (int k = 0; k < len; ++k)
+      if (!(lc[k] >= c0 && lc[k] < c1)) { tc.push_back(lc[k]); tv.push_back(lv[k]); }
+    for (int k = 0; k < len; ++k) { lc[k] = tc[k]; lv[k] = tv[k]; }
+  }
+  return len;
+}
+
+static void interp_classical(const Csr &A, const Csr &S, const std::vector<int> &cf, const std::vector<int> &f2c,
+                             const std::vector<int> &rpart, const std::vector<int> &cpart, int ncoarse, double trunc_factor,
+                             int p_max, Csr &P) {
+  const int n = A.nr;
+  P.nr = n;
+  P.nc = ncoarse;
+  std::vector<std::vector<int>> rc(n);
+  std::vector<std::vector<double>> rv(n);
+#pragma omp parallel
+  {
+    std::vector<int> where(n, -1);       // position of a C point in the list of the current row; -2 - i: strong F neighbour of i
+    std::vector<int> lc, touched;
+    std::vector<double> lv;
+#pragma omp for schedule(dynamic, 256)
+    for (int i = 0; i < n; ++i) {
+      if (cf[i] >= 0) {
+        rc[i].assign(1, f2c[i]);
+        rv[i].assign(1, 1.0);
+        continue;
+      }
+      if (cf[i] == -3) continue;
+      const int r = owner_of(rpart, i);
+      const int strong_f = -2 - i;
+      lc.clear();
+      touched.clear();
+      // the strength row lists own-range columns first (parcsr_order), so this is P_diag's order followed by P_offd's
+      for (int kk = S.ptr[i]; kk < S.ptr[i + 1]; ++kk) {
+        const int j = S.col[kk];
+        if (cf[j] >= 0) { where[j] = (int)lc.size(); lc.push_back(j); touched.push_back(j); }
+        else if (cf[j] != -3) { where[j] = strong_f; touched.push_back(j); }
+      }
+      lv.assign(lc.size(), 0.0);
+      double diagonal = A.val[A.ptr[i]];
+      for (int jj = A.ptr[i] + 1; jj < A.ptr[i + 1]; ++jj) {
+        const int j = A.col[jj];
+        const double aij = A.val[jj];
+        if (where[j] >= 0) {
+          lv[where[j]] += aij;
+        } else if (where[j] == strong_f) {
+          const double sgn = (A.val[A.ptr[j]] < 0) ? -1.0 : 1.0;
+          double sum = 0.0;
+          for (int j1 = A.ptr[j]; j1 < A.ptr[j + 1]; ++j1) {
+            const int m = A.col[j1];
+            if (where[m] >= 0 && (sgn * A.val[j1]) < 0) sum += A.val[j1];
+          }
+          if (sum != 0.0) {
+            const double distribute = aij / sum;
+            for (int j1 = A.ptr[j]; j1 < A.ptr[j + 1]; ++j1) {
+              const int m = A.col[j1];
+              if (where[m] >= 0 && (sgn * A.val[j1]) < 0) lv[where[m]] += distribute * A.val[j1];
+            }
+          } else {
+            diagonal += aij;
+          }
+        } else if (cf[j] != -3) {
+          diagonal += aij;
+        }
+      }
+      if (diagonal == 0.0) {
+        for (double &w : lv) w = 0.0;
+      } else {
+        for (double &w : lv) w /= -diagonal;
+      }
+      for (int j : touched) where[j] = -1;
+      for (int &c : lc) c = f2c[c];
+      const int len = truncate_row(lc.data(), lv.data(), (int)lc.size(), cpart[r], cpart[r + 1], trunc_factor, p_max);
+      rc[i].assign(lc.begin(), lc.begin() + len);
+      rv[i].assign(lv.begin(), lv.begin() + len);
+    }
+  }
+  P.ptr.assign(n + 1, 0);
+  for (int i = 0; i < n; ++i) P.ptr[i + 1] = P.ptr[i] + (int)rc[i].size();
+  P.col.resize(P.ptr[n]);
+  P.val.resize(P.ptr[n]);
+#pragma omp parallel for schedule(static)
+  for (int i = 0; i < n; ++i) {
+    std::copy(rc[i].begin(), rc[i].end(), P.col.begin() + P.ptr[i]);
+    std::copy(rv[i].begin(), rv[i].end(), P.val.begin() + P.ptr[i]);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // smoother data
 // ---------------------------------------------------------------------------------------------------------
 static inline bool is_gs(int t) { return t == 3 || t == 4 || t == 6 || t == 8 || t == 13 || t == 14; }
@@ -928,7 +1059,8 @@ static void amg_setup(Sys &s) {
       }
       if (nc == 0 || nc == fine || nc < o.min_coarse_size) last = true;
       else {
-        interp_extpi(L.A, L.S, L.cf_raw, f2c, L.part, cpart, nc, o.trunc_factor, o.p_max_elmts, L.P);
+        if (o.interp_type == 0) interp_classical(L.A, L.S, L.cf_raw, f2c, L.part, cpart, nc, o.trunc_factor, o.p_max_elmts, L.P);
+        else interp_extpi(L.A, L.S, L.cf_raw, f2c, L.part, cpart, nc, o.trunc_factor, o.p_max_elmts, L.P);
         L.cf = L.cf_raw;
         for (int &c : L.cf) if (c == -3) c = -1;
         L.R = transpose(L.P);

@@ -20,16 +20,21 @@ CASES = {
     "lap7_8": dict(n=8, stencil=7, grid=(1, 1, 1), opts=dict(strong_threshold=0.25, tolerance=1e-8, kspace=50, max_iterations=100)),
     "lap27_6": dict(n=6, stencil=27, grid=(1, 1, 1), opts=dict(strong_threshold=0.57, tolerance=1e-8, kspace=50, max_iterations=100)),
     "lap7_6_2ranks": dict(n=6, stencil=7, grid=(2, 1, 1), opts=dict(strong_threshold=0.25, tolerance=1e-8, kspace=50, max_iterations=100)),
+    # classical modified interpolation (interp_type 0, the reference's sample input), on two virtual ranks
+    "lap7_8_classical_2ranks": dict(n=(8, 8, 4), stencil=7, grid=(1, 1, 2),
+                                    opts=dict(strong_threshold=0.25, interp_type=0, tolerance=1e-8, kspace=50, max_iterations=100)),
 }
 
 
 def main():
     for name, c in CASES.items():
+        if len(sys.argv) > 1 and name not in sys.argv[1:]:   # python tests/golden/make_golden.py [case ...]
+            continue
         o = Oracle(**c["opts"])
         o.gen_laplace(c["n"], p=c["grid"], stencil=c["stencil"])
         o.setup()
         x = o.solve()
-        out = {"n": c["n"], "stencil": c["stencil"], "grid": np.array(c["grid"]), "num_levels": o.num_levels,
+        out = {"n": np.array(c["n"]), "stencil": c["stencil"], "grid": np.array(c["grid"]), "num_levels": o.num_levels,
                "iterations": o.iterations, "x": x, "history": o.history(), "relres": o.relres}
         for k, v in c["opts"].items():
             out["opt_" + k] = v

@@ -330,3 +330,70 @@ def test_unmodified_reference_host_runs_on_the_library(app, tmp_path, linsys_typ
         sols[name] = read_ijv(wd / "IJV0.sln.00000")
     assert np.abs(sols["reference"] - xref).max() <= 1e-7 * max(1.0, np.abs(xref).max())
     assert np.abs(sols["reference"] - sols["twin"]).max() <= 1e-12 * max(1.0, np.abs(xref).max())
+
+
+SAMPLE_INPUT = """linear_system:
+  type: matrix_market
+  matrix_file: mat.mm
+  rhs_file: rhs.mm
+  sln_file: sln.mm
+  write_outputs: false
+  num_partitions: 2
+  write_solution: true
+  rtol: 1.0e-3
+  atol: 1.0e-5
+
+solver_settings:
+  method: gmres
+  preconditioner: boomeramg
+  tolerance: 1.0e-6
+  max_iterations: 100
+  kspace: 10
+  print_level: 4
+  reuse_preconditioner: false
+
+boomeramg_settings:
+  print_level: 1
+  max_iterations: 1
+  tolerance: 0.0
+  coarsen_type: 6
+  cycle_type: 1
+  relax_type: 6
+  relax_order: 1
+  num_sweeps: 2
+  max_levels: 20
+  interp_type: 0
+  strong_threshold: 0.57
+"""
+
+
+def test_reference_sample_input_runs_through_both_hosts(app, tmp_path):
+    """the options of the reference's sample input (/root/reference/etc/hypre_app.yaml: every key and value of its three sections;
+    write_solution added so that the result can be read back, rtol / atol of the solution check widened to what a solve to the
+    sample's tolerance of 1e-6 can meet) on a MatrixMarket system: classical interpolation (interp_type 0) is
+    built, coarsen_type 6 runs as PMIS with a warning on stderr.  Round 1 rejected this input at Setup."""
+    n = 12
+    A = laplace3d(n).tocsr()
+    rng = np.random.default_rng(5)
+    xref = rng.standard_normal(A.shape[0])
+    b = A @ xref
+    write_mm_matrix(tmp_path / "mat.mm", A, shuffle=rng)
+    write_mm_vector(tmp_path / "rhs.mm", b)
+    write_mm_vector(tmp_path / "sln.mm", xref)
+    hosts = [("twin", app)] + ([("reference", REF_APP)] if os.path.exists(REF_APP) else [])
+    sols = {}
+    for name, exe in hosts:
+        wd = tmp_path / name
+        wd.mkdir()
+        for f in ("mat.mm", "rhs.mm", "sln.mm"):
+            os.symlink(tmp_path / f, wd / f)
+        (wd / "hypre_app.yaml").write_text(SAMPLE_INPUT)
+        r = subprocess.run([exe, "hypre_app.yaml"], cwd=wd, capture_output=True, text=True, timeout=600)
+        out = r.stdout + r.stderr
+        assert r.returncode == 0, out
+        assert "coarsen_type 6 (Falgout) is run as coarsen_type 8 (PMIS)" in out, out
+        assert "Timer summary" in out
+        sols[name] = read_ijv(wd / "IJV0.sln.00000")
+        assert np.abs(sols[name] - xref).max() <= 1e-4 * np.abs(xref).max(), name
+    if "reference" in sols:
+        assert np.abs(sols["reference"] - sols["twin"]).max() <= 1e-12 * np.abs(xref).max()

@@ -178,6 +178,16 @@ def test_multirank_truncation_modes(b200, pmax, tf):
     compare_with_oracle(res, n, grid, 7, 0.25, p_max_elmts=pmax, trunc_factor=tf)
 
 
+@pytest.mark.parametrize("n,grid,stencil,theta,pmax", [((10, 10, 10), (2, 1, 1), 7, 0.25, 4), ((6, 6, 6), (2, 2, 1), 27, 0.57, 0),
+                                                        ((8, 7, 6), (2, 2, 2), 7, 0.25, 2)])
+def test_multirank_classical_interpolation(b200, n, grid, stencil, theta, pmax):
+    """interp_type 0 across ranks: strong F neighbours on other ranks are distributed through their fetched rows (hypre's A_ext),
+    C points of other ranks land in P_offd: N ranks on one GPU against the N-virtual-rank oracle"""
+    nranks = grid[0] * grid[1] * grid[2]
+    res = run_ranks(nranks, settings(n, grid, stencil, strong_threshold=theta, interp_type=0, p_max_elmts=pmax))
+    compare_with_oracle(res, n, grid, stencil, theta, interp_type=0, p_max_elmts=pmax)
+
+
 @pytest.mark.parametrize("relax", [11, 12])
 def test_multirank_two_stage_gauss_seidel(b200, relax):
     """relax 11 / 12 on 2 ranks: the triangle is taken from every rank's own diagonal block (hybrid), off-rank couplings enter

@@ -357,3 +357,75 @@ def test_interpolation_truncation_modes_bit_exact(b200, n, stencil, theta, pmax,
     assert abs(s.solver.iterations - o.iterations) <= 1
     assert np.abs(s.solution() - 1.0).max() < 1e-6
     s.destroy_system()
+
+
+@pytest.mark.parametrize("n,stencil,theta,pmax,tf", [
+    (20, 7, 0.25, 4, 0.0),      # the mini-app's P_max_elmts default on the classical rows
+    (20, 7, 0.25, 0, 0.0),      # untruncated
+    (14, 27, 0.57, 0, 0.0),     # the sample input's threshold on the reference generator's stencil
+    (14, 27, 0.25, 2, 0.0),     # rows longer than P_max: qsort2abs tie order
+    (24, 7, 0.25, 3, 0.2),      # both truncation rules
+    (48, 7, 0.25, 4, 0.0),
+])
+def test_classical_interpolation_bit_exact(b200, n, stencil, theta, pmax, tf):
+    """interp_type 0 (classical modified interpolation, hypre_BoomerAMGBuildInterp): what the reference's sample input selects
+    (etc/hypre_app.yaml:41).  Whole hierarchy bit for bit against the oracle, iterations within one, solution within 1e-10."""
+    s = make_system(b200, n, stencil, strong_threshold=theta, interp_type=0, p_max_elmts=pmax, trunc_factor=tf)
+    s.solver.destroy()
+    s.solver = b200.GMRES(tolerance=1e-8, max_iterations=200, kspace=50, orthogonalization="mgs")
+    s.solve()
+    o = make_oracle(n, stencil, strong_threshold=theta, interp_type=0, p_max_elmts=pmax, trunc_factor=tf)
+    o.setup()
+    xo = o.solve()
+    amg = s.precond
+    assert amg.num_levels == o.num_levels
+    for l in range(o.num_levels):
+        assert_same_csr(amg.level_matrix(l, "A"), o.matrix(l, "A"), f"A[{l}]")
+        if l + 1 < o.num_levels:
+            assert np.array_equal(amg.level_cf(l), o.cf(l)), f"CF[{l}] differs"
+            assert_same_csr(amg.level_matrix(l, "P"), o.matrix(l, "P"), f"P[{l}]")
+            assert_same_csr(amg.level_matrix(l, "R"), o.matrix(l, "R"), f"R[{l}]")
+    assert abs(s.solver.iterations - o.iterations) <= 1
+    assert s.solver.converged == 1
+    x = s.solution()
+    assert np.abs(x - 1.0).max() < 1e-6
+    if s.solver.iterations == o.iterations:
+        assert np.abs(x - xo).max() / np.abs(xo).max() <= VAL_RTOL
+    # not the ext+i hierarchy: a different operator is being built, not the default under another name
+    e = make_oracle(n, stencil, strong_threshold=theta, p_max_elmts=pmax, trunc_factor=tf)
+    e.setup()
+    assert len(e.matrix(0, "P")[1]) != len(o.matrix(0, "P")[1])
+    s.destroy_system()
+
+
+def test_reference_sample_input_settings_run(b200):
+    """boomeramg_settings of /root/reference/etc/hypre_app.yaml:30-42, verbatim: coarsen_type 6 (Falgout; run as PMIS, said on
+    stderr), relax_type 6 with relax_order 1 and two sweeps, interp_type 0, strong_threshold 0.57, with its solver_settings
+    (GMRES, kspace 10, tolerance 1e-6) on the reference generator's 27-point system.  The solve must converge to the generator's
+    known answer, and the hierarchy must be the oracle's for the same options with PMIS in place of Falgout."""
+    sample = dict(print_level=1, max_iterations=1, tolerance=0.0, coarsen_type=6, cycle_type=1, relax_type=6, relax_order=1,
+                  num_sweeps=2, max_levels=20, interp_type=0, strong_threshold=0.57)
+    n = 16
+    settings = {
+        "linear_system": {"type": "build_27pt_stencil", "nx": n, "ny": n, "nz": n},
+        "solver_settings": {"method": "gmres", "preconditioner": "boomeramg", "tolerance": 1e-6, "kspace": 10, "max_iterations": 100,
+                            "print_level": 0},
+        "boomeramg_settings": sample,
+    }
+    s = b200.HypreSystem(settings)
+    s.setup_precon_and_solver()
+    s.load()
+    s.solve()
+    assert s.solver.converged == 1 and s.solver.iterations < 30
+    assert np.abs(s.solution() - 1.0).max() < 1e-4
+    o = make_oracle(n, 27, strong_threshold=0.57, interp_type=0, coarsen_type=8, relax_type=6, relax_order=1, num_sweeps=2,
+                    tolerance=1e-6, kspace=10, max_iterations=100)
+    o.setup()
+    amg = s.precond
+    assert amg.num_levels == o.num_levels
+    for l in range(o.num_levels - 1):
+        assert np.array_equal(amg.level_cf(l), o.cf(l))
+        assert_same_csr(amg.level_matrix(l, "P"), o.matrix(l, "P"), f"P[{l}]")
+    o.solve()
+    assert abs(s.solver.iterations - o.iterations) <= 1
+    s.destroy_system()

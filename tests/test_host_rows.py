@@ -83,3 +83,47 @@ def test_device_workload_rows_match_numpy_builders(tmp_path, kind, n):
     else:
         assert np.abs(ent[:, 2] - coo.data).max() <= 1e-13 * np.abs(coo.data).max()
         assert np.abs(rhs - b).max() <= 1e-12 * np.abs(coo.data).max()
+
+
+@pytest.mark.skipif(shutil.which("nvcc") is None, reason="nvcc not on PATH")
+@pytest.mark.parametrize("interp_type", [0, 6])
+def test_interpolation_row_functions_equal_the_oracle_on_the_host(tmp_path, interp_type):
+    """rows::classical_row (interp_type 0, the reference's sample input) and rows::interp_row (ext+i) are the sequential definitions the
+    device kernels follow; compiled for the host with contraction off they must reproduce the oracle's P bit for bit, with every
+    truncation mode, on the first two levels of a 3-D Laplacian (7-point at level 0, the wider Galerkin stencil at level 1)."""
+    import numpy as np
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from oracle_lib import Oracle
+    exe = tmp_path / "classical_rows"
+    subprocess.check_call(["nvcc", "-std=c++17", "-O1", "-fmad=false", "-Xcompiler", "-ffp-contract=off", "-Wno-deprecated-gpu-targets",
+                           "-I", CSRC, "-o", str(exe), os.path.join(ROOT, "tests", "host", "classical_rows.cu")])
+    checked = 0
+    for tf, pmax in ((0.0, 0), (0.0, 2), (0.3, 0), (0.2, 3), (0.0, 4)):
+        o = Oracle(interp_type=interp_type, trunc_factor=tf, p_max_elmts=pmax, strong_threshold=0.25)
+        o.gen_laplace(14)
+        o.setup()
+        assert o.num_levels >= 3
+        for l in (0, 1):
+            ap, ac, av, shape = o.matrix(l, "A")
+            sp_, sc, _, _ = o.matrix(l, "S")
+            pp, pc, pv, _ = o.matrix(l, "P")
+            cf = o.cf(l)
+            n = shape[0]
+            fin, fout = tmp_path / "in.bin", tmp_path / "out.bin"
+            with open(fin, "wb") as f:
+                np.array([n, len(ac), len(sc), pmax], dtype=np.int32).tofile(f)
+                np.array([tf], dtype=np.float64).tofile(f)
+                for a, t in ((ap, np.int32), (ac, np.int32), (av, np.float64), (sp_, np.int32), (sc, np.int32), (cf, np.int32)):
+                    np.ascontiguousarray(a, dtype=t).tofile(f)
+            subprocess.check_call([str(exe), str(fin), str(fout), str(interp_type)])
+            raw = open(fout, "rb").read()
+            nnz = int(np.frombuffer(raw, dtype=np.int32, count=1)[0])
+            gp = np.frombuffer(raw, dtype=np.int32, count=n + 1, offset=4)
+            gc = np.frombuffer(raw, dtype=np.int32, count=nnz, offset=4 + 4 * (n + 1))
+            gv = np.frombuffer(raw, dtype=np.float64, count=nnz, offset=4 + 4 * (n + 1) + 4 * nnz)
+            assert np.array_equal(gp, pp), (tf, pmax, l)
+            assert np.array_equal(gc, pc), (tf, pmax, l)
+            assert np.array_equal(gv, pv), (tf, pmax, l, float(np.abs(gv - pv).max()))
+            checked += 1
+    assert checked == 10
