@@ -6,7 +6,8 @@
 //   * `method: boomeramg` applies its options to the solver handle (the reference applies them to the still-null
 //     preconditioner handle, HypreSystem.cpp:99-110);
 //   * build_27pt_stencil / build_7pt_stencil call the device generator of libb200hypre with true-neighbour halo columns
-//     (the reference glue at HypreSystem.cpp:1555 maps halo indices to fictitious global columns);
+//     (the reference glue at HypreSystem.cpp:1555 maps halo indices to fictitious global columns; the input key
+//     linear_system.halo_map: reference reproduces that numbering);
 //   * ILU: only the default combination (ilu_type 0, fill 0, local_reordering 0, trisolve 1 = block-Jacobi ILU(0)) is built;
 //     other values are passed on and rejected by HYPRE_ILUSetup.
 #include "HypreSystem.h"
@@ -837,6 +838,13 @@ void HypreSystem::build_stencil(int stencil) {
   HYPRE_Complex *vals = nullptr, *rhs = nullptr;
   if (b200hypre_generate_laplace(nx, ny, nz, px, py, pz, iproc_, stencil, &rows, &cols, &vals, &rhs, &nnz, &nloc, &rstart, &grows))
     throw std::runtime_error(std::string("generator failed: ") + b200hypre_last_error());
+  const std::string halo_map = get_optional(linsys, "halo_map", std::string("true"));
+  if (halo_map == "reference") {   // the surrogate off-rank numbering of HypreSystem.cpp:1553-1556 instead of the true neighbours
+    if (b200hypre_apply_reference_halo_map(cols, nnz, rstart, rstart + nloc - 1, iproc_, NULL))
+      throw std::runtime_error(std::string("halo_map failed: ") + b200hypre_last_error());
+  } else if (halo_map != "true") {
+    throw std::runtime_error("linear_system.halo_map must be 'true' or 'reference'");
+  }
   totalRows_ = M_ = N_ = grows;
   nnz_ = nnz;
   iLower_ = jLower_ = rstart;

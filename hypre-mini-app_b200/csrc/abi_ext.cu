@@ -162,6 +162,15 @@ HYPRE_Int b200hypre_generate_laplace(HYPRE_Int nx, HYPRE_Int ny, HYPRE_Int nz, H
   API_END
 }
 
+HYPRE_Int b200hypre_apply_reference_halo_map(HYPRE_BigInt *cols, HYPRE_BigInt nnz, HYPRE_BigInt ilower, HYPRE_BigInt iupper, HYPRE_Int rank,
+                                             HYPRE_BigInt *n_halo) {
+  API_ARG(cols || nnz == 0, "b200hypre_apply_reference_halo_map: null columns");
+  API_BEGIN
+  const i64 nh = apply_reference_halo_map(cols, nnz, ilower, iupper, rank);
+  if (n_halo) *n_halo = nh;
+  API_END
+}
+
 HYPRE_Int b200hypre_generate_workload(HYPRE_Int kind, HYPRE_Int n, HYPRE_BigInt ilower, HYPRE_BigInt iupper, unsigned long long seed,
                                       HYPRE_BigInt **rows, HYPRE_BigInt **cols, HYPRE_Complex **vals, HYPRE_Complex **rhs,
                                       HYPRE_BigInt *nnz, HYPRE_BigInt *global_rows) {

@@ -239,6 +239,7 @@ inline bool interp_type_built(int t) { return t == 6 || t == 0; }
 // fills device COO (global ids) + rhs for this rank's box; returns nnz.  Arrays are allocated by the callee.
 struct GenOut { DVec<i64> rows, cols; DVec<double> vals, rhs; i64 nnz = 0, n_local = 0, row_start = 0, g_rows = 0; };
 void generate_laplace(int nx, int ny, int nz, int px, int py, int pz, int rank, int stencil, GenOut &out);
+i64 apply_reference_halo_map(i64 *cols_dev, i64 nnz, i64 i_lower, i64 i_upper, int rank);   // HypreSystem.cpp:1553-1556; returns n_halo
 // rows [row_lo, row_hi] of poisson27_hex(n) (kind 0) or momentum3(n) (kind 1): workload_rows.cuh
 void generate_workload(int kind, int n, i64 row_lo, i64 row_hi, unsigned long long seed, GenOut &out);
 

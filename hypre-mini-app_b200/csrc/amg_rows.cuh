@@ -295,6 +295,10 @@ B200_HD int classical_row(const Csr &A, const int *Sptr, const int *Scol, const 
     }
   }
   for (int k = 0; k < L; ++k) lv[k] = 0.0;
+  // membership filter for "is column m in C_i": one bit per (column mod 64); a row of a neighbour has few members of C_i among its
+  // entries, and the filter rejects most of the others without the list search
+  unsigned long long filter = 0ull;
+  for (int k = 0; k < L; ++k) filter |= 1ull << (lc[k] & 63);
   double diagonal = A.val[A.ptr[i]];
   int sp = Sptr[i];
   const int se = Sptr[i + 1];
@@ -309,18 +313,37 @@ B200_HD int classical_row(const Csr &A, const int *Sptr, const int *Scol, const 
     } else if (strong && cf[j] != -3) {
       const int b1 = A.ptr[j], e1 = A.ptr[j + 1];
       const double sgn = (A.val[b1] < 0) ? -1.0 : 1.0;
+      // one walk over row j: the sum in storage order, and the (slot, value) pairs that will receive a share, in the same order
+      constexpr int HB = 16;
+      int hpos[HB];
+      double hval[HB];
+      int nh = 0;
       double sum = 0.0;
       for (int j1 = b1 + 1; j1 < e1; ++j1) {
         const double a = A.val[j1];
-        if ((sgn * a) < 0 && list_find(lc, L, A.col[j1]) >= 0) sum = sum + a;
+        if ((sgn * a) < 0) {
+          const int m = A.col[j1];
+          if ((filter >> (m & 63)) & 1ull) {
+            const int p2 = list_find(lc, L, m);
+            if (p2 >= 0) {
+              sum = sum + a;
+              if (nh < HB) { hpos[nh] = p2; hval[nh] = a; }
+              ++nh;
+            }
+          }
+        }
       }
       if (sum != 0.0) {
         const double distribute = aij / sum;
-        for (int j1 = b1 + 1; j1 < e1; ++j1) {
-          const double a = A.val[j1];
-          if ((sgn * a) < 0) {
-            const int p2 = list_find(lc, L, A.col[j1]);
-            if (p2 >= 0) { const double t = distribute * a; lv[p2] = lv[p2] + t; }
+        if (nh <= HB) {
+          for (int h = 0; h < nh; ++h) { const double t = distribute * hval[h]; lv[hpos[h]] = lv[hpos[h]] + t; }
+        } else {  // more members than the buffer holds: walk the row again
+          for (int j1 = b1 + 1; j1 < e1; ++j1) {
+            const double a = A.val[j1];
+            if ((sgn * a) < 0) {
+              const int p2 = list_find(lc, L, A.col[j1]);
+              if (p2 >= 0) { const double t = distribute * a; lv[p2] = lv[p2] + t; }
+            }
           }
         }
       } else {

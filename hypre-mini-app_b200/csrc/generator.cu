@@ -5,8 +5,8 @@
 // (rank % px, (rank / px) % py, rank / (px*py)); local rows are lexicographic (x fastest); global row =
 // rank * nx*ny*nz + local; neighbours outside the global grid are dropped; diagonal = 26 (27-point, the reference)
 // or 6 (7-point, BASELINE.json configs), off-diagonals -1, rhs = diag - (nnz_row - 1) so that x == 1.
-// Off-rank neighbours carry the TRUE neighbour's global row id (the reference glue's surrogate
-// numbering at HypreSystem.cpp:1555 is not reproduced).
+// Off-rank neighbours carry the TRUE neighbour's global row id; apply_reference_halo_map (below) turns them into the reference
+// glue's surrogate numbering (HypreSystem.cpp:1555) when the input asks for `halo_map: reference`.
 // Output: COO triplets in row order, ascending global column inside a row (= stencil order z, y, x on one rank), plus the rhs.
 #include "amg.h"
 #include "workload_rows.cuh"
@@ -136,6 +136,71 @@ void generate_laplace(int nx, int ny, int nz, int px, int py, int pz, int rank, 
   count_launch(4);
   B200_KERNEL_CHECK();
   B200_CUDA(cudaStreamSynchronize(stream()));
+}
+
+// ---- `halo_map: reference`: the off-rank column numbering the reference glue really hands to hypre -----------------------------------
+// /root/reference/src/HypreSystem.cpp:1553-1556 turns the generator's LOCAL halo index into a "global" column by adding iUpper + 1 on
+// rank 0 and 0 on every other rank.  The generator numbers a rank's halo points 0 .. n_halo-1 by neighbour rank ascending and, inside a
+// neighbour, by ascending grid id (src/laplace_3d_weak_scaling.hpp:495-531: slot = (dz+1)*9 + (dy+1)*3 + (dx+1); :966-1056: radix sort +
+// run-length encode per neighbour, offsets accumulated in slot order) -- with rank-contiguous row ids that is the ascending order of the
+// distinct off-rank columns of the rank.  So: column' = (position of the true column among the sorted distinct off-rank columns) +
+// (rank == 0 ? i_upper + 1 : 0).  Every rank >= 1 couples to the first rows of rank 0, rank 0 to the first rows of rank 1: a
+// nonsymmetric surrogate with the same row sums (x == 1 stays the solution).  In place on device COO columns; returns n_halo.
+namespace {
+__global__ void k_flag_offrank(i64 nnz, const i64 *__restrict__ cols, i64 lo, i64 hi, int *flag) {
+  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k <= nnz) flag[k] = (k < nnz && (cols[k] < lo || cols[k] > hi)) ? 1 : 0;
+}
+__global__ void k_gather_offrank(i64 nnz, const i64 *__restrict__ cols, const int *__restrict__ flag, const int *__restrict__ pos, i64 *out) {
+  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < nnz && flag[k]) out[pos[k]] = cols[k];
+}
+__global__ void k_remap_offrank(i64 nnz, i64 *cols, const int *__restrict__ flag, const i64 *__restrict__ halo, int n_halo, i64 shift) {
+  i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= nnz || !flag[k]) return;
+  const i64 c = cols[k];
+  int lo = 0, hi = n_halo;   // lower bound
+  while (lo < hi) {
+    const int mid = lo + ((hi - lo) >> 1);
+    if (halo[mid] < c) lo = mid + 1; else hi = mid;
+  }
+  cols[k] = (i64)lo + shift;
+}
+}  // namespace
+
+i64 apply_reference_halo_map(i64 *cols, i64 nnz, i64 i_lower, i64 i_upper, int rank) {
+  ensure_init();
+  B200_REQUIRE(nnz >= 0 && nnz < (1LL << 31) - 8 && i_upper >= i_lower - 1, "halo_map: bad arguments");
+  if (nnz == 0) return 0;
+  DVec<int> flag((size_t)nnz + 1), pos((size_t)nnz + 1);
+  const int grid = div_up(nnz + 1, 256);
+  k_flag_offrank<<<grid, 256, 0, stream()>>>(nnz, cols, i_lower, i_upper, flag.p);
+  size_t tb = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, tb, flag.p, pos.p, (int)(nnz + 1), stream());
+  DVec<char> tmp(tb);
+  cub::DeviceScan::ExclusiveSum(tmp.p, tb, flag.p, pos.p, (int)(nnz + 1), stream());
+  int n_off = 0;
+  B200_CUDA(cudaMemcpyAsync(&n_off, pos.p + nnz, sizeof(int), cudaMemcpyDeviceToHost, stream()));
+  B200_CUDA(cudaStreamSynchronize(stream()));
+  count_launch(3);
+  if (n_off == 0) return 0;
+  DVec<i64> off((size_t)n_off), sorted((size_t)n_off), uniq((size_t)n_off);
+  DVec<int> n_uniq(1);
+  k_gather_offrank<<<grid, 256, 0, stream()>>>(nnz, cols, flag.p, pos.p, off.p);
+  cub::DeviceRadixSort::SortKeys(nullptr, tb, off.p, sorted.p, n_off, 0, 64, stream());
+  DVec<char> tmp2(tb);
+  cub::DeviceRadixSort::SortKeys(tmp2.p, tb, off.p, sorted.p, n_off, 0, 64, stream());
+  cub::DeviceSelect::Unique(nullptr, tb, sorted.p, uniq.p, n_uniq.p, n_off, stream());
+  DVec<char> tmp3(tb);
+  cub::DeviceSelect::Unique(tmp3.p, tb, sorted.p, uniq.p, n_uniq.p, n_off, stream());
+  int n_halo = 0;
+  B200_CUDA(cudaMemcpyAsync(&n_halo, n_uniq.p, sizeof(int), cudaMemcpyDeviceToHost, stream()));
+  B200_CUDA(cudaStreamSynchronize(stream()));
+  k_remap_offrank<<<grid, 256, 0, stream()>>>(nnz, cols, flag.p, uniq.p, n_halo, rank == 0 ? i_upper + 1 : 0);
+  count_launch(4);
+  B200_KERNEL_CHECK();
+  B200_CUDA(cudaStreamSynchronize(stream()));
+  return n_halo;
 }
 
 // ---- synthetic nalu-wind-like systems (BASELINE.json configs[3] / [4]): rows [row_lo, row_hi] of the global system, built by

@@ -11,7 +11,7 @@ import time
 
 import numpy as np
 
-from . import (HYPRE_MEMORY_DEVICE, I32, I64, VP, IJMatrix, IJVector, check, lib, process_grid, synchronize)
+from . import (HYPRE_MEMORY_DEVICE, I32, I64, VP, HypreError, IJMatrix, IJVector, check, lib, process_grid, synchronize)
 from .solvers import ILU, AMGSolver, BoomerAMG, ParKrylov
 
 
@@ -39,6 +39,17 @@ def generate_laplace(nx, ny, nz, grid=(1, 1, 1), rank=0, stencil=7):
                                        C.byref(vals), C.byref(rhs), C.byref(nnz), C.byref(nloc), C.byref(rs), C.byref(gr)),
           "generate_laplace")
     return DeviceCOO(rows.value, cols.value, vals.value, rhs.value, nnz.value, nloc.value, rs.value, gr.value)
+
+
+def apply_reference_halo_map(coo, rank):
+    """`halo_map: reference`: off-rank columns of the device COO become generator-local halo index + (rank == 0 ? iUpper + 1 : 0),
+    what /root/reference/src/HypreSystem.cpp:1553-1556 hands to hypre; returns the number of halo points"""
+    L = lib()
+    L.b200hypre_apply_reference_halo_map.argtypes = [VP, I64, I64, I64, I32, C.POINTER(I64)]
+    nh = I64()
+    check(L.b200hypre_apply_reference_halo_map(coo.cols, coo.nnz, coo.row_start, coo.row_start + coo.n_local - 1, rank, C.byref(nh)),
+          "apply_reference_halo_map")
+    return nh.value
 
 
 WORKLOAD_KINDS = {"poisson27_hex": (0, 20260, 1), "momentum3": (1, 20261, 3)}   # kind id, seed, rows per node
@@ -155,6 +166,11 @@ class HypreSystem:
         grid = tuple(ls.get("grid", process_grid(self.nranks)))
         t0 = time.perf_counter()
         coo = generate_laplace(nx, ny, nz, grid, self.rank, stencil)
+        halo_map = ls.get("halo_map", "true")
+        if halo_map == "reference":      # the reference glue's surrogate off-rank numbering (HypreSystem.cpp:1553-1556)
+            self.n_halo = apply_reference_halo_map(coo, self.rank)
+        elif halo_map != "true":
+            raise HypreError(f"linear_system.halo_map must be 'true' or 'reference', got {halo_map!r}")
         self.global_rows = coo.global_rows
         self._init_system(coo.row_start, coo.row_start + coo.n_local - 1)
         self.A.set_values_ptr(coo.nnz, coo.rows, coo.cols, coo.vals)

@@ -37,6 +37,12 @@ HYPRE_Int b200hypre_generate_laplace(HYPRE_Int nx, HYPRE_Int ny, HYPRE_Int nz, H
 HYPRE_Int b200hypre_generate_workload(HYPRE_Int kind, HYPRE_Int n, HYPRE_BigInt ilower, HYPRE_BigInt iupper, unsigned long long seed,
                                       HYPRE_BigInt **rows, HYPRE_BigInt **cols, HYPRE_Complex **vals, HYPRE_Complex **rhs,
                                       HYPRE_BigInt *nnz, HYPRE_BigInt *global_rows);
+/* `halo_map: reference` -- rewrites, in place, the off-rank columns (outside [ilower, iupper]) of DEVICE COO columns into the numbering
+ * the reference glue hands to hypre (/root/reference/src/HypreSystem.cpp:1553-1556: generator-local halo index + (rank == 0 ? iUpper + 1
+ * : 0)); the halo index is the position of the true column among the rank's sorted distinct off-rank columns
+ * (src/laplace_3d_weak_scaling.hpp:495-531,966-1056).  n_halo (may be NULL) receives the number of halo points. */
+HYPRE_Int b200hypre_apply_reference_halo_map(HYPRE_BigInt *cols, HYPRE_BigInt nnz, HYPRE_BigInt ilower, HYPRE_BigInt iupper, HYPRE_Int rank,
+                                             HYPRE_BigInt *n_halo);
 void b200hypre_block_partition(HYPRE_BigInt n, HYPRE_Int nranks, HYPRE_BigInt *starts /* nranks + 1 */);  /* HypreSystem.cpp:525-544; host only */
 /* receive side of the halo plan for sorted halo column ids; returns the number of neighbours; host only */
 HYPRE_Int b200hypre_plan_recv(const HYPRE_BigInt *col_map, HYPRE_Int n_halo, const HYPRE_BigInt *col_starts, HYPRE_Int nranks,

@@ -234,6 +234,7 @@ struct Options {
   int cgs = 0;                                  // COGMRES: 0/1 = one classical Gram-Schmidt pass, 2 = two passes
   // amg
   int coarsen_type = 8, interp_type = 6, relax_type = 18, relax_order = 0, max_levels = 20;
+  int halo_map = 0;            // generator: 0 = true neighbour ids, 1 = the reference glue's surrogate numbering (gen_laplace)
   int num_sweeps = 1, p_max_elmts = 4, max_coarse_size = 9, min_coarse_size = 0, cheby_order = 2, cheby_eig_est = 10;
   double strong_threshold = 0.25, max_row_sum = 0.9, trunc_factor = 0.0, cheby_fraction = 0.3, relax_weight = 1.0;
 };
@@ -273,8 +274,8 @@ static void ilu_apply(Sys &s, const double *r, double *z);
 // HypreSystem.cpp:1516,1540-1556).  stencil = 27 (reference) or 7.  Rows are numbered rank-contiguously
 // (global row = rank*nx*ny*nz + local lexicographic index, x fastest); neighbours outside the global grid are
 // dropped; diag = (#stencil points - 1), off-diagonals = -1; rhs = row sum so that x == 1.
-// Off-rank columns use the TRUE neighbour's global row id (the reference glue's surrogate numbering at
-// HypreSystem.cpp:1555 is documented in DESIGN.md as not reproduced).
+// Off-rank columns use the TRUE neighbour's global row id; option halo_map = 1 applies the reference glue's surrogate
+// numbering (HypreSystem.cpp:1555) instead, see the end of gen_laplace.
 // ---------------------------------------------------------------------------------------------------------
 static void gen_laplace(Sys &s, int nx, int ny, int nz, int px, int py, int pz, int stencil) {
   int np = px * py * pz;
@@ -342,6 +343,25 @@ static void gen_laplace(Sys &s, int nx, int ny, int nz, int px, int py, int pz, 
           ++cnt;
         }
     s.b[row] = dval - (cnt - 1);  // laplace_3d_weak_scaling.hpp:321
+  }
+  if (s.opt.halo_map == 1 && np > 1) {
+    // `halo_map: reference` -- what the reference glue really hands to hypre (/root/reference/src/HypreSystem.cpp:1553-1556): the
+    // generator numbers a rank's halo points 0 .. n_halo-1 (neighbour ranks ascending, inside a neighbour ascending grid id =
+    // ascending rank-contiguous id, src/laplace_3d_weak_scaling.hpp:495-531,966-1056) and the glue adds iUpper + 1 on rank 0 and 0
+    // on the others to that LOCAL index.  Every rank >= 1 thus couples to the first rows of rank 0 and rank 0 to the first rows of
+    // rank 1: nonsymmetric, same row sums (x == 1 stays the solution).
+    for (int r = 0; r < np; ++r) {
+      const int r0 = L.part[r], r1 = L.part[r + 1];
+      std::vector<int> halo;
+      for (int k = A.ptr[r0]; k < A.ptr[r1]; ++k)
+        if (A.col[k] < r0 || A.col[k] >= r1) halo.push_back(A.col[k]);
+      std::sort(halo.begin(), halo.end());
+      halo.erase(std::unique(halo.begin(), halo.end()), halo.end());
+      const int shift = (r == 0) ? r1 : 0;
+      for (int k = A.ptr[r0]; k < A.ptr[r1]; ++k)
+        if (A.col[k] < r0 || A.col[k] >= r1)
+          A.col[k] = int(std::lower_bound(halo.begin(), halo.end(), A.col[k]) - halo.begin()) + shift;
+    }
   }
   parcsr_order(A, L.part, L.part, true);
 }
@@ -1436,7 +1456,7 @@ int ora_set_opt(void *h, const char *name, double v) {
 #define OPT_D(key, field) if (k == key) { o.field = v; return 0; }
   OPT_D("tolerance", tol) OPT_D("absolute_tolerance", atol) OPT_I("max_iterations", max_iter) OPT_I("kspace", kdim)
   OPT_I("preconditioner", precond) OPT_I("cgs", cgs) OPT_I("coarsen_type", coarsen_type) OPT_I("interp_type", interp_type)
-  OPT_I("relax_type", relax_type) OPT_I("relax_order", relax_order) OPT_I("max_levels", max_levels)
+  OPT_I("relax_type", relax_type) OPT_I("relax_order", relax_order) OPT_I("max_levels", max_levels) OPT_I("halo_map", halo_map)
   OPT_I("num_sweeps", num_sweeps) OPT_I("p_max_elmts", p_max_elmts) OPT_I("max_coarse_size", max_coarse_size)
   OPT_I("min_coarse_size", min_coarse_size) OPT_I("cheby_order", cheby_order) OPT_I("cheby_eig_est", cheby_eig_est)
   OPT_D("strong_threshold", strong_threshold) OPT_D("max_row_sum", max_row_sum) OPT_D("trunc_factor", trunc_factor)

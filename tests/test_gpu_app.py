@@ -397,3 +397,14 @@ def test_reference_sample_input_runs_through_both_hosts(app, tmp_path):
         assert np.abs(sols[name] - xref).max() <= 1e-4 * np.abs(xref).max(), name
     if "reference" in sols:
         assert np.abs(sols["reference"] - sols["twin"]).max() <= 1e-12 * np.abs(xref).max()
+
+
+def test_generator_with_reference_halo_map_on_two_ranks(app, tmp_path):
+    """linear_system.halo_map: reference through the host application: the surrogate off-rank numbering of the reference glue on 2 ranks;
+    x == 1 stays the solution (row sums are unchanged)"""
+    rc, out = run_app(app, str(tmp_path), ["type: build_27pt_stencil", "nx: 10", "ny: 10", "nz: 10", "halo_map: reference",
+                                           "write_solution: true"], nranks=2)
+    assert rc == 0, out
+    s0 = np.loadtxt(tmp_path / "IJV0.sln.00000", skiprows=1)
+    s1 = np.loadtxt(tmp_path / "IJV0.sln.00001", skiprows=1)
+    assert np.abs(np.concatenate([s0[:, 1], s1[:, 1]]) - 1.0).max() < 1e-7

@@ -188,6 +188,23 @@ def test_multirank_classical_interpolation(b200, n, grid, stencil, theta, pmax):
     compare_with_oracle(res, n, grid, stencil, theta, interp_type=0, p_max_elmts=pmax)
 
 
+@pytest.mark.parametrize("n,grid,stencil", [((8, 8, 8), (2, 1, 1), 27), ((8, 8, 8), (2, 2, 1), 27), ((10, 10, 10), (2, 2, 2), 7)])
+def test_multirank_reference_halo_map(b200, n, grid, stencil):
+    """`halo_map: reference`: the matrix the reference glue really assembles on several ranks (/root/reference/src/HypreSystem.cpp:1553-1556:
+    off-rank column = generator-local halo index + (rank == 0 ? iUpper + 1 : 0)) -- nonsymmetric, every rank >= 1 coupled to the first
+    rows of rank 0.  Assembled on the device, set up and solved; hierarchy and solution against the oracle with the same surrogate."""
+    nranks = grid[0] * grid[1] * grid[2]
+    cfg = settings(n, grid, stencil, strong_threshold=0.25)
+    cfg["linear_system"]["halo_map"] = "reference"
+    res = run_ranks(nranks, cfg)
+    compare_with_oracle(res, n, grid, stencil, 0.25, halo_map=1)
+    # rank 1's off-rank columns all lie at the start of rank 0's rows
+    nloc = n[0] * n[1] * n[2]
+    ptr, col = res[1]["A0_ptr"], res[1]["A0_col"]
+    off = col[(col < nloc) | (col >= 2 * nloc)]
+    assert len(off) > 0 and off.min() == 0 and off.max() == len(np.unique(off)) - 1 and off.max() < nloc
+
+
 @pytest.mark.parametrize("relax", [11, 12])
 def test_multirank_two_stage_gauss_seidel(b200, relax):
     """relax 11 / 12 on 2 ranks: the triangle is taken from every rank's own diagonal block (hybrid), off-rank couplings enter
