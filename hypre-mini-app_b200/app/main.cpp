@@ -59,6 +59,16 @@ int main(int argc, char *argv[]) {
       v.fn(use == 1);
     }
 
+    // main.cpp:108-114 sizes hypre's Umpire device pool from this key; here it pre-grows the library's stream-ordered pool in one
+    // piece (only when the input names it: the pool otherwise grows on demand and never shrinks).  fast_matrix_assemble /
+    // fast_vector_assemble (HypreSystem.cpp:933,994) guard code the reference compiles out (#if 0): accepted, nothing to do.
+    if (node["umpire_device_pool_mbs"]) {
+      const long long mbs = node["umpire_device_pool_mbs"].as<long long>();
+      if (!iproc) std::cout << "umpire_device_pool_mbs=" << mbs << std::endl;
+      if (mbs > 0 && b200hypre_pool_reserve((unsigned long long)mbs * 1024ULL * 1024ULL))
+        fprintf(stderr, "hypre_app: could not reserve %lld MiB of device pool: %s\n", mbs, b200hypre_last_error());
+    }
+
     std::string csv_profile_file = nalu::get_optional<std::string>(node, "csv_profile_file", "");
     std::vector<std::string> names;
     std::vector<std::vector<double>> data;

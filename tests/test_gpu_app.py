@@ -159,8 +159,10 @@ def test_hypre_ij_path_two_partitions_and_level_dump(app, tmp_path):
 
 
 def test_generator_path_and_no_preconditioner(app, tmp_path):
-    rc, out = run_app(app, str(tmp_path), ["type: build_7pt_stencil", "nx: 16", "ny: 16", "nz: 16", "write_solution: true"])
+    rc, out = run_app(app, str(tmp_path), ["type: build_7pt_stencil", "nx: 16", "ny: 16", "nz: 16", "write_solution: true"],
+                      solver_extra="  umpire_device_pool_mbs: 64\n  fast_matrix_assemble: 1\n  fast_vector_assemble: 1")
     assert rc == 0, out
+    assert "umpire_device_pool_mbs=64" in out      # main.cpp:108-114: the pool-size key pre-grows the library's pool
     sol = np.loadtxt(tmp_path / "IJV0.sln.00000", skiprows=1)
     assert np.abs(sol[:, 1] - 1.0).max() < 1e-7   # generator known answer
     its_amg = iterations(out)
