@@ -65,6 +65,9 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if full:
         return run_full_size(bh, world)
+    if "--segregated" in sys.argv:
+        k = sys.argv.index("--segregated")
+        return run_segregated(bh, int(sys.argv[k + 1]) if len(sys.argv) > k + 1 else 256)
     bh.comm_init(0, 1)
     bh.pool_reserve(int((8 if quick else 60) * 2 ** 30))
     from workloads import momentum3, poisson27_hex
@@ -116,6 +119,60 @@ def run_full_size(bh, world):
 
 
 RANKS = (0, 1)
+
+
+def run_segregated(bh, n):
+    """the reference's own notion of several components (HypreSystem.cpp:1033-1036,681-692; SURVEY.md section 8d input 5): ONE scalar
+    matrix, one right-hand side per component, solved one after the other.  The reference calls Setup inside its component loop; this
+    times one setup followed by the three solves (what a user of the segregated path pays when the preconditioner is reused)
+    and, beside it, the reference's literal order (setup + solve per component).
+        python profiles/run_workloads.py --segregated [n]"""
+    import numpy as np
+    import torch
+    bh.comm_init(0, 1)
+    stream = torch.cuda.ExternalStream(bh.stream_ptr())
+    gm = {"method": "gmres", "preconditioner": "boomeramg", "tolerance": 1e-8, "kspace": 50, "max_iterations": 400}
+    s = bh.HypreSystem({"linear_system": {"type": "build_7pt_stencil", "nx": n, "ny": n, "nz": n}, "solver_settings": gm,
+                        "boomeramg_settings": {}})
+    s.setup_precon_and_solver()
+    s.load()
+    s.assemble_system()
+    N = n ** 3
+    g = np.arange(N, dtype=np.float64)
+    fields = [np.ones(N), 1.0 + 0.5 * np.sin(2e-5 * g), np.cos(3e-7 * g) + 2.0]     # three "components": known solutions
+    xk = bh.IJVector(0, N - 1)
+    rhs = []
+    for f in fields:
+        xk.set_values(f)
+        xk.assemble()
+        b = bh.IJVector(0, N - 1)
+        b.assemble()
+        bh.matvec(s.A, xk, b)
+        rhs.append(b)
+    for mode in ("one setup, three solves", "setup and solve per component (the reference's loop)"):
+        its, errs = [], []
+        setup_ms = solve_ms = 0.0
+        for c, (f, b) in enumerate(zip(fields, rhs)):
+            s.x.fill(0.0)
+            if c == 0 or mode.startswith("setup and"):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                s.solver.set_precond(s.precond)
+                s.solver.setup(s.A, b, s.x)
+                e1.record(stream)
+                bh.synchronize(); torch.cuda.synchronize()
+                setup_ms += e0.elapsed_time(e1)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            s.solver.solve(s.A, b, s.x)
+            e1.record(stream)
+            bh.synchronize(); torch.cuda.synchronize()
+            solve_ms += e0.elapsed_time(e1)
+            its.append(int(s.solver.iterations))
+            errs.append(float(np.abs(s.solution() - f).max()))
+        print(json.dumps({"case": f"segregated_3rhs_lap7_{n}", "mode": mode, "rows": N, "components": 3, "setup_s": setup_ms * 1e-3,
+                          "solve_s": solve_ms * 1e-3, "iterations": its, "max_err_vs_known": errs}), flush=True)
+    s.destroy_system()
 
 
 def run_host_built(bh, gm, n_poisson, n_momentum):
