@@ -343,6 +343,7 @@ HYPRE_Int b200hypre_solver_converged(HYPRE_Solver solver) {  // any Krylov handl
     return b->kind == SolverBase::GMRES ? static_cast<GmresHandle *>(b)->g.converged : static_cast<KrylovHandle *>(b)->k.converged;
   } catch (const std::exception &e) { set_error(HYPRE_ERROR_ARG, e.what()); return -1; }
 }
+unsigned long long b200hypre_h2d_bytes(void) { return ij_h2d_bytes(); }
 unsigned long long b200hypre_launch_count(void) { return ctx().launches; }
 // out[0..3] = bytes the library's stream-ordered pool holds from the driver (now / high-water) and bytes in use (now / high)
 HYPRE_Int b200hypre_pool_stats(unsigned long long *out) {

@@ -219,6 +219,7 @@ struct IJVector {
 void ij_matrix_set(IJMatrix &M, i64 nrows, const int *ncols, const i64 *rows, const int *row_indexes, const i64 *cols,
                    const double *vals, int op);
 void ij_matrix_assemble(IJMatrix &M);
+unsigned long long ij_h2d_bytes();   // bytes the IJ interface has copied from caller host buffers to the device so far
 void ij_vector_init(IJVector &v);
 void ij_vector_set(IJVector &v, i64 n, const i64 *idx, const double *vals, int op);
 void ij_vector_get(IJVector &v, i64 n, const i64 *idx, double *out);

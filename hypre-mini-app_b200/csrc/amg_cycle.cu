@@ -65,7 +65,9 @@ void relax_sweep(Amg &amg, AmgLevel &L, LevelBufs &b, int rtype, bool down, bool
   const AmgOptions &o = amg.opt;
   ParCsr &A = *L.A;
   int n = A.n;
-  if (n == 0) return;
+  // A rank may own no rows of a coarse level (n == 0).  It still walks through the sweep: every kernel wrapper below is a no-op for
+  // an empty vector, but the halo exchanges inside par_spmv / gs_halo are collective on the host-staged transport of the N-ranks-on-
+  // one-GPU tests, and the buffer flips must stay in step with init_bufs.  (An early return here left the other ranks waiting.)
   if (rtype == 16) {
     int ord = (int)L.cheby_coef.size();
     double *r = L.r.p, *v0 = L.t0.p, *v1 = L.t1.p;
@@ -129,7 +131,7 @@ void relax_sweep(Amg &amg, AmgLevel &L, LevelBufs &b, int rtype, bool down, bool
       gs_halo(A, b.cur);
       for (int dir = 0; dir < 2; ++dir) {
         if (dir == 0 ? !fwd : !bwd) continue;
-        B200_REQUIRE(L.gs[ps][dir].built, "Gauss-Seidel plan missing for this level (internal error)");
+        B200_REQUIRE(n == 0 || L.gs[ps][dir].built, "Gauss-Seidel plan missing for this level (internal error)");
         gs_sweep(A, L.gs[ps][dir], l1, L.dsm.p, b.f, b.cur, b.other);
         std::swap(b.cur, b.other);
       }

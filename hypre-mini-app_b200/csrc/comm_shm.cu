@@ -65,7 +65,9 @@ void shm_barrier() {
     if ((++spins & 1023) == 0) {
       usleep(50);
       double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-      if (dt > 300.0) fail(__FILE__, __LINE__, "shm transport: barrier timed out after 300 s (a peer rank died?)");
+      static double limit = 0.0;   // B200_SHM_TIMEOUT_S: seconds a rank waits for its peers (default 300; sweeps use less)
+      if (limit == 0.0) { const char *e = getenv("B200_SHM_TIMEOUT_S"); limit = (e && atof(e) > 0) ? atof(e) : 300.0; }
+      if (dt > limit) fail(__FILE__, __LINE__, "shm transport: barrier timed out after " + std::to_string((int)limit) + " s (a peer rank died?)");
     }
   }
 }

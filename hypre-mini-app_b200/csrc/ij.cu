@@ -8,6 +8,12 @@
 #include "amg.h"
 #include <cub/cub.cuh>
 #include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <sched.h>
+#include <thread>
 
 namespace b200 {
 
@@ -24,11 +30,113 @@ bool is_device_ptr(const void *p) {
   return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
 }
 
+std::atomic<unsigned long long> g_h2d_bytes{0};   // bytes copied from caller host buffers to the device by the IJ interface
+
 template <class T>
 void stage_copy(DVec<T> &dst, const T *src, i64 n) {
   dst.alloc((size_t)n);
   if (n == 0) return;
-  B200_CUDA(cudaMemcpyAsync(dst.p, src, n * sizeof(T), is_device_ptr(src) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, stream()));
+  const bool dev = is_device_ptr(src);
+  if (!dev) g_h2d_bytes += (unsigned long long)n * sizeof(T);
+  B200_CUDA(cudaMemcpyAsync(dst.p, src, n * sizeof(T), dev ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, stream()));
+}
+
+// ---- host rows -> row pointer: the row ids of a triplet list that is sorted by row (the mini-app's loaders and generators produce
+// that, /root/reference/src/HypreSystem.cpp:897-955) carry nloc + 1 numbers of information in nnz 64-bit words.  When the caller's
+// arrays live on the host the link is the bottleneck of SetValues2 (2.9 GB for 256^3 at ~56 GB/s), so the host threads turn `rows`
+// into a local row pointer while the DMA engine ships cols and vals, and only the pointer crosses the link; a kernel expands it
+// again.  Anything else (unsorted rows, a row outside [ilower, iupper]) takes the plain copy and is judged by Assemble.
+struct PinnedInts {
+  int *p = nullptr;
+  size_t cap = 0;
+  int *get(size_t n) {
+    if (n > cap) {
+      if (p) cudaFreeHost(p);
+      p = nullptr;
+      cap = 0;
+      if (cudaHostAlloc((void **)&p, n * sizeof(int), cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); p = nullptr; return nullptr; }
+      cap = n;
+    }
+    return p;
+  }
+};
+PinnedInts g_ptr_stage;   // grow-only, one per process (one rank per process)
+
+int host_threads_for_staging() {
+  cpu_set_t set;
+  int avail = (int)std::thread::hardware_concurrency();
+  if (sched_getaffinity(0, sizeof(set), &set) == 0) avail = CPU_COUNT(&set);
+  int t = avail / std::max(1, ctx().nranks);
+  return std::max(1, std::min(t, 16));
+}
+
+// ptr[r - ilower] = first position of row r (nloc + 1 entries); false if rows are not nondecreasing or leave [ilower, iupper]
+bool host_rows_to_ptr(const i64 *rows, i64 n, i64 ilower, i64 iupper, int *ptr) {
+  const int T = host_threads_for_staging();
+  std::atomic<int> bad{0};
+  auto work = [&](int t) {
+    const i64 a = n * t / T, b = n * (t + 1) / T;
+    if (a >= b) return;
+    i64 prev;
+    i64 k = a;
+    if (a == 0) {
+      prev = rows[0];
+      if (prev < ilower || prev > iupper) { bad = 1; return; }
+      for (i64 r = ilower; r <= prev; ++r) ptr[r - ilower] = 0;
+      k = 1;
+    } else {
+      prev = rows[a - 1];
+    }
+    for (; k < b; ++k) {
+      const i64 cur = rows[k];
+      if (cur != prev) {
+        if (cur < prev || cur > iupper || prev < ilower) { bad = 1; return; }
+        for (i64 r = prev + 1; r <= cur; ++r) ptr[r - ilower] = (int)k;
+        prev = cur;
+      }
+    }
+  };
+  std::vector<std::thread> th;
+  for (int t = 1; t < T; ++t) th.emplace_back(work, t);
+  work(0);
+  for (auto &x : th) x.join();
+  if (bad.load()) return false;
+  const i64 last = rows[n - 1];
+  for (i64 r = last + 1; r <= iupper + 1; ++r) ptr[r - ilower] = (int)n;
+  return true;
+}
+
+__global__ void k_expand_rows(int nloc, const int *__restrict__ ptr, i64 ilower, i64 *rows) {
+  // one warp per row: rows are a handful of entries
+  const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (r >= nloc) return;
+  const i64 g = ilower + r;
+  for (int k = ptr[r] + lane; k < ptr[r + 1]; k += 32) rows[k] = g;
+}
+
+// stages `rows` (host pointer) through the row pointer; returns false when the plain copy has to be used instead
+bool stage_rows_compressed(DVec<i64> &dst, const i64 *rows, i64 n, i64 ilower, i64 iupper) {
+  const i64 nloc = iupper - ilower + 1;
+  if (n < (1 << 20) || n >= (1LL << 31) - 8 || nloc <= 0 || nloc >= (1LL << 31) - 8 || nloc > n) return false;
+  int *hptr = g_ptr_stage.get((size_t)nloc + 1);
+  if (!hptr) return false;
+  const bool timing = getenv("B200_IJ_TIMING") != nullptr;
+  const auto t0 = std::chrono::steady_clock::now();
+  const bool sorted = host_rows_to_ptr(rows, n, ilower, iupper, hptr);
+  if (timing)
+    fprintf(stderr, "[b200hypre] IJ staging: %lld row ids -> row pointer on %d host threads in %.2f ms (%s)\n", (long long)n,
+            host_threads_for_staging(), std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(),
+            sorted ? "sorted" : "not sorted: plain copy");
+  if (!sorted) return false;
+  DVec<int> dptr((size_t)nloc + 1);
+  dst.alloc((size_t)n);
+  g_h2d_bytes += (unsigned long long)(nloc + 1) * sizeof(int);
+  B200_CUDA(cudaMemcpyAsync(dptr.p, hptr, (size_t)(nloc + 1) * sizeof(int), cudaMemcpyHostToDevice, stream()));
+  k_expand_rows<<<div_up((i64)nloc * 32, 256), 256, 0, stream()>>>((int)nloc, dptr.p, ilower, dst.p);
+  count_launch();
+  // the pinned pointer is reused by the next call: it must have left the host before this function returns
+  B200_CUDA(cudaStreamSynchronize(stream()));
+  return true;
 }
 
 __global__ void k_check_sorted(i64 n, const i64 *rows, const i64 *cols, int *bad) {
@@ -209,9 +317,10 @@ void ij_matrix_set(IJMatrix &M, i64 nrows, const int *ncols, const i64 *rows, co
   ch.op = op;
   if (ncols == nullptr) {  // one entry per "row" (the mini-app's usage)
     ch.n = nrows;
-    stage_copy(ch.rows, rows, nrows);
+    // cols and vals first: their transfers run while the host threads look at the rows
     stage_copy(ch.cols, cols, nrows);
     stage_copy(ch.vals, vals, nrows);
+    if (is_device_ptr(rows) || !stage_rows_compressed(ch.rows, rows, nrows, M.ilower, M.iupper)) stage_copy(ch.rows, rows, nrows);
   } else {  // general CSR-like call: expand on the host (host pointers only)
     B200_REQUIRE(!is_device_ptr(ncols) && !is_device_ptr(rows) && !is_device_ptr(cols) && !is_device_ptr(vals),
                  "IJMatrixSetValues2 with ncols != NULL expects host pointers");
@@ -232,6 +341,8 @@ void ij_matrix_set(IJMatrix &M, i64 nrows, const int *ncols, const i64 *rows, co
   M.assembled = false;
   M.staged.push_back(std::move(ch));
 }
+
+unsigned long long ij_h2d_bytes() { return g_h2d_bytes.load(); }
 
 void ij_matrix_assemble(IJMatrix &M) {
   ensure_init();
@@ -457,8 +568,8 @@ void ij_vector_set(IJVector &v, i64 n, const i64 *idx, const double *vals, int o
   DVec<double> dv;
   const i64 *pi = idx;
   const double *pv = vals;
-  if (idx && !is_device_ptr(idx)) { di.from_host(idx, (size_t)n); pi = di.p; }
-  if (!is_device_ptr(vals)) { dv.from_host(vals, (size_t)n); pv = dv.p; }
+  if (idx && !is_device_ptr(idx)) { di.from_host(idx, (size_t)n); pi = di.p; g_h2d_bytes += (unsigned long long)n * sizeof(i64); }
+  if (!is_device_ptr(vals)) { dv.from_host(vals, (size_t)n); pv = dv.p; g_h2d_bytes += (unsigned long long)n * sizeof(double); }
   k_vec_set<<<div_up(n, 256), 256, 0, stream()>>>(n, pi, pv, v.jlower, v.jupper, v.par.p, op, v.jlower);
   count_launch();
   B200_CUDA(cudaStreamSynchronize(stream()));

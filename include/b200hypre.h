@@ -87,6 +87,9 @@ HYPRE_Int b200hypre_device_info(char *name, HYPRE_Int name_cap, int *device, int
 
 /* ---- instrumentation ------------------------------------------------------------------------------------------------------- */
 unsigned long long b200hypre_launch_count(void);   /* kernels launched by the library so far */
+/* bytes the IJ interface (SetValues2 / AddToValues2 / IJVectorSetValues) has copied from caller HOST buffers to the device so far.
+ * Row ids of a triplet list sorted by row cross the link as a row pointer (nloc + 1 ints instead of nnz 64-bit words). */
+unsigned long long b200hypre_h2d_bytes(void);
 /* device memory pool of the library (stream-ordered, never shrinks): out[0..3] = reserved now / high, used now / high */
 HYPRE_Int b200hypre_pool_stats(unsigned long long *out);
 /* pre-grow the pool to `bytes` in one piece (what HYPRE_SetGPUMemoryPoolSize is for, /root/reference/src/main.cpp:104) */

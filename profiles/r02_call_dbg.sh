@@ -1,13 +1,8 @@
 #!/bin/bash
 cd "$GRAFT_REPO_ROOT"
-FAIL=""
-for n in 24 48 96 160 256; do
-  timeout 600 python profiles/dbg_poisson.py $n > gpurun_out/dbg_p$n.log 2>&1; rc=$?
-  tail -2 gpurun_out/dbg_p$n.log | cut -c1-300
-  if [ $rc -ne 0 ] && [ -z "$FAIL" ]; then FAIL=$n; fi
-done
-echo "first failing size: $FAIL"
-if [ -n "$FAIL" ]; then
-  timeout 1500 compute-sanitizer --tool memcheck --print-limit 20 python profiles/dbg_poisson.py $FAIL > gpurun_out/dbg_memcheck.log 2>&1
-  grep -v "^$" gpurun_out/dbg_memcheck.log | head -60 | cut -c1-400
-fi
+export B200_SHM_TIMEOUT_S=45
+timeout 600 python profiles/dbg_ranks_case.py '[2,2,2]' '[8,5,5]' 27 0.5 0 4 0.0 > gpurun_out/dbg_case15.log 2>&1
+grep -v "^\s*File\|^    " gpurun_out/dbg_case15.log | tail -12
+timeout 900 python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "host_rows_cross" > gpurun_out/r02h_pytest_hostrows.log 2>&1; tail -12 gpurun_out/r02h_pytest_hostrows.log
+timeout 1500 python profiles/parity_sweep_ranks.py 40 20261106 > gpurun_out/r02_parity_sweep_ranks.jsonl 2> gpurun_out/r02_parity_sweep_ranks.err
+echo "ranks sweep rc=$?"; tail -1 gpurun_out/r02_parity_sweep_ranks.jsonl; grep '"ok": false' gpurun_out/r02_parity_sweep_ranks.jsonl | cut -c1-400 | head -5

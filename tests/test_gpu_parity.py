@@ -429,3 +429,69 @@ def test_reference_sample_input_settings_run(b200):
     o.solve()
     assert abs(s.solver.iterations - o.iterations) <= 1
     s.destroy_system()
+
+
+@pytest.mark.parametrize("case", ["sorted", "unsorted_rows", "row_out_of_range", "device_pointers"])
+def test_ij_host_rows_cross_the_link_as_a_row_pointer(b200, case):
+    """SetValues2 with HOST arrays of >= 2^20 triplets sorted by row (columns in any order, empty rows anywhere): the row ids are
+    turned into a row pointer by the host threads and only that crosses the link (csrc/ij.cu); the assembled matrix must be what the
+    plain copy gives.  Unsorted rows and rows outside [ilower, iupper] take the plain copy; the latter is rejected by Assemble."""
+    import ctypes as C
+    import scipy.sparse as sp
+    rng = np.random.default_rng(31)
+    n = 220_000
+    # (scipy.sparse.random would draw from all n^2 positions: tens of GB at this size)
+    rr = np.repeat(np.arange(n, dtype=np.int64), 5)
+    cc = rng.integers(0, n, size=5 * n)
+    keep = ~np.isin(rr, [0, 1, 777, n - 2, n - 1])           # empty rows at both ends and inside
+    M = sp.coo_matrix((rng.standard_normal(int(keep.sum())), (rr[keep], cc[keep])), shape=(n, n)).tocsr()
+    D = np.full(n, 3.0)
+    D[[0, 1, 777, n - 2, n - 1]] = 0.0
+    M = (M + sp.diags(D)).tocsr()
+    M.eliminate_zeros()
+    M.sort_indices()
+    assert all(M.indptr[r + 1] == M.indptr[r] for r in (0, 1, 777, n - 2, n - 1))
+    rows = np.repeat(np.arange(n, dtype=np.int64), np.diff(M.indptr))
+    cols, vals = M.indices.astype(np.int64), M.data.copy()
+    for i in range(0, n, 3):                 # columns shuffled inside every third row
+        a, b = M.indptr[i], M.indptr[i + 1]
+        p = rng.permutation(b - a)
+        cols[a:b], vals[a:b] = cols[a:b][p], vals[a:b][p]
+    nnz = len(rows)
+    assert nnz >= 1 << 20
+    L = b200.lib()
+    L.b200hypre_h2d_bytes.restype = C.c_ulonglong
+    if case == "unsorted_rows":
+        k = nnz // 2
+        while rows[k] == rows[k + 1]:
+            k += 1
+        for arr in (rows, cols, vals):
+            arr[k], arr[k + 1] = arr[k + 1], arr[k]
+    if case == "row_out_of_range":
+        rows[-1] = n
+    A = b200.IJMatrix(0, n - 1)
+    moved0 = L.b200hypre_h2d_bytes()
+    if case == "device_pointers":
+        dev = [L.b200hypre_malloc(nnz * 8, 1) for _ in range(3)]
+        for d, h in zip(dev, (rows, cols, vals)):
+            L.b200hypre_memcpy(d, h.ctypes.data, nnz * 8, 1, 0)
+        moved0 = L.b200hypre_h2d_bytes()
+        A.set_values_ptr(nnz, dev[0], dev[1], dev[2])
+    else:
+        A.set_values(rows, cols, vals)
+    moved = L.b200hypre_h2d_bytes() - moved0
+    assert moved == {"sorted": nnz * 16 + (n + 1) * 4, "device_pointers": 0}.get(case, nnz * 24), (case, moved, nnz)
+    if case == "row_out_of_range":
+        with pytest.raises(b200.HypreError):
+            A.assemble()
+        A.destroy()
+        return
+    A.assemble()
+    ptr, col, val, _ = A.to_csr()
+    got = sp.csr_matrix((val, col, ptr), shape=(n, n))
+    assert abs(got - M).max() == 0.0
+    assert np.array_equal(np.diff(ptr), np.diff(M.indptr))
+    if case == "device_pointers":
+        for d in dev:
+            L.b200hypre_free(d, 1)
+    A.destroy()
