@@ -229,17 +229,17 @@ void cheby_setup(Amg &amg, AmgLevel &L) {
   ParCsr &A = *L.A;
   int n = A.n;
   const AmgOptions &o = amg.opt;
-  L.dsm.alloc(n);
-  k_inv_sqrt_diag<<<div_up(n, 256), 256, 0, stream()>>>(rv(A.diag), L.dsm.p);
-  count_launch();
+  L.dsm.alloc((size_t)std::max(n, 1));
+  // a rank may own no rows of a coarse level: no launch then (an empty grid is an invalid configuration), but it still takes part in
+  // the inner products and exchanges below
+  if (n) { k_inv_sqrt_diag<<<div_up(n, 256), 256, 0, stream()>>>(rv(A.diag), L.dsm.p); count_launch(); }
   double lmax = 0, lmin = 0;
   i64 gn = A.g_rows;
   int m = (int)std::min<i64>(o.cheby_eig_est, gn);
   if (m > 0) {
     i64 ld = ((i64)n + 1) & ~1LL;
     DVec<double> r(ld), p(ld), s(ld);
-    k_cheby_rand<<<div_up(n, 256), 256, 0, stream()>>>(n, ctx().rank + 1, 0, r.p);
-    count_launch();
+    if (n) { k_cheby_rand<<<div_up(n, 256), 256, 0, stream()>>>(n, ctx().rank + 1, 0, r.p); count_launch(); }
     std::vector<double> td, te;
     double gamma = dot_host(amg.dw, r.p, r.p, n), gamma_old, alpha, alpha_old = 0, beta = 0;
     vec_copy(p.p, r.p, n);

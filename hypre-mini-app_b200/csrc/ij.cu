@@ -118,6 +118,9 @@ __global__ void k_expand_rows(int nloc, const int *__restrict__ ptr, i64 ilower,
 bool stage_rows_compressed(DVec<i64> &dst, const i64 *rows, i64 n, i64 ilower, i64 iupper) {
   const i64 nloc = iupper - ilower + 1;
   if (n < (1 << 20) || n >= (1LL << 31) - 8 || nloc <= 0 || nloc >= (1LL << 31) - 8 || nloc > n) return false;
+  // the scan has to hide behind the transfer of cols and vals (16 threads: 12 ms per 117 M ids, against 34 ms of DMA): with fewer
+  // than 6 threads per rank (many ranks on a small host) the plain copy is the faster way
+  if (host_threads_for_staging() < 6) return false;
   int *hptr = g_ptr_stage.get((size_t)nloc + 1);
   if (!hptr) return false;
   const bool timing = getenv("B200_IJ_TIMING") != nullptr;

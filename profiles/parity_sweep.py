@@ -23,8 +23,9 @@ def one_case(bh, Oracle, rng, k):
     interp = int(rng.choice([6, 6, 0]))
     pmax = int(rng.choice([0, 2, 4, 4, 6]))
     tf = float(rng.choice([0.0, 0.0, 0.1, 0.3]))
-    relax = int(rng.choice([18, 18, 7, 16, 11]))
-    amg = dict(strong_threshold=theta, interp_type=interp, p_max_elmts=pmax, trunc_factor=tf, relax_type=relax, relax_order=0, coarsen_type=8)
+    relax = int(rng.choice([18, 18, 7, 16, 11, 12, 6, 8, 3]))
+    order = int(rng.choice([0, 0, 1])) if relax in (18, 7, 6, 8, 3) else 0
+    amg = dict(strong_threshold=theta, interp_type=interp, p_max_elmts=pmax, trunc_factor=tf, relax_type=relax, relax_order=order, coarsen_type=8)
     rec = {"case": k, "n": n, "stencil": stencil, **amg}
     s = bh.HypreSystem({"linear_system": {"type": f"build_{stencil}pt_stencil", "nx": n[0], "ny": n[1], "nz": n[2]},
                         "solver_settings": {"method": "gmres", "preconditioner": "boomeramg", "tolerance": 1e-8, "kspace": 50,
@@ -34,7 +35,7 @@ def one_case(bh, Oracle, rng, k):
     s.load()
     s.solve()
     o = Oracle(tolerance=1e-8, kspace=50, max_iterations=300, strong_threshold=theta, interp_type=interp, p_max_elmts=pmax,
-               trunc_factor=tf, relax_type=relax, relax_order=0)
+               trunc_factor=tf, relax_type=relax, relax_order=order)
     o.threads(len(os.sched_getaffinity(0)))
     o.gen_laplace(n, stencil=stencil)
     o.setup()

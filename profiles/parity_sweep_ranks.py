@@ -32,12 +32,14 @@ def main():
         pmax = int(rng.choice([0, 2, 4, 4]))
         tf = float(rng.choice([0.0, 0.0, 0.2]))
         surrogate = bool(rng.integers(3) == 0)
+        relax = int(rng.choice([18, 18, 7, 16, 11, 6, 8]))
+        order = int(rng.choice([0, 0, 1])) if relax in (18, 7, 6, 8) else 0
         nloc = n[0] * n[1] * n[2]
-        amg = dict(strong_threshold=theta, interp_type=interp, p_max_elmts=pmax, trunc_factor=tf)
+        amg = dict(strong_threshold=theta, interp_type=interp, p_max_elmts=pmax, trunc_factor=tf, relax_type=relax, relax_order=order)
         rec = {"case": k, "grid": grid, "n": n, "stencil": stencil, "halo_map": "reference" if surrogate else "true", **amg}
         try:
             cfg = T.settings(n, grid, stencil, **amg)
-            extra = dict(interp_type=interp, p_max_elmts=pmax, trunc_factor=tf)
+            extra = dict(interp_type=interp, p_max_elmts=pmax, trunc_factor=tf, relax_type=relax, relax_order=order)
             if surrogate:
                 cfg["linear_system"]["halo_map"] = "reference"
                 extra["halo_map"] = 1

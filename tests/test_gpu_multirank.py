@@ -209,6 +209,17 @@ def test_multirank_reference_halo_map(b200, n, grid, stencil):
     assert len(off) > 0 and off.min() == 0 and off.max() == len(np.unique(off)) - 1 and off.max() < nloc
 
 
+def test_multirank_chebyshev_with_a_rank_without_coarse_rows(b200):
+    """found by profiles/parity_sweep_ranks.py: 8 ranks, classical interpolation, Chebyshev smoother, the reference glue's halo
+    numbering -- a rank owns no rows of a coarse level; the eigenvalue estimate of the Chebyshev setup must not launch an empty grid
+    there and the rank must keep taking part in the inner products"""
+    n, grid = (8, 8, 7), (2, 2, 2)
+    cfg = settings(n, grid, 27, strong_threshold=0.57, interp_type=0, p_max_elmts=0, relax_type=16)
+    cfg["linear_system"]["halo_map"] = "reference"
+    res = run_ranks(8, cfg)
+    compare_with_oracle(res, n, grid, 27, 0.57, interp_type=0, p_max_elmts=0, relax_type=16, halo_map=1)
+
+
 @pytest.mark.parametrize("relax", [11, 12])
 def test_multirank_two_stage_gauss_seidel(b200, relax):
     """relax 11 / 12 on 2 ranks: the triangle is taken from every rank's own diagonal block (hybrid), off-rank couplings enter
