@@ -1,12 +1,11 @@
 #!/bin/bash
-# round-2, 8 GPUs: bench (parity leg + timed steps) at N = 8 and N = 4
+# 8 GPUs, final sources: bench (parity leg + timed steps + e2e)
 cd "$GRAFT_REPO_ROOT"
-for N in 8 2; do
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2962$N bench.py --gpus $N --steps 5 --warmup 3 > gpurun_out/r02m${N}_bench.json 2> gpurun_out/r02m${N}_bench.err
-tail -c 400 gpurun_out/r02m${N}_bench.err
-python - <<PY
+nvidia-smi --query-gpu=index,name --format=csv,noheader | head -8; nproc
+timeout 500 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29631 bench.py --gpus 8 --steps 5 --warmup 3 > gpurun_out/r02n8c_bench.json 2> gpurun_out/r02n8c_bench.err
+tail -c 400 gpurun_out/r02n8c_bench.err
+python - <<'PY'
 import json
-d=json.loads(open("gpurun_out/r02m${N}_bench.json").read().strip().splitlines()[-1])
-print("N=${N}", d["ms_per_step"], d["value"], d["setup_phases_ms"], d["iterations"], d["parity"], d["e2e"])
+d=json.loads(open("gpurun_out/r02n8c_bench.json").read().strip().splitlines()[-1])
+print("N=8", d["ms_per_step"], d["value"], d["setup_s"], d["solve_s"], d["iterations"], d["parity"]["ok"], d["parity"]["transport"], d["e2e"])
 PY
-done
