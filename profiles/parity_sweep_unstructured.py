@@ -1,0 +1,121 @@
+"""Randomised parity sweep on UNSTRUCTURED matrices (the suite and the other sweeps use grid stencils): weighted k-nearest-neighbour
+graphs of random points in 2-D / 3-D, symmetrised, optionally with a few hub rows of hundreds of entries (the capacity tiers and the
+overflow paths of the interpolation and SpGEMM kernels) and with a fraction of positive off-diagonals (the sign rules of the
+interpolation formulas), made diagonally dominant; rhs = A 1.  The matrices enter through the IJ interface as CSR.
+    python profiles/parity_sweep_unstructured.py [cases] [seed] > gpurun_out/parity_sweep_unstructured.jsonl
+Comparison as in profiles/parity_sweep.py: levels, CF, patterns of A_l / P_l bit for bit, values 1e-10, iterations within one."""
+import json
+import os
+import sys
+
+import numpy as np
+import scipy.sparse as sp
+from scipy.spatial import cKDTree
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "hypre-mini-app_b200", "python"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def random_matrix(rng, n, dim, k, hubs, hub_deg, positive_frac, shift):
+    pts = rng.random((n, dim))
+    d, idx = cKDTree(pts).query(pts, k=k + 1)
+    rows = np.repeat(np.arange(n), k)
+    cols = idx[:, 1:].ravel()
+    w = 1.0 / (d[:, 1:].ravel() + 0.05)
+    for h in rng.choice(n, size=hubs, replace=False):
+        nb = rng.choice(n, size=hub_deg, replace=False)
+        nb = nb[nb != h]
+        rows = np.concatenate([rows, np.full(len(nb), h)])
+        cols = np.concatenate([cols, nb])
+        w = np.concatenate([w, rng.random(len(nb)) + 0.1])
+    W = sp.coo_matrix((w, (rows, cols)), shape=(n, n)).tocsr()
+    W = W.maximum(W.T).tocoo()
+    sign = np.ones(W.nnz)
+    if positive_frac > 0:
+        up = W.row < W.col
+        flip = up & (rng.random(W.nnz) < positive_frac)
+        key = set(zip(W.row[flip].tolist(), W.col[flip].tolist()))
+        sign = np.array([-1.0 if ((r, c) in key or (c, r) in key) else 1.0 for r, c in zip(W.row.tolist(), W.col.tolist())])
+    off = sp.coo_matrix((-W.data * sign, (W.row, W.col)), shape=(n, n)).tocsr()
+    diag = np.asarray(abs(off).sum(axis=1)).ravel() * (1.0 + shift) + 1e-3
+    A = (off + sp.diags(diag)).tocsr()
+    A.sort_indices()
+    return A
+
+
+def main():
+    cases = int(sys.argv[1]) if len(sys.argv) > 1 else 60
+    seed = int(sys.argv[2]) if len(sys.argv) > 2 else 3
+    import b200hypre as bh
+    from oracle_lib import Oracle
+    bh.comm_init(0, 1)
+    rng = np.random.default_rng(seed)
+    bad = 0
+    for c in range(cases):
+        n = int(rng.integers(1500, 25000))
+        dim = int(rng.choice([2, 3]))
+        k = int(rng.choice([4, 8, 16, 32]))
+        hubs = int(rng.choice([0, 0, 1, 3]))
+        hub_deg = int(rng.choice([120, 300, 700]))
+        pos = float(rng.choice([0.0, 0.0, 0.1]))
+        shift = float(rng.choice([0.0, 0.01, 0.2]))
+        theta = float(rng.choice([0.25, 0.5]))
+        interp = int(rng.choice([6, 6, 0]))
+        pmax = int(rng.choice([0, 4, 4]))
+        tf = float(rng.choice([0.0, 0.0, 0.2]))
+        relax = int(rng.choice([18, 18, 7, 11]))
+        A = random_matrix(rng, n, dim, k, hubs, hub_deg, pos, shift)
+        b = A @ np.ones(n)
+        amg = dict(strong_threshold=theta, interp_type=interp, p_max_elmts=pmax, trunc_factor=tf, relax_type=relax, relax_order=0, coarsen_type=8)
+        rec = {"case": c, "n": n, "dim": dim, "k": k, "hubs": hubs, "hub_deg": hub_deg if hubs else 0, "positive_frac": pos, "shift": shift,
+               "nnz": int(A.nnz), "max_row": int(np.diff(A.indptr).max()), **amg}
+        s = bh.HypreSystem({"linear_system": {"type": "csr", "ptr": A.indptr, "col": A.indices, "val": A.data, "rhs": b},
+                            "solver_settings": {"method": "gmres", "preconditioner": "boomeramg", "tolerance": 1e-8, "kspace": 50,
+                                                "max_iterations": 400, "orthogonalization": "mgs"},
+                            "boomeramg_settings": amg})
+        s.setup_precon_and_solver()
+        s.load()
+        s.solve()
+        o = Oracle(tolerance=1e-8, kspace=50, max_iterations=400, strong_threshold=theta, interp_type=interp, p_max_elmts=pmax,
+                   trunc_factor=tf, relax_type=relax, relax_order=0)
+        o.threads(len(os.sched_getaffinity(0)))
+        o.set_csr(A.indptr, A.indices, A.data, b)
+        o.setup()
+        o.solve()
+        g = s.precond
+        why = []
+        if g.num_levels != o.num_levels:
+            why.append(f"levels {g.num_levels} vs {o.num_levels}")
+        else:
+            worst = 0.0
+            for l in range(o.num_levels):
+                for which in (("A", "P") if l + 1 < o.num_levels else ("A",)):
+                    gp, gc, gv = g.level_matrix(l, which)
+                    rp, rc, rv, _ = o.matrix(l, which)
+                    if not (np.array_equal(gp, rp) and np.array_equal(gc, rc.astype(gc.dtype))):
+                        why.append(f"{which}[{l}] pattern")
+                    elif len(rv):
+                        worst = max(worst, float(np.abs(gv - rv).max() / np.abs(rv).max()))
+                if l + 1 < o.num_levels and not np.array_equal(g.level_cf(l), o.cf(l)):
+                    why.append(f"CF[{l}]")
+            rec["val_relerr"] = worst
+            if worst > 1e-10:
+                why.append(f"values {worst:.2e}")
+        rec.update(levels=int(g.num_levels), iters=[int(s.solver.iterations), int(o.iterations)], converged=int(s.solver.converged),
+                   err_vs_1=float(np.abs(s.solution() - 1.0).max()))
+        if abs(s.solver.iterations - o.iterations) > 1:
+            why.append("iterations")
+        if s.solver.converged != 1 and o.iterations < 400:
+            why.append("solve")
+        rec["ok"] = not why
+        rec["why"] = why
+        bad += 0 if rec["ok"] else 1
+        print(json.dumps(rec), flush=True)
+        s.destroy_system()
+    print(json.dumps({"summary": True, "cases": cases, "seed": seed, "failed": bad}), flush=True)
+    sys.exit(1 if bad else 0)
+
+
+if __name__ == "__main__":
+    main()
