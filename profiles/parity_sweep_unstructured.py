@@ -44,7 +44,72 @@ def random_matrix(rng, n, dim, k, hubs, hub_deg, positive_frac, shift):
     return A
 
 
+def main_ranks(cases, seed):
+    """--ranks: the same matrices, block rows over 2 .. 8 ranks sharing the GPU (tests/mr_worker.py), against the N-virtual-rank
+    oracle.  The points are in random order, so nearly every connection of a row leaves its rank: many halo points, every rank a
+    neighbour of every other, distance-two points everywhere."""
+    import tempfile
+    import traceback
+    import test_gpu_multirank as T
+    from oracle_lib import Oracle
+    rng = np.random.default_rng(seed)
+    bad = 0
+    for c in range(cases):
+        nranks = int(rng.choice([2, 3, 4, 8]))
+        n = int(rng.integers(800, 6000))
+        dim = int(rng.choice([2, 3]))
+        k = int(rng.choice([4, 8, 16]))
+        hubs = int(rng.choice([0, 0, 2]))
+        pos = float(rng.choice([0.0, 0.0, 0.1]))
+        shift = float(rng.choice([0.0, 0.01, 0.2]))
+        theta = float(rng.choice([0.25, 0.5]))
+        interp = int(rng.choice([6, 6, 0]))
+        pmax = int(rng.choice([0, 4, 4]))
+        tf = float(rng.choice([0.0, 0.0, 0.2]))
+        relax = int(rng.choice([18, 18, 7, 11, 16]))
+        A = random_matrix(rng, n, dim, k, hubs, 150, pos, shift)
+        b = A @ np.ones(n)
+        amg = dict(strong_threshold=theta, interp_type=interp, p_max_elmts=pmax, trunc_factor=tf, relax_type=relax, relax_order=0)
+        rec = {"case": c, "ranks": nranks, "n": n, "dim": dim, "k": k, "hubs": hubs, "positive_frac": pos, "shift": shift, "nnz": int(A.nnz), **amg}
+        try:
+            with tempfile.TemporaryDirectory() as tmp:
+                f = os.path.join(tmp, "sys.npz")
+                np.savez(f, ptr=A.indptr, col=A.indices, val=A.data, rhs=b)
+                cfg = {"linear_system": {"type": "csr_npz", "file": f},
+                       "solver_settings": {"method": "gmres", "preconditioner": "boomeramg", "tolerance": 1e-8, "kspace": 50, "max_iterations": 400},
+                       "boomeramg_settings": amg}
+                res = T.run_ranks(nranks, cfg)
+            o = Oracle(tolerance=1e-8, kspace=50, max_iterations=400, **amg)
+            o.threads(len(os.sched_getaffinity(0)))
+            o.set_csr(A.indptr, A.indices, A.data, b, nparts=nranks)
+            o.setup()
+            xo = o.solve()
+            nl = int(res[0]["num_levels"])
+            assert nl == o.num_levels, (nl, o.num_levels)
+            for l in range(nl):
+                T.check_csr(T.stack_csr(res, f"A{l}"), o.matrix(l, "A"), f"A[{l}]")
+                if l + 1 < nl:
+                    cf = np.concatenate([d[f"cf{l}"] for d in res])
+                    assert np.array_equal(cf, o.cf(l)), f"CF[{l}] differs"
+                    T.check_csr(T.stack_csr(res, f"P{l}"), o.matrix(l, "P"), f"P[{l}]")
+                    T.check_csr(T.stack_csr(res, f"R{l}"), o.matrix(l, "R"), f"R[{l}]")
+            its = int(res[0]["iterations"])
+            assert abs(its - o.iterations) <= 1, (its, o.iterations)
+            x = np.concatenate([d["x"] for d in res])
+            assert np.abs(x - 1.0).max() < 1e-5
+            rec.update(ok=True, levels=nl, iters=[its, int(o.iterations)])
+        except Exception as e:
+            rec.update(ok=False, why="".join(traceback.format_exception_only(type(e), e))[-1500:])
+            bad += 1
+        print(json.dumps(rec), flush=True)
+    print(json.dumps({"summary": True, "ranks": True, "cases": cases, "seed": seed, "failed": bad}), flush=True)
+    sys.exit(1 if bad else 0)
+
+
 def main():
+    if "--ranks" in sys.argv:
+        args = [a for a in sys.argv[1:] if a != "--ranks"]
+        return main_ranks(int(args[0]) if args else 30, int(args[1]) if len(args) > 1 else 4)
     cases = int(sys.argv[1]) if len(sys.argv) > 1 else 60
     seed = int(sys.argv[2]) if len(sys.argv) > 2 else 3
     import b200hypre as bh

@@ -26,6 +26,10 @@ def main():
         b200hypre.comm_init_torch()
     else:
         b200hypre.comm_init_shm(rank, nranks, transport)
+    ls = cfg["linear_system"]
+    if ls.get("type") == "csr_npz":   # a global CSR system stored by the caller (profiles/parity_sweep_unstructured.py --ranks)
+        z = np.load(ls["file"])
+        ls.update(type="csr", ptr=z["ptr"], col=z["col"], val=z["val"], rhs=z["rhs"])
     s = b200hypre.HypreSystem(cfg, rank=rank, nranks=nranks)
     s.setup_precon_and_solver()
     s.load()
