@@ -9,8 +9,6 @@ import os
 import sys
 
 import numpy as np
-import scipy.sparse as sp
-from scipy.spatial import cKDTree
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "hypre-mini-app_b200", "python"))
@@ -18,30 +16,8 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 
 def random_matrix(rng, n, dim, k, hubs, hub_deg, positive_frac, shift):
-    pts = rng.random((n, dim))
-    d, idx = cKDTree(pts).query(pts, k=k + 1)
-    rows = np.repeat(np.arange(n), k)
-    cols = idx[:, 1:].ravel()
-    w = 1.0 / (d[:, 1:].ravel() + 0.05)
-    for h in rng.choice(n, size=hubs, replace=False):
-        nb = rng.choice(n, size=hub_deg, replace=False)
-        nb = nb[nb != h]
-        rows = np.concatenate([rows, np.full(len(nb), h)])
-        cols = np.concatenate([cols, nb])
-        w = np.concatenate([w, rng.random(len(nb)) + 0.1])
-    W = sp.coo_matrix((w, (rows, cols)), shape=(n, n)).tocsr()
-    W = W.maximum(W.T).tocoo()
-    sign = np.ones(W.nnz)
-    if positive_frac > 0:
-        up = W.row < W.col
-        flip = up & (rng.random(W.nnz) < positive_frac)
-        key = set(zip(W.row[flip].tolist(), W.col[flip].tolist()))
-        sign = np.array([-1.0 if ((r, c) in key or (c, r) in key) else 1.0 for r, c in zip(W.row.tolist(), W.col.tolist())])
-    off = sp.coo_matrix((-W.data * sign, (W.row, W.col)), shape=(n, n)).tocsr()
-    diag = np.asarray(abs(off).sum(axis=1)).ravel() * (1.0 + shift) + 1e-3
-    A = (off + sp.diags(diag)).tocsr()
-    A.sort_indices()
-    return A
+    from workloads import knn_graph_matrix   # tests/workloads.py: the generator the test suite uses as well
+    return knn_graph_matrix(rng, n, dim, k, hubs, hub_deg, positive_frac, shift)
 
 
 def main_ranks(cases, seed):

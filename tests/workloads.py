@@ -108,6 +108,38 @@ def momentum3(n, seed=20261, peclet=2.0, coupling=0.05, time_term=0.5):
     return A, b
 
 
+def knn_graph_matrix(rng, n, dim=3, k=8, hubs=0, hub_deg=150, positive_frac=0.0, shift=0.01):
+    """Unstructured test operator: weighted k-nearest-neighbour graph of n random points in the unit square / cube, symmetrised;
+    `hubs` rows get `hub_deg` extra random connections (rows of hundreds of entries: the capacity tiers and overflow paths of the
+    interpolation and SpGEMM kernels); a fraction of the off-diagonal pairs is made positive (the sign rules of the interpolation
+    formulas); the diagonal is (1 + shift) times the absolute row sum.  Symmetric, diagonally dominant; rhs = A 1 has solution 1."""
+    from scipy.spatial import cKDTree
+    pts = rng.random((n, dim))
+    d, idx = cKDTree(pts).query(pts, k=k + 1)
+    rows = np.repeat(np.arange(n), k)
+    cols = idx[:, 1:].ravel()
+    w = 1.0 / (d[:, 1:].ravel() + 0.05)
+    for h in rng.choice(n, size=hubs, replace=False):
+        nb = rng.choice(n, size=hub_deg, replace=False)
+        nb = nb[nb != h]
+        rows = np.concatenate([rows, np.full(len(nb), h)])
+        cols = np.concatenate([cols, nb])
+        w = np.concatenate([w, rng.random(len(nb)) + 0.1])
+    W = sp.coo_matrix((w, (rows, cols)), shape=(n, n)).tocsr()
+    W = W.maximum(W.T).tocoo()
+    sign = np.ones(W.nnz)
+    if positive_frac > 0:
+        up = W.row < W.col
+        flip = up & (rng.random(W.nnz) < positive_frac)
+        key = set(zip(W.row[flip].tolist(), W.col[flip].tolist()))
+        sign = np.array([-1.0 if ((r, c) in key or (c, r) in key) else 1.0 for r, c in zip(W.row.tolist(), W.col.tolist())])
+    off = sp.coo_matrix((-W.data * sign, (W.row, W.col)), shape=(n, n)).tocsr()
+    diag = np.asarray(abs(off).sum(axis=1)).ravel() * (1.0 + shift) + 1e-3
+    A = (off + sp.diags(diag)).tocsr()
+    A.sort_indices()
+    return A
+
+
 def write_matrix_market(A, b, mat_path, rhs_path):
     """MatrixMarket coordinate real general matrix + array rhs, 1-based"""
     A = A.tocoo()
