@@ -127,3 +127,41 @@ def test_interpolation_row_functions_equal_the_oracle_on_the_host(tmp_path, inte
             assert np.array_equal(gv, pv), (tf, pmax, l, float(np.abs(gv - pv).max()))
             checked += 1
     assert checked == 10
+
+
+@pytest.mark.skipif(shutil.which("nvcc") is None or not os.path.exists(LIB), reason="nvcc or the built library missing")
+def test_host_rows_to_row_pointer(tmp_path):
+    """SetValues2 from host arrays: the row ids of a row-sorted triplet list are turned into a row pointer by host threads (csrc/ij.cu).
+    Against numpy.searchsorted on random lists with empty rows at both ends and inside, at sizes around the thread-chunk boundaries;
+    lists that are not nondecreasing or leave [ilower, iupper] must be refused (they take the plain copy)."""
+    import numpy as np
+    exe = tmp_path / "rows_to_ptr"
+    subprocess.check_call(["nvcc", "-std=c++17", "-O1", "-gencode", "arch=compute_100a,code=sm_100a", "--expt-relaxed-constexpr",
+                           "-I", CSRC, "-o", str(exe), os.path.join(ROOT, "tests", "host", "rows_to_ptr.cu"),
+                           "-L", os.path.dirname(LIB), "-lb200hypre", "-Xlinker", "-rpath", "-Xlinker", os.path.dirname(LIB)])
+    rng = np.random.default_rng(77)
+    cases, want = [], []
+    for n in [1, 2, 3, 7, 8, 9, 15, 16, 17, 31, 33, 100, 1000, 4097, 50001]:
+        for trial in range(4):
+            lo = int(rng.integers(0, 1000))
+            nloc = int(rng.integers(1, max(2, n)))
+            hi = lo + nloc - 1
+            rows = np.sort(rng.integers(lo, hi + 1, size=n))
+            if trial == 1 and nloc > 4:          # empty rows at both ends
+                rows = np.clip(rows, lo + 2, hi - 2)
+            kind = "ok"
+            if trial == 2 and n > 3 and rows[0] != rows[-1]:
+                k = int(np.argmax(rows[1:] != rows[:-1]))    # swap across a row boundary: not nondecreasing any more
+                rows[k], rows[k + 1] = rows[k + 1], rows[k]
+                kind = "bad"
+            if trial == 3:
+                rows = rows.copy()
+                rows[int(rng.integers(0, n))] = hi + 1 if n % 2 else lo - 1
+                rows = rows if n < 2 else np.concatenate([np.sort(rows[rows < lo]), np.sort(rows[rows >= lo])])
+                kind = "bad"
+            cases.append(f"{n} {lo} {hi}\n" + " ".join(str(int(r)) for r in rows))
+            want.append("bad" if kind == "bad" else " ".join(str(int(v)) for v in np.searchsorted(rows, np.arange(lo, hi + 2), side="left")))
+    out = subprocess.run([str(exe)], input="\n".join(cases) + "\n", capture_output=True, text=True, check=True).stdout.splitlines()
+    assert len(out) == len(want)
+    for k, (g, w) in enumerate(zip(out, want)):
+        assert g == w, (k, cases[k][:80], g[:80], w[:80])
