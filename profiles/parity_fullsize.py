@@ -3,6 +3,7 @@
 values by maximum relative difference -- plus iteration counts and solutions of the GMRES solve.
     python profiles/parity_fullsize.py 256 > gpurun_out/parity_256.jsonl            # 7-pt, theta 0.25
     python profiles/parity_fullsize.py 160 27 0.57 > gpurun_out/parity_27pt_160.jsonl
+    python profiles/parity_fullsize.py 256 7 0.25 0 > gpurun_out/parity_256_classical.jsonl   # interp_type 0
 The oracle is test infrastructure; this script is a checker like the tests, kept out of the -m gpu suite because of its size."""
 import json
 import os
@@ -20,18 +21,19 @@ def main():
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 256
     stencil = int(sys.argv[2]) if len(sys.argv) > 2 else 7
     theta = float(sys.argv[3]) if len(sys.argv) > 3 else 0.25
+    interp = int(sys.argv[4]) if len(sys.argv) > 4 else 6      # 6 = extended+i, 0 = classical modified
     import b200hypre as bh
     from oracle_lib import Oracle
     bh.comm_init(0, 1)
     s = bh.HypreSystem({"linear_system": {"type": f"build_{stencil}pt_stencil", "nx": n, "ny": n, "nz": n},
                         "solver_settings": {"method": "gmres", "preconditioner": "boomeramg", "tolerance": 1e-8, "kspace": 50,
                                             "max_iterations": 200, "orthogonalization": "mgs"},
-                        "boomeramg_settings": {"strong_threshold": theta}})
+                        "boomeramg_settings": {"strong_threshold": theta, "interp_type": interp}})
     s.setup_precon_and_solver()
     s.load()
     s.solve()
     t0 = time.time()
-    o = Oracle(tolerance=1e-8, kspace=50, max_iterations=200, strong_threshold=theta)
+    o = Oracle(tolerance=1e-8, kspace=50, max_iterations=200, strong_threshold=theta, interp_type=interp)
     cores = o.threads(0)
     o.gen_laplace(n, stencil=stencil)
     o.setup()
