@@ -5,7 +5,8 @@
     python profiles/make_roofline_traffic.py gpurun_out/traffic.csv
 `dram_bytes_per_launch` of a kernel class = DRAM bytes of all its kernels in ONE step / the number of profiler scopes of that
 class in one step (bench.py's `launches_timed` / steps), i.e. per launch in the sense of `roofline.achieved`.  bench.py only
-reports the number when `source_sha` equals the hash of the sources it runs (source_sha() below, same function there)."""
+reports the number when `source_sha` equals the hash of the sources it runs (source_sha() below, which bench.py imports).  The hash is
+taken over the code with comments and white space removed (code_only): what the compiler sees."""
 import csv
 import glob
 import hashlib
@@ -20,11 +21,36 @@ CLASSES = {"interp_rows": ("k_interp_flat", "k_interp_trunc", "k_interp_ovf"), "
 SCOPES_PER_STEP = {"interp_rows": 4, "spgemm_numeric": 8, "spgemm_symbolic": 8}   # scopes above bench.py's 32 MB threshold at lap7_256
 
 
+def code_only(text):
+    """the C++ / CUDA source without // and /* */ comments (string and character literals respected) and with every run of white
+    space collapsed: what the compiler sees, so that a comment or layout edit does not orphan a traffic capture"""
+    out, i, n = [], 0, len(text)
+    while i < n:
+        c = text[i]
+        if c == "/" and i + 1 < n and text[i + 1] == "/":
+            while i < n and text[i] != "\n":
+                i += 1
+        elif c == "/" and i + 1 < n and text[i + 1] == "*":
+            j = text.find("*/", i + 2)
+            i = n if j < 0 else j + 2
+            out.append(" ")
+        elif c in "\"'":
+            j = i + 1
+            while j < n and text[j] != c:
+                j += 2 if text[j] == "\\" else 1
+            out.append(text[i:j + 1])
+            i = j + 1
+        else:
+            out.append(c)
+            i += 1
+    return " ".join("".join(out).split())
+
+
 def source_sha():
     h = hashlib.sha256()
     for f in sorted(glob.glob(os.path.join(ROOT, "hypre-mini-app_b200", "csrc", "*"))):
         h.update(os.path.basename(f).encode())
-        h.update(open(f, "rb").read())
+        h.update(code_only(open(f, encoding="utf-8").read()).encode())
     return h.hexdigest()[:16]
 
 
@@ -46,7 +72,7 @@ def main():
                 tot[c] += float(r[value].replace(",", "")) * scale.get(r[unit], 1.0)
                 launches[c] += 1 if r[metric].endswith("read.sum") else 0
                 break
-    out = {"source_sha": source_sha(), "how": "ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum over one step of bench.py (lap7_256); "
+    out = {"source_sha": source_sha(), "source_sha_kind": "sha256 over csrc/* with comments and white space removed (code_only)", "how": "ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum over one step of bench.py (lap7_256); "
                                               "bytes of all kernels of the class / profiler scopes of the class per step"}
     for c in CLASSES:
         if launches[c]:
