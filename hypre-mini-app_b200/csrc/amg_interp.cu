@@ -1,4 +1,4 @@
-// amg_interp.cu -- extended+i interpolation (interp_type 6) with truncation: tier driver.
+// amg_interp.cu -- extended+i interpolation (interp_type 6) with truncation: tier driver; classical interpolation (interp_type 0).
 // Replaces hypre_BoomerAMGBuildExtPIInterp + hypre_BoomerAMGInterpTruncation reached from HYPRE_BoomerAMGSetup
 // (/root/reference/src/HypreSystem.cpp:197,212,232 set the options, :323 via :692 runs it); formula and entry order:
 // SURVEY.md A.5.  hypre itself is not in /root/reference.
@@ -7,8 +7,9 @@
 // storage order, and for a strong F neighbour its strong C neighbours in storage order"; every weight is a sum whose terms
 // arrive in (entry of row i, entry of the neighbour row) order.  The group kernel k_interp_flat (amg_interp_flat.cuh, design
 // notes there and in DESIGN.md section 4.0) produces bit-identical rows with G lanes per row.  Rows are tiered by |C-hat| and
-// hash load: (G, capacity) = (8, 32) when strength rows are short, then (32, 128); the few rows beyond that run
-// rows::interp_row itself with a global-memory scratch list.  Compiled with -fmad=false (the operation order of every value
+// hash load: (G, capacity) = (8, 32) when strength rows are short, (16, 64) when matrix rows average at most 40 entries, then
+// (32, 128); a row that overflows its tier is taken by the next, and the few rows beyond the last run rows::interp_row itself with
+// a global-memory scratch list.  The second half of the file is classical modified interpolation (interp_type 0).  Compiled with -fmad=false (the operation order of every value
 // that feeds a discrete decision is part of the parity contract).
 #include "amg.h"
 #include "amg_rows.cuh"

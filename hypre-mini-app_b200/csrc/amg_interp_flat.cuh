@@ -3,7 +3,8 @@
 // Replaces hypre_BoomerAMGBuildExtPIInterp + hypre_BoomerAMGInterpTruncation reached from HYPRE_BoomerAMGSetup
 // (/root/reference/src/HypreSystem.cpp:197,212,232 options, :323 via :692 call).
 //
-// G lanes own one row; 256 / G rows per block.  What changed against the first kernel (profiles/r01_interp_sass_notes.md:
+// G lanes own one row (G = 8, 16 or 32, chosen per level by the tier driver); BT / G rows per block of BT = 128 threads.  What changed
+// against the first kernel (profiles/r01_interp_sass_notes.md:
 // 6 078 warp instructions per row on level 1, control-flow bound):
 //   * the walks run over C-COMPRESSED rows.  Of the row of a distributed neighbour j only the entries whose column is a C
 //     point can be in C-hat_i, plus the one back-edge a_ji; of its strength row only the C entries can enter C-hat_i.  Those
@@ -22,8 +23,9 @@
 //   * every C-hat slot keeps a bit mask of the neighbours (tags) that contribute to it; a lane per slot then adds its
 //     terms in ascending tag order, which is the order of the sequential loop over the entries of row i;
 //   * the diagonal accumulates its at most one term per tag through a shuffle chain in tag order;
-//   * truncation (qsort2abs tie order, sequential by definition) runs after a block barrier with one LANE per row of the
-//     block in a single warp, instead of one lane of every group;
+//   * truncation (qsort2abs tie order, sequential by definition) is a kernel of its own, k_interp_trunc, with one THREAD per row:
+//     rows that need it are written raw to a chunked scratch and marked pending (MODE 2), so the row kernel has no block barrier
+//     (one lane of every group, and later one warp per block behind a barrier, both left the machine idle);
 //   * every collective names the full warp with width = G and every loop that contains one has a warp-uniform trip count
 //     (per-group masks make the compiler serialise collectives over the groups, profiles/r01_interp_sass_notes.md).
 #pragma once

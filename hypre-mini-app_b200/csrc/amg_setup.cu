@@ -1,5 +1,5 @@
 // amg_setup.cu -- BoomerAMG setup entirely on the device (no CPU fallback): strength of connection, PMIS
-// coarsening with hypre's seeded random measure, coarse numbering, extended+i interpolation with truncation,
+// coarsening with hypre's seeded random measure, coarse numbering, extended+i or classical interpolation with truncation,
 // transposition and the Galerkin product RAP as two two-pass hash SpGEMMs, smoother data, coarsest dense LU.
 // Replaces HYPRE_BoomerAMGSetup (/root/reference/src/HypreSystem.cpp:323, reached through
 // HYPRE_ParCSRGMRESSetup at :692); algorithm definitions: SURVEY.md Appendix A.3-A.9 (hypre is not in /root/reference).
