@@ -14,8 +14,11 @@
 //   * block-row partition                           /root/reference/src/HypreSystem.cpp:525-544
 //   * generator numbering / values                  /root/reference/src/laplace_3d_weak_scaling.hpp:98-169,216-233,321,558,600
 //                                                   /root/reference/src/HypreSystem.cpp:1516,1540-1556
+//   * interpolation type of the sample input         /root/reference/etc/hypre_app.yaml:41 via src/HypreSystem.cpp:195-198 (classical)
+//   * surrogate off-rank numbering (halo_map = 1)    /root/reference/src/HypreSystem.cpp:1553-1556
 // Pins that do exist are exercised in tests/: generator known answer x==1 and nnz=(3n-2)^3, scipy cross
-// checks (SpMV, P^T A P, GMRES solution), hand-computable PMIS/ext+i cases.
+// checks (SpMV, P^T A P, GMRES solution), hand-computable PMIS / ext+i / classical-interpolation cases, dense
+// restatements of both interpolation formulas, the HMIS checkerboard, a numpy restatement of the halo map.
 //
 // Multi-rank semantics are modelled with "virtual ranks": one global matrix plus a row partition.  Every row is
 // stored in ParCSR order as seen by its owner (diagonal entry, then own-range columns, then off-range columns)
