@@ -649,30 +649,40 @@ void HypreSystem::build_mm_matrix(const std::string &matfile) {
   LineParser lp;
   read_size_line(f, lp);
   rows_.clear(); cols_.clear(); vals_.clear();
-  size_t guess = (size_t)((double)nnz_ / std::max(1, nproc_) * 1.1) + 16;
-  rows_.reserve(guess); cols_.reserve(guess); vals_.reserve(guess);
-  auto keep = [&](long long r, long long c, double v) {
-    if (r >= iLower_ && r <= iUpper_) { rows_.push_back(r); cols_.push_back(c); vals_.push_back(v); }
-  };
-  const char *b, *e;
-  long long seen = 0;
-  while (f.next(b, e)) {
-    if ((b < e && *b == '%') || blank(b, e)) continue;
-    lp.set(b, e);
-    long long i, j;
+  // the body is parsed by all the host threads this rank may use (mm_text.h: read_lines_parallel); the pieces are appended in file
+  // order, so rows_ / cols_ / vals_ are what a single reader would have produced (duplicates keep their order: Set semantics)
+  struct Piece { std::vector<HYPRE_BigInt> rows, cols; std::vector<HYPRE_Complex> vals; long long seen = 0; };
+  const int threads = mmtext::loader_threads(nproc_);
+  std::vector<Piece> piece((size_t)threads);
+  const bool pattern = m.pattern, cplx = complexNumbers_;
+  const long long lo = iLower_, hi = iUpper_;
+  mmtext::read_lines_parallel(f, threads, [&](int k, const char *b, const char *e) {
+    long long i = 0, j = 0;
     double re = 1.0, im = 0.0;
-    if (!lp.integer(i) || !lp.integer(j)) throw std::runtime_error("Malformed entry line in " + matfile);
-    if (!m.pattern && !lp.real(re)) throw std::runtime_error("Malformed entry line in " + matfile);
-    if (complexNumbers_ && !lp.real(im)) throw std::runtime_error("complex_numbers: missing imaginary part in " + matfile);
+    if (!mmtext::parse_entry_line(b, e, true, pattern, cplx, matfile, i, j, re, im)) return;
     --i; --j;
-    ++seen;
-    if (!complexNumbers_) keep(i, j, re);
+    Piece &P = piece[(size_t)k];
+    ++P.seen;
+    auto keep = [&](long long r, long long cc, double v) {
+      if (r >= lo && r <= hi) { P.rows.push_back(r); P.cols.push_back(cc); P.vals.push_back(v); }
+    };
+    if (!cplx) keep(i, j, re);
     else {
       keep(2 * i, 2 * j, re);
       keep(2 * i, 2 * j + 1, -im);
       keep(2 * i + 1, 2 * j, im);
       keep(2 * i + 1, 2 * j + 1, re);
     }
+  });
+  long long seen = 0;
+  size_t kept = 0;
+  for (auto &P : piece) { seen += P.seen; kept += P.rows.size(); }
+  rows_.reserve(kept); cols_.reserve(kept); vals_.reserve(kept);
+  for (auto &P : piece) {
+    rows_.insert(rows_.end(), P.rows.begin(), P.rows.end());
+    cols_.insert(cols_.end(), P.cols.begin(), P.cols.end());
+    vals_.insert(vals_.end(), P.vals.begin(), P.vals.end());
+    Piece().rows.swap(P.rows); Piece().cols.swap(P.cols); Piece().vals.swap(P.vals);   // release the piece
   }
   if (seen * (complexNumbers_ ? 4 : 1) != nnz_ && iproc_ == 0)
     std::cout << "WARNING: " << matfile << " declares " << nnz_ << " entries, found " << seen * (complexNumbers_ ? 4 : 1) << std::endl;
@@ -779,14 +789,21 @@ void HypreSystem::build_ij_matrix(const std::string &matfile, int nfiles) {
     long long il, iu, jl, ju;
     if (!lp.integer(il) || !lp.integer(iu) || !lp.integer(jl) || !lp.integer(ju)) throw std::runtime_error("Bad IJ matrix header in " + f.path());
     if (iu < iLower_ || il > iUpper_) continue;
-    const char *b, *e;
-    while (f.next(b, e)) {
-      if (blank(b, e)) continue;
-      lp.set(b, e);
-      long long r, c;
-      double v;
-      if (!lp.integer(r) || !lp.integer(c) || !lp.real(v)) throw std::runtime_error("Malformed entry line in " + f.path());
-      if (r >= iLower_ && r <= iUpper_) { rows_.push_back(r); cols_.push_back(c); vals_.push_back(v); }
+    struct Piece { std::vector<HYPRE_BigInt> rows, cols; std::vector<HYPRE_Complex> vals; };
+    const int threads = mmtext::loader_threads(nproc_);
+    std::vector<Piece> piece((size_t)threads);
+    const long long lo = iLower_, hi = iUpper_;
+    const std::string path = f.path();
+    mmtext::read_lines_parallel(f, threads, [&](int k, const char *b, const char *e) {
+      long long r = 0, c = 0;
+      double v = 0.0, unused = 0.0;
+      if (!mmtext::parse_entry_line(b, e, false, false, false, path, r, c, v, unused)) return;
+      if (r >= lo && r <= hi) { piece[(size_t)k].rows.push_back(r); piece[(size_t)k].cols.push_back(c); piece[(size_t)k].vals.push_back(v); }
+    });
+    for (auto &P : piece) {
+      rows_.insert(rows_.end(), P.rows.begin(), P.rows.end());
+      cols_.insert(cols_.end(), P.cols.begin(), P.cols.end());
+      vals_.insert(vals_.end(), P.vals.begin(), P.vals.end());
     }
   }
   MPI_Barrier(comm_);

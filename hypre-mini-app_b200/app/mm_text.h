@@ -1,5 +1,5 @@
 // mm_text.h -- text-file primitives of the MatrixMarket / HYPRE-IJ loaders (app/HypreSystem.cpp): a read-only memory map
-// with a line cursor, bounded number parsing, the MatrixMarket banner and size line.  Written fresh; accepts what the
+// with a line cursor, bounded number parsing, a multi-threaded reader of body lines, the MatrixMarket banner and size line.  Written fresh; accepts what the
 // reference's reader accepts (/root/reference/src/mmio.c:96-217 mm_read_banner / mm_read_mtx_crd_size, used from
 // /root/reference/src/HypreSystem.cpp:1670-1969) -- tests/test_mmio_crosscheck.py compares the two on odd banners.
 #pragma once
@@ -7,12 +7,17 @@
 #include <sys/mman.h>
 #include <sys/stat.h>
 #include <unistd.h>
+#include <sched.h>
 #include <algorithm>
+#include <charconv>
 #include <cstdlib>
 #include <cstring>
+#include <exception>
 #include <sstream>
 #include <stdexcept>
 #include <string>
+#include <thread>
+#include <vector>
 
 namespace nalu {
 namespace mmtext {
@@ -47,6 +52,12 @@ class TextFile {
     return true;
   }
   const std::string &path() const { return path_; }
+  // the unread rest of the file as one byte range; the cursor moves to the end (read_lines_parallel)
+  void take_rest(const char *&b, const char *&e) {
+    b = data_ + std::min(pos_, size_);
+    e = data_ + size_;
+    pos_ = size_;
+  }
 
  private:
   std::string path_;
@@ -84,6 +95,103 @@ struct LineParser {
     return true;
   }
 };
+
+// Numbers read straight from the mapped line [p, e) with std::from_chars: no copy, no locale, no errno.  A token that from_chars does not
+// take exactly like strtoll / strtod would (out-of-range values, hexadecimal floats, anything not followed by white space or the end of the
+// line) makes the caller fall back to LineParser for that line, so every line is accepted, rejected and valued as before.
+struct LineCursor {
+  const char *p, *e;
+  bool clean = true;   // false: re-parse this line with LineParser
+  void skip() {
+    while (p < e && (*p == ' ' || *p == '\t')) ++p;
+    if (p + 1 < e && *p == '+' && ((p[1] >= '0' && p[1] <= '9') || p[1] == '.')) ++p;
+  }
+  bool delimited() const { return p == e || *p == ' ' || *p == '\t'; }
+  bool integer(long long &v) {
+    skip();
+    auto r = std::from_chars(p, e, v);
+    if (r.ec != std::errc() || r.ptr == p) { clean = false; return false; }
+    p = r.ptr;
+    if (!delimited()) clean = false;
+    return clean;
+  }
+  bool real(double &v) {
+    skip();
+    auto r = std::from_chars(p, e, v);
+    if (r.ec != std::errc() || r.ptr == p) { clean = false; return false; }
+    p = r.ptr;
+    if (!delimited()) clean = false;
+    return clean;
+  }
+};
+
+// One body line "i j [re [im]]" of a coordinate file (MatrixMarket entries, HYPRE-IJ matrix rows).  Returns false for a blank line and,
+// when percent_comments is set, for a '%' comment; throws on a malformed line.  Missing value fields keep what the caller put there.
+inline bool parse_entry_line(const char *b, const char *e, bool percent_comments, bool pattern, bool cplx, const std::string &path,
+                             long long &i, long long &j, double &re, double &im) {
+  if ((percent_comments && b < e && *b == '%') || blank(b, e)) return false;
+  LineCursor c{b, e};
+  if (c.integer(i) && c.integer(j) && (pattern || c.real(re)) && cplx) c.real(im);
+  if (!c.clean) {   // anything from_chars does not take like strtoll / strtod: the bounded-copy parser decides
+    LineParser slow;
+    slow.set(b, e);
+    if (!slow.integer(i) || !slow.integer(j)) throw std::runtime_error("Malformed entry line in " + path);
+    if (!pattern && !slow.real(re)) throw std::runtime_error("Malformed entry line in " + path);
+    if (cplx && !slow.real(im)) throw std::runtime_error("complex_numbers: missing imaginary part in " + path);
+  }
+  return true;
+}
+
+// host threads a loader may use: the cores this process may run on, divided by the ranks that read at the same time, at most 32
+inline int loader_threads(int ranks_on_host) {
+  int avail = (int)std::thread::hardware_concurrency();
+  cpu_set_t set;
+  if (sched_getaffinity(0, sizeof(set), &set) == 0) avail = CPU_COUNT(&set);
+  return std::max(1, std::min(avail / std::max(1, ranks_on_host), 32));
+}
+
+// Body lines of a text file from the cursor to the end, parsed by `threads` host threads: the byte range is cut at line boundaries,
+// piece k is handed line by line to per_line(k, b, e) (line without its terminator; CR of a CRLF pair removed), and the caller appends
+// what the pieces produced in the order k = 0, 1, ... -- exactly what one reader walking the file would have produced.  The text
+// loaders of the mini-app are single-threaded fscanf loops (/root/reference/src/HypreSystem.cpp:1181-1247,1717-1850); a 50 M-row system
+// is tens of GB of text.  An exception thrown by per_line in any piece is rethrown (the one of the earliest piece).
+template <class PerLine>
+void read_lines_parallel(TextFile &f, int threads, PerLine per_line) {
+  const char *b, *e;
+  f.take_rest(b, e);
+  const size_t total = (size_t)(e - b);
+  threads = (int)std::max<size_t>(1, std::min<size_t>((size_t)threads, total / (1 << 16) + 1));   // small files: one piece
+  std::vector<const char *> cut((size_t)threads + 1, e);
+  cut[0] = b;
+  for (int k = 1; k < threads; ++k) {
+    const char *q = b + total * (size_t)k / (size_t)threads;
+    if (q < cut[k - 1]) q = cut[k - 1];
+    const char *nl = (const char *)memchr(q, '\n', (size_t)(e - q));
+    cut[k] = nl ? nl + 1 : e;
+  }
+  std::vector<std::exception_ptr> err((size_t)threads);
+  auto work = [&](int k) {
+    try {
+      const char *p = cut[k], *end = cut[k + 1];
+      while (p < end) {
+        const char *nl = (const char *)memchr(p, '\n', (size_t)(end - p));
+        const char *le = nl ? nl : end;
+        const char *next = nl ? nl + 1 : end;
+        if (le > p && le[-1] == '\r') --le;
+        per_line(k, p, le);
+        p = next;
+      }
+    } catch (...) {
+      err[k] = std::current_exception();
+    }
+  };
+  std::vector<std::thread> th;
+  for (int k = 1; k < threads; ++k) th.emplace_back(work, k);
+  work(0);
+  for (auto &t : th) t.join();
+  for (auto &x : err)
+    if (x) std::rethrow_exception(x);
+}
 
 struct MMBanner {
   bool coordinate = false, array = false, complex_field = false, pattern = false, integer_field = false;
